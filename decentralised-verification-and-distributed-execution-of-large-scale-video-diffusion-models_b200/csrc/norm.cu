@@ -1,0 +1,325 @@
+// HBM-bound normalisation / layout kernels of the UNet3D ([UPSTREAM diffusers] ResnetBlock2D,
+// TemporalConvLayer, Transformer2DModel, TransformerTemporalModel, BasicTransformerBlock):
+//   * GroupNorm(32) (+SiLU) over channels-last rows, statistics per (item, group) where an item is a
+//     frame (spatial norms) or a whole batch element (temporal norms over [B,C,F,H,W])
+//   * LayerNorm over channels
+//   * nearest 2x upsample, channel concat, explicit im2col (fallback / stride-2 cross-check)
+// All 128-bit vectorised, 8 bf16 per thread per access, fp32 math.
+#include "common.cuh"
+#include "ops.h"
+
+namespace b2v {
+namespace {
+
+// ---------------- GroupNorm ----------------
+// pass 1: per-(item, group) sum / sum of squares. grid = (row_splits, n_items); block = 64 x 4 threads:
+// threadIdx.x walks the 8-channel vectors of a row (coalesced 1 KiB per 64 threads), threadIdx.y the rows.
+// C/groups is always even, so a bf16 pair never straddles two groups: partial sums are kept per pair in
+// registers, flushed once per thread through shared-memory atomics, then one fp64 atomic per (CTA, group).
+constexpr int GN_TX = 64, GN_TY = 4, GN_THREADS = GN_TX * GN_TY;
+
+template <int ITERS>
+__global__ void __launch_bounds__(GN_THREADS)
+gn_stats_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat16* __restrict__ x2, int C2,
+                int64_t rows_per_item, int groups, double* __restrict__ stats) {
+  extern __shared__ float sh[];  // [2][groups]
+  const int C = C1 + C2;
+  const int vecs = C >> 3;
+  const int cpg = C / groups;
+  const int item = blockIdx.y;
+  const int tx = threadIdx.x & (GN_TX - 1), ty = threadIdx.x / GN_TX;
+  for (int i = threadIdx.x; i < 2 * groups; i += GN_THREADS) sh[i] = 0.f;
+  __syncthreads();
+  const int64_t rows_per_cta = (rows_per_item + gridDim.x - 1) / gridDim.x;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta;
+  int64_t r1 = r0 + rows_per_cta;
+  if (r1 > rows_per_item) r1 = rows_per_item;
+  float s[ITERS][4], ss[ITERS][4];
+#pragma unroll
+  for (int i = 0; i < ITERS; ++i)
+#pragma unroll
+    for (int j = 0; j < 4; ++j) { s[i][j] = 0.f; ss[i][j] = 0.f; }
+  for (int64_t r = r0 + ty; r < r1; r += GN_TY) {
+    const int64_t grow = (int64_t)item * rows_per_item + r;
+#pragma unroll
+    for (int i = 0; i < ITERS; ++i) {
+      const int c = (tx + i * GN_TX) << 3;
+      if (c < C) {
+        uint4 u;
+        if (c < C1) u = __ldg(reinterpret_cast<const uint4*>(x1 + grow * C1 + c));
+        else u = __ldg(reinterpret_cast<const uint4*>(x2 + grow * C2 + (c - C1)));
+        const uint32_t uu[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 f = unpack_bf16x2(uu[j]);
+          s[i][j] += f.x + f.y;
+          ss[i][j] += f.x * f.x + f.y * f.y;
+        }
+      }
+    }
+  }
+#pragma unroll
+  for (int i = 0; i < ITERS; ++i) {
+    const int c = (tx + i * GN_TX) << 3;
+    if (c < C) {
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const int g = (c + 2 * j) / cpg;
+        atomicAdd(&sh[g], s[i][j]);
+        atomicAdd(&sh[groups + g], ss[i][j]);
+      }
+    }
+  }
+  __syncthreads();
+  for (int i = threadIdx.x; i < groups; i += GN_THREADS) {
+    atomicAdd(&stats[((int64_t)item * groups + i) * 2], (double)sh[i]);
+    atomicAdd(&stats[((int64_t)item * groups + i) * 2 + 1], (double)sh[groups + i]);
+  }
+}
+
+// pass 2: y = (x - mean) * rstd * gamma + beta, optional SiLU. One thread per 8-channel vector.
+__global__ void __launch_bounds__(256)
+gn_apply_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat16* __restrict__ x2, int C2,
+                const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
+                int64_t total_rows, int64_t rows_per_item, int groups, float eps, int silu,
+                const double* __restrict__ stats) {
+  const int C = C1 + C2;
+  const int vecs = C >> 3;
+  const int cpg = C / groups;
+  const double cnt = (double)rows_per_item * (double)cpg;
+  const int64_t total = total_rows * vecs;
+  for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < total; w += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t grow = w / vecs;
+    const int c = (int)(w % vecs) << 3;
+    const int64_t item = grow / rows_per_item;
+    uint4 u;
+    if (c < C1) u = __ldg(reinterpret_cast<const uint4*>(x1 + grow * C1 + c));
+    else u = __ldg(reinterpret_cast<const uint4*>(x2 + grow * C2 + (c - C1)));
+    const uint32_t uu[4] = {u.x, u.y, u.z, u.w};
+    float f[8];
+#pragma unroll
+    for (int j = 0; j < 4; ++j) {
+      const float2 t = unpack_bf16x2(uu[j]);
+      f[2 * j] = t.x; f[2 * j + 1] = t.y;
+    }
+    const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + c)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + c + 4));
+    const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + c)), b1 = __ldg(reinterpret_cast<const float4*>(beta + c + 4));
+    const float gm[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+    const float bt[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+    int last_g = -1;
+    float mean = 0.f, rstd = 0.f;
+#pragma unroll
+    for (int j = 0; j < 8; ++j) {
+      const int g = (c + j) / cpg;
+      if (g != last_g) {
+        const double sm = stats[(item * groups + g) * 2], sq = stats[(item * groups + g) * 2 + 1];
+        const double m = sm / cnt;
+        double var = sq / cnt - m * m;
+        if (var < 0.0) var = 0.0;
+        mean = (float)m;
+        rstd = (float)(1.0 / sqrt(var + (double)eps));
+        last_g = g;
+      }
+      float v = (f[j] - mean) * rstd * gm[j] + bt[j];
+      if (silu) v = silu_f(v);
+      f[j] = v;
+    }
+    uint4 o;
+    o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
+    o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
+    *reinterpret_cast<uint4*>(y + grow * C + c) = o;
+  }
+}
+
+// ---------------- LayerNorm: one warp per row, row cached in registers ----------------
+template <int MAXV>  // max 8-channel vectors per lane
+__global__ void __launch_bounds__(256)
+layer_norm_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
+                  __nv_bfloat16* __restrict__ y, int64_t rows, int C, float eps) {
+  const int lane = threadIdx.x & 31;
+  const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
+  const int vecs = C >> 3;
+  for (int64_t r = warp; r < rows; r += nwarps) {
+    float f[MAXV][8];
+    float s = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int v = lane + 32 * i;
+      if (v < vecs) {
+        const uint4 u = __ldg(reinterpret_cast<const uint4*>(x + r * C + (v << 3)));
+        const uint32_t uu[4] = {u.x, u.y, u.z, u.w};
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 t = unpack_bf16x2(uu[j]);
+          f[i][2 * j] = t.x; f[i][2 * j + 1] = t.y;
+          s += t.x + t.y;
+        }
+      }
+    }
+    const float mean = warp_sum(s) / (float)C;
+    float ss = 0.f;
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int v = lane + 32 * i;
+      if (v < vecs) {
+#pragma unroll
+        for (int j = 0; j < 8; ++j) { const float d = f[i][j] - mean; ss += d * d; }
+      }
+    }
+    const float rstd = rsqrtf(warp_sum(ss) / (float)C + eps);
+#pragma unroll
+    for (int i = 0; i < MAXV; ++i) {
+      const int v = lane + 32 * i;
+      if (v < vecs) {
+        const int c = v << 3;
+        const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + c)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + c + 4));
+        const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + c)), b1 = __ldg(reinterpret_cast<const float4*>(beta + c + 4));
+        const float gm[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
+        const float bt[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
+        float o[8];
+#pragma unroll
+        for (int j = 0; j < 8; ++j) o[j] = (f[i][j] - mean) * rstd * gm[j] + bt[j];
+        uint4 u;
+        u.x = pack_bf16x2(o[0], o[1]); u.y = pack_bf16x2(o[2], o[3]);
+        u.z = pack_bf16x2(o[4], o[5]); u.w = pack_bf16x2(o[6], o[7]);
+        *reinterpret_cast<uint4*>(y + r * C + c) = u;
+      }
+    }
+  }
+}
+
+// ---------------- layout helpers ----------------
+__global__ void upsample2x_kernel(const uint4* __restrict__ x, uint4* __restrict__ y, int N, int H, int W, int vecs) {
+  const int64_t total = (int64_t)N * (2 * H) * (2 * W) * vecs;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int v = (int)(i % vecs);
+    int64_t p = i / vecs;
+    const int ox = (int)(p % (2 * W)); p /= (2 * W);
+    const int oy = (int)(p % (2 * H));
+    const int n = (int)(p / (2 * H));
+    y[i] = __ldg(x + (((int64_t)n * H + (oy >> 1)) * W + (ox >> 1)) * vecs + v);
+  }
+}
+
+__global__ void concat_kernel(const uint4* __restrict__ a, int va, const uint4* __restrict__ b, int vb,
+                              uint4* __restrict__ y, int64_t rows) {
+  const int vt = va + vb;
+  const int64_t total = rows * vt;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int64_t r = i / vt;
+    const int v = (int)(i % vt);
+    y[i] = v < va ? __ldg(a + r * va + v) : __ldg(b + r * vb + (v - va));
+  }
+}
+
+// explicit im2col: [N,H,W,C] -> [N*P*Q, 9*C] (tap-major, then channel), zero padded
+__global__ void im2col3x3_kernel(const uint4* __restrict__ x, uint4* __restrict__ col, int N, int H, int W, int vecs,
+                                 int stride, int P, int Q) {
+  const int64_t total = (int64_t)N * P * Q * 9 * vecs;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
+    const int v = (int)(i % vecs);
+    int64_t t = i / vecs;
+    const int tap = (int)(t % 9); t /= 9;
+    const int q = (int)(t % Q); t /= Q;
+    const int p = (int)(t % P);
+    const int n = (int)(t / P);
+    const int iy = p * stride - 1 + tap / 3, ix = q * stride - 1 + tap % 3;
+    uint4 val = make_uint4(0, 0, 0, 0);
+    if (iy >= 0 && iy < H && ix >= 0 && ix < W) val = __ldg(x + (((int64_t)n * H + iy) * W + ix) * vecs + v);
+    col[i] = val;
+  }
+}
+
+inline int grid_1d(int64_t work_items, int block, int per_sm) {
+  int64_t g = (work_items + block - 1) / block;
+  const int64_t cap = (int64_t)sm_count() * per_sm;
+  if (g > cap) g = cap;
+  return g < 1 ? 1 : (int)g;
+}
+
+}  // namespace
+
+int group_norm(const void* x1, int C1, const void* x2, int C2, const float* gamma, const float* beta, void* y,
+               int64_t n_items, int64_t rows_per_item, int groups, float eps, int silu, double* stats,
+               cudaStream_t s) {
+  const int C = C1 + C2;
+  B2V_CHECK(C % 8 == 0 && C1 % 8 == 0 && C % groups == 0 && (C / groups) % 2 == 0, "group_norm: C=%d (C1=%d) groups=%d unsupported", C, C1, groups);
+  B2V_CHECK(n_items > 0 && n_items < 65536 && rows_per_item > 0, "group_norm: bad item count");
+  B2V_CUDA_OK(cudaMemsetAsync(stats, 0, sizeof(double) * 2 * (size_t)n_items * groups, s));
+  // enough CTAs per item to fill the machine ~4x, at least 32 rows each
+  int64_t splits = ((int64_t)sm_count() * 4 + n_items - 1) / n_items;
+  const int64_t max_splits = (rows_per_item + 31) / 32;
+  if (splits > max_splits) splits = max_splits;
+  if (splits < 1) splits = 1;
+  dim3 grid((unsigned)splits, (unsigned)n_items);
+  const int iters = ((C >> 3) + GN_TX - 1) / GN_TX;
+  const size_t shb = sizeof(float) * 2 * groups;
+#define B2V_GN_STATS(I)                                                                                     \
+  gn_stats_kernel<I><<<grid, GN_THREADS, shb, s>>>((const __nv_bfloat16*)x1, C1, (const __nv_bfloat16*)x2, C2, \
+                                                   rows_per_item, groups, stats)
+  switch (iters) {
+    case 1: B2V_GN_STATS(1); break;
+    case 2: B2V_GN_STATS(2); break;
+    case 3: B2V_GN_STATS(3); break;
+    case 4: B2V_GN_STATS(4); break;
+    case 5: B2V_GN_STATS(5); break;
+    default: return fail(B2V_ERR_ARG, "group_norm: C=%d too wide (max 2560)", C);
+  }
+#undef B2V_GN_STATS
+  count_launch();
+  const int64_t total_rows = n_items * rows_per_item;
+  gn_apply_kernel<<<grid_1d(total_rows * (C >> 3), 256, 8), 256, 0, s>>>(
+      (const __nv_bfloat16*)x1, C1, (const __nv_bfloat16*)x2, C2, gamma, beta, (__nv_bfloat16*)y, total_rows,
+      rows_per_item, groups, eps, silu, stats);
+  count_launch();
+  B2V_CUDA_OK(launch_check());
+  return 0;
+}
+
+int layer_norm(const void* x, const float* gamma, const float* beta, void* y, int64_t rows, int C, float eps,
+               cudaStream_t s) {
+  B2V_CHECK(C % 8 == 0 && C <= 2048 && rows > 0, "layer_norm: C=%d unsupported", C);
+  const int vecs = C >> 3;
+  const int grid = grid_1d(rows * 32, 256, 8);
+  if (vecs <= 64)
+    layer_norm_kernel<2><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, gamma, beta, (__nv_bfloat16*)y, rows, C, eps);
+  else if (vecs <= 160)
+    layer_norm_kernel<5><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, gamma, beta, (__nv_bfloat16*)y, rows, C, eps);
+  else
+    layer_norm_kernel<8><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, gamma, beta, (__nv_bfloat16*)y, rows, C, eps);
+  count_launch();
+  B2V_CUDA_OK(launch_check());
+  return 0;
+}
+
+int upsample2x(const void* x, void* y, int N, int H, int W, int C, cudaStream_t s) {
+  B2V_CHECK(C % 8 == 0, "upsample2x: C %% 8");
+  const int64_t total = (int64_t)N * 4 * H * W * (C >> 3);
+  upsample2x_kernel<<<grid_1d(total, 256, 8), 256, 0, s>>>((const uint4*)x, (uint4*)y, N, H, W, C >> 3);
+  count_launch();
+  B2V_CUDA_OK(launch_check());
+  return 0;
+}
+
+int concat_channels(const void* a, int Ca, const void* b, int Cb, void* y, int64_t rows, cudaStream_t s) {
+  B2V_CHECK(Ca % 8 == 0 && Cb % 8 == 0, "concat: C %% 8");
+  const int64_t total = rows * ((Ca + Cb) >> 3);
+  concat_kernel<<<grid_1d(total, 256, 8), 256, 0, s>>>((const uint4*)a, Ca >> 3, (const uint4*)b, Cb >> 3, (uint4*)y,
+                                                       rows);
+  count_launch();
+  B2V_CUDA_OK(launch_check());
+  return 0;
+}
+
+int im2col3x3(const void* x, void* col, int N, int H, int W, int C, int stride, cudaStream_t s) {
+  B2V_CHECK(C % 8 == 0, "im2col: C %% 8");
+  const int P = (H - 1) / stride + 1, Q = (W - 1) / stride + 1;
+  const int64_t total = (int64_t)N * P * Q * 9 * (C >> 3);
+  im2col3x3_kernel<<<grid_1d(total, 256, 8), 256, 0, s>>>((const uint4*)x, (uint4*)col, N, H, W, C >> 3, stride, P, Q);
+  count_launch();
+  B2V_CUDA_OK(launch_check());
+  return 0;
+}
+
+}  // namespace b2v

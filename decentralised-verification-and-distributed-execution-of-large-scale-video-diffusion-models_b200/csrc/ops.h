@@ -1,0 +1,48 @@
+// Internal (C++) launch API of the kernels; capi.cu exposes the tested subset through include/b2v.h.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+#include "tmap.h"
+
+namespace b2v {
+
+// norm.cu
+int group_norm(const void* x1, int C1, const void* x2, int C2, const float* gamma, const float* beta, void* y,
+               int64_t n_items, int64_t rows_per_item, int groups, float eps, int silu, double* stats,
+               cudaStream_t s);
+int layer_norm(const void* x, const float* gamma, const float* beta, void* y, int64_t rows, int C, float eps,
+               cudaStream_t s);
+int upsample2x(const void* x, void* y, int N, int H, int W, int C, cudaStream_t s);
+int concat_channels(const void* a, int Ca, const void* b, int Cb, void* y, int64_t rows, cudaStream_t s);
+int im2col3x3(const void* x, void* col, int N, int H, int W, int C, int stride, cudaStream_t s);
+
+// attention.cu
+struct AttnArgs {
+  const void* q = nullptr;  // bf16, row (b, s) at q + (b*Sq + s)*ldq, head h at column h*64
+  const void* k = nullptr;  // bf16, row (b/kv_group, s) at k + ((b/kv_group)*Skv + s)*ldkv
+  const void* v = nullptr;
+  void* out = nullptr;
+  int64_t ldq = 0, ldkv = 0, ldo = 0;
+  int nb = 0, heads = 0, Sq = 0, Skv = 0, kv_group = 1;
+  float scale = 0.125f;
+};
+int attention(const AttnArgs& a, cudaStream_t s);
+int temporal_attention(const void* qkv, int64_t ld, int q_off, int k_off, int v_off, void* out, int64_t ldo, int B,
+                       int F, int64_t HW, int heads, float scale, cudaStream_t s);
+
+// small.cu : SIMT kernels for the thin ends of the network
+int time_embedding(float timestep, int B, int dim0, const float* w1, const float* b1, const float* w2, const float* b2,
+                   int temb_dim, float* silu_emb_out /*[B,temb_dim] = SiLU(emb)*/, cudaStream_t s);
+// out[b, n] = bias[n] + sum_k W[n,k] * in[b,k]  (fp32, tiny M)
+int small_linear(const float* in, const float* w, const float* bias, float* out, int B, int N, int K, cudaStream_t s);
+// conv_in: NCFHW (io dtype) -> NHWC bf16, 3x3 pad 1, Cin tiny
+int conv_in_3x3(const void* x, int io_dtype, const float* w /*[Cout][Cin][3][3]*/, const float* bias, void* y, int B,
+                int Cin, int F, int H, int W, int Cout, cudaStream_t s);
+// conv_out: NHWC bf16 -> NCFHW (io dtype), 3x3 pad 1, Cout tiny
+int conv_out_3x3(const void* x, const float* w /*[Cout][3][3][Cin]*/, const float* bias, void* y, int io_dtype, int B,
+                 int Cin, int F, int H, int W, int Cout, cudaStream_t s);
+// dtype conversion of the text embeddings to bf16 rows
+int to_bf16(const void* x, int dtype, void* y, int64_t n, cudaStream_t s);
+
+}  // namespace b2v

@@ -1,0 +1,50 @@
+// Host-side TMA descriptor (CUtensorMap) construction and the argument structs of the GEMM entry points.
+#pragma once
+#include <cuda.h>
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace b2v {
+
+// bf16 tensor, 128-byte swizzle, zero fill out of bounds.
+int tmap_tiled_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                    const uint32_t* box);
+int tmap_im2col_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                     const int* lower, const int* upper, uint32_t channels_per_pixel, uint32_t pixels_per_column,
+                     const uint32_t* elem_strides);
+
+struct GemmArgs {
+  const void* a = nullptr;  // bf16 [M, lda]
+  int64_t lda = 0;          // 0 -> Kc
+  const void* w = nullptr;  // bf16 [N, taps*Kc]
+  const float* bias = nullptr;
+  const float* rowbias = nullptr;
+  int64_t rows_per_group = 0;
+  const void* residual = nullptr;  // bf16 [M, ldo]
+  void* out = nullptr;             // bf16 [M, ldo]
+  int64_t ldo = 0;                 // 0 -> N (N/2 for GEGLU)
+  int64_t M = 0;
+  int N = 0;
+  int Kc = 0;
+  int taps = 1;
+  int64_t tap_row_stride = 0;
+  int64_t rows_per_batch = 0;  // 0 -> M
+  int flags = 0;
+};
+
+struct ConvArgs {
+  const void* x = nullptr;  // bf16 NHWC
+  const void* w = nullptr;  // bf16 [Cout][3][3][Cin]
+  const float* bias = nullptr;
+  const float* rowbias = nullptr;
+  int64_t rows_per_group = 0;
+  const void* residual = nullptr;
+  void* out = nullptr;  // bf16 [N,P,Q,Cout]
+  int N = 0, H = 0, W = 0, Cin = 0, Cout = 0, stride = 1;
+};
+
+int pick_bn(int N, bool geglu);
+int gemm_tiled(const GemmArgs& g, cudaStream_t s);
+int conv3x3_im2col(const ConvArgs& c, cudaStream_t s);
+
+}  // namespace b2v

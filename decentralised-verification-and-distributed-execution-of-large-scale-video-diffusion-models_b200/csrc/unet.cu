@@ -1,0 +1,885 @@
+// UNet3DConditionModel forward on the b2v kernels.
+// Restates what `pipe.unet(x, t, encoder_hidden_states=emb).sample` computes at
+// Distribution/strategies/chunk_only.py:71, fsdp_chunked_coherent.py:140 and InferNet/neurons/miner.py:581
+// ([UPSTREAM diffusers] UNet3DConditionModel, Zeroscope / ModelScope-T2V configuration; module list in
+// SURVEY.md §8a U1-U8). Weights arrive under their diffusers state_dict names and are repacked once:
+//   * every GEMM operand to bf16, K-major [N][K]; conv kernels to [Cout][tap][Cin]
+//   * q/k/v projections fused into one [3C][C] operand; GEGLU value/gate rows interleaved per 128 columns
+//   * biases, norm affines, the time MLP and conv_in/conv_out stay fp32
+// Activations are channels-last bf16 rows [(b,f,y,x), C]; the (b f) c h w <-> b c f h w permutes of the
+// reference vanish because temporal ops address frames by a row stride.
+#include <map>
+#include <memory>
+#include <string>
+#include <vector>
+
+#include "common.cuh"
+#include "ops.h"
+
+namespace b2v {
+namespace {
+
+typedef __nv_bfloat16 bf16;
+
+// ------------------------------------------------------------------------------------------------
+// weight packing kernels
+// ------------------------------------------------------------------------------------------------
+template <typename TI>
+__global__ void cast_to_f32_kernel(const TI* __restrict__ in, float* __restrict__ out, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = DT<TI>::ld(in + i);
+}
+__global__ void f32_to_bf16_kernel(const float* __restrict__ in, bf16* __restrict__ out, int64_t n) {
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
+    out[i] = __float2bfloat16_rn(in[i]);
+}
+// [Cout][Cin][taps] -> [Cout][taps][Cin]
+template <typename TO>
+__global__ void permute_taps_kernel(const float* __restrict__ in, TO* __restrict__ out, int Cout, int Cin, int taps) {
+  const int64_t n = (int64_t)Cout * Cin * taps;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int ci = (int)(i % Cin);
+    const int tap = (int)((i / Cin) % taps);
+    const int co = (int)(i / ((int64_t)Cin * taps));
+    DT<TO>::st(out + i, in[((int64_t)co * Cin + ci) * taps + tap]);
+  }
+}
+// GEGLU: proj.weight rows [0,H) are the value half, [H,2H) the gate half (H = 4*dim).
+// packed row j*256 + i       (i < 128) = value row j*128 + i
+// packed row j*256 + 128 + i (i < 128) = gate  row j*128 + i
+__global__ void pack_geglu_kernel(const float* __restrict__ w, const float* __restrict__ b, bf16* __restrict__ wo,
+                                  float* __restrict__ bo, int H, int K) {
+  const int64_t n = (int64_t)2 * H * K;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int k = (int)(i % K);
+    const int r = (int)(i / K);
+    const int tile = r / 256, within = r % 256;
+    const int src = within < 128 ? tile * 128 + within : H + tile * 128 + (within - 128);
+    wo[i] = __float2bfloat16_rn(w[(int64_t)src * K + k]);
+    if (k == 0) bo[r] = b[src];
+  }
+}
+
+inline int ew_grid(int64_t n) {
+  int64_t g = (n + 255) / 256;
+  if (g > 148 * 16) g = 148 * 16;
+  return g < 1 ? 1 : (int)g;
+}
+
+// ------------------------------------------------------------------------------------------------
+// workspace allocator: first-fit over [0, cap) with coalescing; deterministic for a given call sequence, so
+// addresses repeat across forwards of the same shape. In dry mode nothing is touched, only the peak is tracked.
+// ------------------------------------------------------------------------------------------------
+class Arena {
+ public:
+  void reset(uint8_t* base, size_t cap, bool dry) {
+    base_ = dry ? reinterpret_cast<uint8_t*>((uintptr_t)1 << 30) : base;  // dry runs never dereference
+    cap_ = cap; dry_ = dry; peak_ = 0; failed_ = false;
+    free_.clear(); used_.clear();
+    free_[0] = dry ? (size_t)1 << 60 : cap;
+  }
+  void* alloc(size_t bytes) {
+    bytes = (bytes + 1023) & ~(size_t)1023;  // 1 KiB granularity keeps every tensor TMA/vector aligned
+    if (bytes == 0) bytes = 1024;
+    for (auto it = free_.begin(); it != free_.end(); ++it) {
+      if (it->second >= bytes) {
+        const size_t off = it->first, rest = it->second - bytes;
+        free_.erase(it);
+        if (rest) free_[off + bytes] = rest;
+        used_[off] = bytes;
+        if (off + bytes > peak_) peak_ = off + bytes;
+        return base_ + off;
+      }
+    }
+    failed_ = true;
+    return nullptr;
+  }
+  void release(void* p) {
+    if (!p) return;
+    const size_t off = (size_t)((uint8_t*)p - base_);
+    auto u = used_.find(off);
+    if (u == used_.end()) return;
+    size_t o = off, sz = u->second;
+    used_.erase(u);
+    auto nx = free_.lower_bound(o);
+    if (nx != free_.end() && o + sz == nx->first) { sz += nx->second; nx = free_.erase(nx); }
+    if (nx != free_.begin()) {
+      auto pv = std::prev(nx);
+      if (pv->first + pv->second == o) { o = pv->first; sz += pv->second; free_.erase(pv); }
+    }
+    free_[o] = sz;
+  }
+  size_t peak() const { return peak_; }
+  bool dry() const { return dry_; }
+  bool failed() const { return failed_; }
+
+ private:
+  uint8_t* base_ = nullptr;
+  size_t cap_ = 0, peak_ = 0;
+  bool dry_ = false, failed_ = false;
+  std::map<size_t, size_t> free_, used_;
+};
+
+// ------------------------------------------------------------------------------------------------
+// packed weights
+// ------------------------------------------------------------------------------------------------
+struct Norm { float* g = nullptr; float* b = nullptr; int C = 0; };
+struct Lin { bf16* w = nullptr; float* b = nullptr; int N = 0, K = 0; };  // w [N][K]
+struct Conv { bf16* w = nullptr; float* b = nullptr; int Cout = 0, Cin = 0; };  // w [Cout][9][Cin]
+
+struct ResnetW {
+  int Cin = 0, Cout = 0;
+  Norm n1, n2;
+  Conv c1, c2;
+  float* temb_w = nullptr;  // fp32 [Cout][temb]
+  float* temb_b = nullptr;
+  bool has_sc = false;
+  Lin sc;
+  float* rowbias = nullptr;  // [maxB][Cout] scratch filled every forward
+};
+struct TempConvW { int C = 0; Norm n[4]; Lin c[4]; };  // c: N=C, K=3C ([C][3][C])
+struct BlockW {                                        // BasicTransformerBlock
+  int dim = 0, heads = 0;
+  bool cross = false;
+  Norm ln1, ln2, ln3;
+  Lin qkv1, o1;
+  Lin q2, kv2;   // cross attention (kv2: N=2*dim, K=cross_dim)
+  Lin qkv2;      // double self-attention
+  Lin o2, ff1, ff2;
+};
+struct SpatialW { int C = 0; Norm norm; Lin proj_in, proj_out; BlockW blk; };
+struct TemporalW { int C = 0, inner = 0; Norm norm; Lin proj_in, proj_out; BlockW blk; };
+struct LevelW {
+  std::vector<ResnetW> resnets;
+  std::vector<TempConvW> temp_convs;
+  std::vector<SpatialW> attns;
+  std::vector<TemporalW> tattns;
+  bool has_sampler = false;
+  Conv sampler;
+};
+
+}  // namespace
+}  // namespace b2v
+
+using namespace b2v;
+
+struct b2v_unet3d {
+  b2v_unet3d_config cfg;
+  int device = 0;
+  bool finalized = false;
+  int64_t param_count = 0;
+  std::map<std::string, std::pair<float*, std::vector<int64_t>>> raw;  // device fp32 copies until finalize
+  std::vector<void*> owned;                                             // packed device allocations
+
+  // packed
+  float *conv_in_w = nullptr, *conv_in_b = nullptr;
+  float *te_w1 = nullptr, *te_b1 = nullptr, *te_w2 = nullptr, *te_b2 = nullptr;
+  TemporalW transformer_in;
+  std::vector<LevelW> down, up;
+  LevelW mid;
+  Norm norm_out;
+  float *conv_out_w = nullptr, *conv_out_b = nullptr;
+  int temb_dim = 0;
+  static constexpr int kMaxB = 8;
+  float* temb_scratch = nullptr;  // [kMaxB*temb] silu(emb) + sinusoid + hidden
+  std::vector<ResnetW*> all_resnets;
+};
+
+namespace b2v {
+namespace {
+
+// ------------------------------------------------------------------------------------------------
+// loader helpers (run at finalize)
+// ------------------------------------------------------------------------------------------------
+struct Loader {
+  b2v_unet3d* u;
+  std::string err;
+  cudaStream_t s = 0;
+
+  template <typename T>
+  T* dalloc(size_t n) {
+    void* p = nullptr;
+    if (cudaMalloc(&p, n * sizeof(T)) != cudaSuccess) { err = "cudaMalloc failed"; return nullptr; }
+    u->owned.push_back(p);
+    return (T*)p;
+  }
+  const float* get(const std::string& name, std::vector<int64_t> shape) {
+    auto it = u->raw.find(name);
+    if (it == u->raw.end()) { if (err.empty()) err = "missing weight: " + name; return nullptr; }
+    if (it->second.second != shape) {
+      if (err.empty()) {
+        err = "shape mismatch for " + name + ": got [";
+        for (auto d : it->second.second) err += std::to_string(d) + ",";
+        err += "] want [";
+        for (auto d : shape) err += std::to_string(d) + ",";
+        err += "]";
+      }
+      return nullptr;
+    }
+    return it->second.first;
+  }
+  float* vec(const std::string& name, int n) {
+    const float* src = get(name, {n});
+    if (!src) return nullptr;
+    float* d = dalloc<float>((size_t)n);
+    if (d) cudaMemcpyAsync(d, src, sizeof(float) * n, cudaMemcpyDeviceToDevice, s);
+    return d;
+  }
+  Norm norm(const std::string& p, int C) {
+    Norm n; n.C = C; n.g = vec(p + ".weight", C); n.b = vec(p + ".bias", C); return n;
+  }
+  bf16* mat_bf16(const float* src, int64_t n) {
+    bf16* d = dalloc<bf16>((size_t)n);
+    if (d && src) f32_to_bf16_kernel<<<ew_grid(n), 256, 0, s>>>(src, d, n);
+    return d;
+  }
+  Lin lin(const std::string& p, int N, int K, bool bias) {
+    Lin l; l.N = N; l.K = K;
+    const float* w = get(p + ".weight", {N, K});
+    if (w) l.w = mat_bf16(w, (int64_t)N * K);
+    if (bias) l.b = vec(p + ".bias", N);
+    return l;
+  }
+  // several [Ni][K] matrices stacked row-wise into one operand (fused q/k/v)
+  Lin lin_stack(const std::vector<std::string>& names, int Neach, int K) {
+    Lin l; l.N = Neach * (int)names.size(); l.K = K;
+    l.w = dalloc<bf16>((size_t)l.N * K);
+    for (size_t i = 0; i < names.size(); ++i) {
+      const float* w = get(names[i] + ".weight", {Neach, K});
+      if (w && l.w) f32_to_bf16_kernel<<<ew_grid((int64_t)Neach * K), 256, 0, s>>>(w, l.w + i * (size_t)Neach * K, (int64_t)Neach * K);
+    }
+    return l;
+  }
+  Lin geglu(const std::string& p, int dim) {  // proj: [8*dim][dim]
+    const int H = 4 * dim;
+    Lin l; l.N = 2 * H; l.K = dim;
+    const float* w = get(p + ".weight", {2 * H, dim});
+    const float* b = get(p + ".bias", {2 * H});
+    l.w = dalloc<bf16>((size_t)2 * H * dim);
+    l.b = dalloc<float>((size_t)2 * H);
+    if (w && b && l.w && l.b) pack_geglu_kernel<<<ew_grid((int64_t)2 * H * dim), 256, 0, s>>>(w, b, l.w, l.b, H, dim);
+    return l;
+  }
+  Conv conv3x3(const std::string& p, int Cout, int Cin) {
+    Conv c; c.Cout = Cout; c.Cin = Cin;
+    const float* w = get(p + ".weight", {Cout, Cin, 3, 3});
+    c.w = dalloc<bf16>((size_t)Cout * Cin * 9);
+    if (w && c.w) permute_taps_kernel<bf16><<<ew_grid((int64_t)Cout * Cin * 9), 256, 0, s>>>(w, c.w, Cout, Cin, 9);
+    c.b = vec(p + ".bias", Cout);
+    return c;
+  }
+  Lin conv1x1(const std::string& p, int Cout, int Cin) {
+    Lin l; l.N = Cout; l.K = Cin;
+    const float* w = get(p + ".weight", {Cout, Cin, 1, 1});
+    if (w) l.w = mat_bf16(w, (int64_t)Cout * Cin);
+    l.b = vec(p + ".bias", Cout);
+    return l;
+  }
+  Lin tconv(const std::string& p, int C) {  // Conv3d [C][C][3][1][1] -> [C][3][C]
+    Lin l; l.N = C; l.K = 3 * C;
+    const float* w = get(p + ".weight", {C, C, 3, 1, 1});
+    l.w = dalloc<bf16>((size_t)C * C * 3);
+    if (w && l.w) permute_taps_kernel<bf16><<<ew_grid((int64_t)C * C * 3), 256, 0, s>>>(w, l.w, C, C, 3);
+    l.b = vec(p + ".bias", C);
+    return l;
+  }
+  ResnetW resnet(const std::string& p, int Cin, int Cout) {
+    ResnetW r; r.Cin = Cin; r.Cout = Cout;
+    r.n1 = norm(p + ".norm1", Cin);
+    r.c1 = conv3x3(p + ".conv1", Cout, Cin);
+    const float* tw = get(p + ".time_emb_proj.weight", {Cout, u->temb_dim});
+    r.temb_w = dalloc<float>((size_t)Cout * u->temb_dim);
+    if (tw && r.temb_w) cudaMemcpyAsync(r.temb_w, tw, sizeof(float) * (size_t)Cout * u->temb_dim, cudaMemcpyDeviceToDevice, s);
+    r.temb_b = vec(p + ".time_emb_proj.bias", Cout);
+    r.n2 = norm(p + ".norm2", Cout);
+    r.c2 = conv3x3(p + ".conv2", Cout, Cout);
+    r.has_sc = Cin != Cout;
+    if (r.has_sc) r.sc = conv1x1(p + ".conv_shortcut", Cout, Cin);
+    r.rowbias = dalloc<float>((size_t)b2v_unet3d::kMaxB * Cout);
+    return r;
+  }
+  TempConvW temp_conv(const std::string& p, int C) {
+    TempConvW t; t.C = C;
+    const char* gn[4] = {".conv1.0", ".conv2.0", ".conv3.0", ".conv4.0"};
+    const char* cv[4] = {".conv1.2", ".conv2.3", ".conv3.3", ".conv4.3"};
+    for (int i = 0; i < 4; ++i) { t.n[i] = norm(p + gn[i], C); t.c[i] = tconv(p + cv[i], C); }
+    return t;
+  }
+  BlockW block(const std::string& p, int dim, int heads, bool cross, int cross_dim) {
+    BlockW b; b.dim = dim; b.heads = heads; b.cross = cross;
+    b.ln1 = norm(p + ".norm1", dim);
+    b.qkv1 = lin_stack({p + ".attn1.to_q", p + ".attn1.to_k", p + ".attn1.to_v"}, dim, dim);
+    b.o1 = lin(p + ".attn1.to_out.0", dim, dim, true);
+    b.ln2 = norm(p + ".norm2", dim);
+    if (cross) {
+      b.q2 = lin(p + ".attn2.to_q", dim, dim, false);
+      b.kv2 = lin_stack({p + ".attn2.to_k", p + ".attn2.to_v"}, dim, cross_dim);
+    } else {
+      b.qkv2 = lin_stack({p + ".attn2.to_q", p + ".attn2.to_k", p + ".attn2.to_v"}, dim, dim);
+    }
+    b.o2 = lin(p + ".attn2.to_out.0", dim, dim, true);
+    b.ln3 = norm(p + ".norm3", dim);
+    b.ff1 = geglu(p + ".ff.net.0.proj", dim);
+    b.ff2 = lin(p + ".ff.net.2", dim, 4 * dim, true);
+    return b;
+  }
+  SpatialW spatial(const std::string& p, int C) {
+    SpatialW a; a.C = C;
+    a.norm = norm(p + ".norm", C);
+    a.proj_in = lin(p + ".proj_in", C, C, true);
+    a.blk = block(p + ".transformer_blocks.0", C, C / u->cfg.attention_head_dim, true, u->cfg.cross_attention_dim);
+    a.proj_out = lin(p + ".proj_out", C, C, true);
+    return a;
+  }
+  TemporalW temporal(const std::string& p, int C, int heads) {
+    TemporalW a; a.C = C; a.inner = heads * u->cfg.attention_head_dim;
+    a.norm = norm(p + ".norm", C);
+    a.proj_in = lin(p + ".proj_in", a.inner, C, true);
+    a.blk = block(p + ".transformer_blocks.0", a.inner, heads, false, 0);
+    a.proj_out = lin(p + ".proj_out", C, a.inner, true);
+    return a;
+  }
+};
+
+// ------------------------------------------------------------------------------------------------
+// forward context
+// ------------------------------------------------------------------------------------------------
+struct Ctx {
+  b2v_unet3d* u;
+  Arena arena;
+  cudaStream_t s;
+  int B, F;
+  int status = 0;
+  double flops = 0.0;  // algorithmic FLOPs (GEMM/conv/attention, MAC = 2)
+  const bf16* text = nullptr;  // [B*text_len, cross_dim]
+
+  bool dry() const { return arena.dry(); }
+  bf16* act(int64_t rows, int C) {
+    void* p = arena.alloc((size_t)rows * C * sizeof(bf16));
+    if (!p && status == 0) status = fail(B2V_ERR_WORKSPACE, "workspace too small");
+    return (bf16*)p;
+  }
+  void* bytes(size_t n) {
+    void* p = arena.alloc(n);
+    if (!p && status == 0) status = fail(B2V_ERR_WORKSPACE, "workspace too small");
+    return p;
+  }
+  void free(void* p) { arena.release(p); }
+  void run(int st) { if (status == 0 && st != 0) status = st; }
+  bool live() const { return status == 0 && !arena.dry(); }
+};
+
+struct Act { bf16* p; int64_t rows; int C; int H, W; };  // rows = B*F*H*W
+
+void gemm(Ctx& c, const bf16* a, int64_t M, const Lin& l, const bf16* residual, bf16* out, int flags = 0,
+          int64_t lda = 0) {
+  c.flops += 2.0 * (double)M * l.N * l.K;
+  if (!c.live()) return;
+  GemmArgs g;
+  g.a = a; g.lda = lda; g.w = l.w; g.bias = l.b; g.residual = residual; g.out = out;
+  g.M = M; g.N = l.N; g.Kc = l.K; g.taps = 1; g.rows_per_batch = M; g.flags = flags;
+  c.run(gemm_tiled(g, c.s));
+}
+
+void gn(Ctx& c, const bf16* x1, int C1, const bf16* x2, int C2, const Norm& n, bf16* y, int64_t items, int64_t rows_per,
+        float eps, int silu) {
+  double* stats = (double*)c.bytes(sizeof(double) * 2 * (size_t)items * c.u->cfg.norm_num_groups);
+  if (c.live()) c.run(group_norm(x1, C1, x2, C2, n.g, n.b, y, items, rows_per, c.u->cfg.norm_num_groups, eps, silu, stats, c.s));
+  c.free(stats);
+}
+
+void conv(Ctx& c, const bf16* x, int N, int H, int W, const Conv& w, int stride, const float* rowbias,
+          int64_t rows_per_group, const bf16* residual, bf16* out) {
+  const int P = (H - 1) / stride + 1, Q = (W - 1) / stride + 1;
+  c.flops += 2.0 * (double)N * P * Q * w.Cout * 9.0 * w.Cin;
+  if (!c.live()) return;
+  ConvArgs a;
+  a.x = x; a.w = w.w; a.bias = w.b; a.rowbias = rowbias; a.rows_per_group = rows_per_group; a.residual = residual;
+  a.out = out; a.N = N; a.H = H; a.W = W; a.Cin = w.Cin; a.Cout = w.Cout; a.stride = stride;
+  c.run(conv3x3_im2col(a, c.s));
+}
+
+// ResnetBlock2D on x = concat(xa, xb) (xb may be null). Returns a new activation; does not free its inputs.
+Act resnet(Ctx& c, const ResnetW& r, const Act& xa, const bf16* xb, int Cb) {
+  const int64_t M = xa.rows;
+  const int N = c.B * c.F, H = xa.H, W = xa.W;
+  const int Cin = xa.C + Cb;
+  bf16* h1 = c.act(M, Cin);
+  gn(c, xa.p, xa.C, xb, Cb, r.n1, h1, N, (int64_t)H * W, c.u->cfg.norm_eps, 1);
+  bf16* h2 = c.act(M, r.Cout);
+  conv(c, h1, N, H, W, r.c1, 1, r.rowbias, (int64_t)c.F * H * W, nullptr, h2);
+  c.free(h1);
+  bf16* h3 = c.act(M, r.Cout);
+  gn(c, h2, r.Cout, nullptr, 0, r.n2, h3, N, (int64_t)H * W, c.u->cfg.norm_eps, 1);
+  c.free(h2);
+  const bf16* res = xa.p;
+  bf16* sc = nullptr;
+  if (r.has_sc) {
+    const bf16* xin = xa.p;
+    bf16* xcat = nullptr;
+    if (xb) {
+      xcat = c.act(M, Cin);
+      if (c.live()) c.run(concat_channels(xa.p, xa.C, xb, Cb, xcat, M, c.s));
+      xin = xcat;
+    }
+    sc = c.act(M, r.Cout);
+    gemm(c, xin, M, r.sc, nullptr, sc);
+    if (xcat) c.free(xcat);
+    res = sc;
+  }
+  bf16* out = c.act(M, r.Cout);
+  conv(c, h3, N, H, W, r.c2, 1, nullptr, 0, res, out);
+  c.free(h3);
+  if (sc) c.free(sc);
+  return Act{out, M, r.Cout, H, W};
+}
+
+// TemporalConvLayer: 4 x [GroupNorm over (b; f,h,w) -> SiLU -> Conv3d(3,1,1)] + identity
+Act temp_conv(Ctx& c, const TempConvW& t, const Act& x) {
+  const int64_t M = x.rows, HW = (int64_t)x.H * x.W;
+  const bf16* cur = x.p;
+  bf16* prev_owned = nullptr;
+  for (int i = 0; i < 4; ++i) {
+    bf16* n = c.act(M, t.C);
+    gn(c, cur, t.C, nullptr, 0, t.n[i], n, c.B, (int64_t)c.F * HW, 1e-5f, 1);
+    bf16* o = c.act(M, t.C);
+    c.flops += 2.0 * (double)M * t.C * 3.0 * t.C;
+    if (c.live()) {
+      GemmArgs g;
+      g.a = n; g.w = t.c[i].w; g.bias = t.c[i].b; g.residual = (i == 3) ? x.p : nullptr; g.out = o;
+      g.M = M; g.N = t.C; g.Kc = t.C; g.taps = 3; g.tap_row_stride = HW; g.rows_per_batch = (int64_t)c.F * HW;
+      c.run(gemm_tiled(g, c.s));
+    }
+    c.free(n);
+    if (prev_owned) c.free(prev_owned);
+    prev_owned = o;
+    cur = o;
+  }
+  return Act{prev_owned, M, t.C, x.H, x.W};
+}
+
+void feed_forward(Ctx& c, const BlockW& b, bf16* h, int64_t M) {
+  bf16* l = c.act(M, b.dim);
+  if (c.live()) c.run(layer_norm(h, b.ln3.g, b.ln3.b, l, M, b.dim, 1e-5f, c.s));
+  bf16* g = c.act(M, 4 * b.dim);
+  gemm(c, l, M, b.ff1, nullptr, g, B2V_EPI_GEGLU);
+  c.free(l);
+  gemm(c, g, M, b.ff2, h, h);  // in-place residual: each element is read then written by the same thread
+  c.free(g);
+}
+
+// Transformer2DModel (spatial self-attention + text cross-attention + GEGLU FF)
+Act spatial(Ctx& c, const SpatialW& a, const Act& x) {
+  const int64_t M = x.rows, HW = (int64_t)x.H * x.W;
+  const int C = a.C, N = c.B * c.F, heads = a.blk.heads;
+  const float scale = 1.0f / sqrtf((float)c.u->cfg.attention_head_dim);
+  bf16* n = c.act(M, C);
+  gn(c, x.p, C, nullptr, 0, a.norm, n, N, HW, 1e-6f, 0);
+  bf16* h = c.act(M, C);
+  gemm(c, n, M, a.proj_in, nullptr, h);
+  c.free(n);
+  const BlockW& b = a.blk;
+  {  // self attention
+    bf16* l = c.act(M, C);
+    if (c.live()) c.run(layer_norm(h, b.ln1.g, b.ln1.b, l, M, C, 1e-5f, c.s));
+    bf16* qkv = c.act(M, 3 * C);
+    gemm(c, l, M, b.qkv1, nullptr, qkv);
+    c.free(l);
+    bf16* o = c.act(M, C);
+    c.flops += 4.0 * (double)N * heads * (double)HW * (double)HW * 64.0;
+    if (c.live()) {
+      AttnArgs t;
+      t.q = qkv; t.k = qkv + C; t.v = qkv + 2 * C; t.out = o;
+      t.ldq = 3 * C; t.ldkv = 3 * C; t.ldo = C; t.nb = N; t.heads = heads; t.Sq = (int)HW; t.Skv = (int)HW;
+      t.kv_group = 1; t.scale = scale;
+      c.run(attention(t, c.s));
+    }
+    c.free(qkv);
+    gemm(c, o, M, b.o1, h, h);
+    c.free(o);
+  }
+  {  // cross attention against the text tokens (K/V depend only on the prompt: B*77 rows, shared by all frames)
+    const int TL = c.u->cfg.text_len;
+    bf16* l = c.act(M, C);
+    if (c.live()) c.run(layer_norm(h, b.ln2.g, b.ln2.b, l, M, C, 1e-5f, c.s));
+    bf16* q = c.act(M, C);
+    gemm(c, l, M, b.q2, nullptr, q);
+    c.free(l);
+    bf16* kv = c.act((int64_t)c.B * TL, 2 * C);
+    gemm(c, c.text, (int64_t)c.B * TL, b.kv2, nullptr, kv);
+    bf16* o = c.act(M, C);
+    c.flops += 4.0 * (double)N * heads * (double)HW * (double)TL * 64.0;
+    if (c.live()) {
+      AttnArgs t;
+      t.q = q; t.k = kv; t.v = kv + C; t.out = o;
+      t.ldq = C; t.ldkv = 2 * C; t.ldo = C; t.nb = N; t.heads = heads; t.Sq = (int)HW; t.Skv = TL;
+      t.kv_group = c.F; t.scale = scale;
+      c.run(attention(t, c.s));
+    }
+    c.free(q);
+    c.free(kv);
+    gemm(c, o, M, b.o2, h, h);
+    c.free(o);
+  }
+  feed_forward(c, b, h, M);
+  bf16* out = c.act(M, C);
+  gemm(c, h, M, a.proj_out, x.p, out);
+  c.free(h);
+  return Act{out, M, C, x.H, x.W};
+}
+
+// TransformerTemporalModel (two self-attentions over the frame axis + GEGLU FF)
+Act temporal(Ctx& c, const TemporalW& a, const Act& x) {
+  const int64_t M = x.rows, HW = (int64_t)x.H * x.W;
+  const int C = a.C, D = a.inner, heads = a.blk.heads;
+  const float scale = 1.0f / sqrtf((float)c.u->cfg.attention_head_dim);
+  bf16* n = c.act(M, C);
+  gn(c, x.p, C, nullptr, 0, a.norm, n, c.B, (int64_t)c.F * HW, 1e-6f, 0);
+  bf16* h = c.act(M, D);
+  gemm(c, n, M, a.proj_in, nullptr, h);
+  c.free(n);
+  const BlockW& b = a.blk;
+  for (int which = 0; which < 2; ++which) {
+    const Norm& ln = which == 0 ? b.ln1 : b.ln2;
+    const Lin& qkvw = which == 0 ? b.qkv1 : b.qkv2;
+    const Lin& ow = which == 0 ? b.o1 : b.o2;
+    bf16* l = c.act(M, D);
+    if (c.live()) c.run(layer_norm(h, ln.g, ln.b, l, M, D, 1e-5f, c.s));
+    bf16* qkv = c.act(M, 3 * D);
+    gemm(c, l, M, qkvw, nullptr, qkv);
+    c.free(l);
+    bf16* o = c.act(M, D);
+    c.flops += 4.0 * (double)c.B * HW * heads * (double)c.F * (double)c.F * 64.0;
+    if (c.live()) c.run(temporal_attention(qkv, 3 * D, 0, D, 2 * D, o, D, c.B, c.F, HW, heads, scale, c.s));
+    c.free(qkv);
+    gemm(c, o, M, ow, h, h);
+    c.free(o);
+  }
+  feed_forward(c, b, h, M);
+  bf16* out = c.act(M, C);
+  gemm(c, h, M, a.proj_out, x.p, out);
+  c.free(h);
+  return Act{out, M, C, x.H, x.W};
+}
+
+int forward_impl(b2v_unet3d* u, Ctx& c, const void* sample, float timestep, const void* ehs, void* out, int io_dtype,
+                 int H, int W) {
+  const b2v_unet3d_config& cfg = u->cfg;
+  const int B = c.B, F = c.F, N = B * F;
+  const int C0 = cfg.block_out_channels[0];
+
+  // text tokens -> bf16 rows; time embedding + the 22 per-resnet projections (fp32, M = B)
+  const int64_t text_n = (int64_t)B * cfg.text_len * cfg.cross_attention_dim;
+  bf16* text = (bf16*)c.bytes((size_t)text_n * 2);
+  c.text = text;
+  if (c.live()) {
+    c.run(to_bf16(ehs, io_dtype, text, text_n, c.s));
+    c.run(time_embedding(timestep, B, C0, u->te_w1, u->te_b1, u->te_w2, u->te_b2, u->temb_dim, u->temb_scratch, c.s));
+    for (ResnetW* r : u->all_resnets)
+      c.run(small_linear(u->temb_scratch, r->temb_w, r->temb_b, r->rowbias, B, r->Cout, u->temb_dim, c.s));
+  }
+
+  Act x{c.act((int64_t)N * H * W, C0), (int64_t)N * H * W, C0, H, W};
+  if (c.live()) c.run(conv_in_3x3(sample, io_dtype, u->conv_in_w, u->conv_in_b, x.p, B, cfg.in_channels, F, H, W, C0, c.s));
+  c.flops += 2.0 * (double)N * H * W * C0 * 9.0 * cfg.in_channels;
+  {
+    Act y = temporal(c, u->transformer_in, x);
+    c.free(x.p);
+    x = y;
+  }
+  std::vector<Act> skips;
+  skips.push_back(x);
+  // ---- down ----
+  for (size_t i = 0; i < u->down.size(); ++i) {
+    LevelW& L = u->down[i];
+    for (size_t j = 0; j < L.resnets.size(); ++j) {
+      Act y = resnet(c, L.resnets[j], x, nullptr, 0);
+      // x is a skip (kept) — do not free
+      Act z = temp_conv(c, L.temp_convs[j], y);
+      c.free(y.p);
+      if (!L.attns.empty()) {
+        Act a = spatial(c, L.attns[j], z);
+        c.free(z.p);
+        Act t = temporal(c, L.tattns[j], a);
+        c.free(a.p);
+        z = t;
+      }
+      x = z;
+      skips.push_back(x);
+    }
+    if (L.has_sampler) {
+      const int P = (x.H - 1) / 2 + 1, Q = (x.W - 1) / 2 + 1;
+      Act y{c.act((int64_t)N * P * Q, x.C), (int64_t)N * P * Q, x.C, P, Q};
+      conv(c, x.p, N, x.H, x.W, L.sampler, 2, nullptr, 0, nullptr, y.p);
+      x = y;
+      skips.push_back(x);
+    }
+  }
+  // ---- mid ----  (x is the last skip: keep it alive)
+  {
+    Act y = resnet(c, u->mid.resnets[0], x, nullptr, 0);
+    Act z = temp_conv(c, u->mid.temp_convs[0], y);
+    c.free(y.p);
+    Act a = spatial(c, u->mid.attns[0], z);
+    c.free(z.p);
+    Act t = temporal(c, u->mid.tattns[0], a);
+    c.free(a.p);
+    Act r = resnet(c, u->mid.resnets[1], t, nullptr, 0);
+    c.free(t.p);
+    Act q = temp_conv(c, u->mid.temp_convs[1], r);
+    c.free(r.p);
+    x = q;
+  }
+  // ---- up ----
+  for (size_t i = 0; i < u->up.size(); ++i) {
+    LevelW& L = u->up[i];
+    for (size_t j = 0; j < L.resnets.size(); ++j) {
+      Act sk = skips.back();
+      skips.pop_back();
+      Act y = resnet(c, L.resnets[j], x, sk.p, sk.C);
+      c.free(x.p);
+      c.free(sk.p);
+      Act z = temp_conv(c, L.temp_convs[j], y);
+      c.free(y.p);
+      if (!L.attns.empty()) {
+        Act a = spatial(c, L.attns[j], z);
+        c.free(z.p);
+        Act t = temporal(c, L.tattns[j], a);
+        c.free(a.p);
+        z = t;
+      }
+      x = z;
+    }
+    if (L.has_sampler) {
+      Act upx{c.act(x.rows * 4, x.C), x.rows * 4, x.C, x.H * 2, x.W * 2};
+      if (c.live()) c.run(upsample2x(x.p, upx.p, N, x.H, x.W, x.C, c.s));
+      c.free(x.p);
+      Act y{c.act(upx.rows, x.C), upx.rows, x.C, upx.H, upx.W};
+      conv(c, upx.p, N, upx.H, upx.W, L.sampler, 1, nullptr, 0, nullptr, y.p);
+      c.free(upx.p);
+      x = y;
+    }
+  }
+  // ---- out ----
+  bf16* hn = c.act(x.rows, x.C);
+  gn(c, x.p, x.C, nullptr, 0, u->norm_out, hn, N, (int64_t)x.H * x.W, cfg.norm_eps, 1);
+  c.free(x.p);
+  c.flops += 2.0 * (double)N * H * W * cfg.out_channels * 9.0 * C0;
+  if (c.live()) c.run(conv_out_3x3(hn, u->conv_out_w, u->conv_out_b, out, io_dtype, B, C0, F, H, W, cfg.out_channels, c.s));
+  c.free(hn);
+  c.free(text);
+  return c.status;
+}
+
+}  // namespace
+}  // namespace b2v
+
+// ------------------------------------------------------------------------------------------------
+// C ABI
+// ------------------------------------------------------------------------------------------------
+extern "C" int b2v_unet3d_create(const b2v_unet3d_config* cfg, b2v_unet3d** out) {
+  B2V_CHECK(cfg && out, "null argument");
+  B2V_TRY(b2v_device_check());
+  for (int i = 0; i < 4; ++i)
+    B2V_CHECK(cfg->block_out_channels[i] > 0 && cfg->block_out_channels[i] % 64 == 0,
+              "block_out_channels[%d]=%d must be a positive multiple of 64", i, cfg->block_out_channels[i]);
+  B2V_CHECK(cfg->attention_head_dim == 64, "attention_head_dim must be 64");
+  B2V_CHECK(cfg->cross_attention_dim % 64 == 0 && cfg->norm_num_groups > 0 && cfg->layers_per_block >= 1,
+            "bad config");
+  B2V_CHECK(cfg->out_channels <= 4 && cfg->in_channels >= 1, "in/out channels unsupported");
+  auto* u = new b2v_unet3d();
+  u->cfg = *cfg;
+  cudaGetDevice(&u->device);
+  u->temb_dim = cfg->block_out_channels[0] * 4;
+  *out = u;
+  return 0;
+}
+
+extern "C" void b2v_unet3d_destroy(b2v_unet3d* u) {
+  if (!u) return;
+  for (auto& kv : u->raw) cudaFree(kv.second.first);
+  for (void* p : u->owned) cudaFree(p);
+  delete u;
+}
+
+extern "C" int b2v_unet3d_load_tensor(b2v_unet3d* u, const char* name, const void* data, int dtype, int ndim,
+                                      const int64_t* shape) {
+  B2V_CHECK(u && name && data && shape && ndim >= 1 && ndim <= 5, "bad argument");
+  if (u->finalized) return fail(B2V_ERR_STATE, "load_tensor after finalize");
+  const size_t es = dtype_size(dtype);
+  B2V_CHECK(es != 0, "bad dtype");
+  int64_t n = 1;
+  std::vector<int64_t> shp;
+  for (int i = 0; i < ndim; ++i) { n *= shape[i]; shp.push_back(shape[i]); }
+  B2V_CHECK(n > 0, "empty tensor");
+  float* dst = nullptr;
+  B2V_CUDA_OK(cudaMalloc((void**)&dst, sizeof(float) * (size_t)n));
+  void* stage = nullptr;
+  cudaPointerAttributes attr;
+  const bool on_dev = cudaPointerGetAttributes(&attr, data) == cudaSuccess &&
+                      (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged);
+  cudaGetLastError();
+  const void* src = data;
+  if (!on_dev) {
+    B2V_CUDA_OK(cudaMalloc(&stage, es * (size_t)n));
+    B2V_CUDA_OK(cudaMemcpy(stage, data, es * (size_t)n, cudaMemcpyHostToDevice));
+    src = stage;
+  }
+  B2V_DISPATCH_DTYPE(dtype, T, (cast_to_f32_kernel<T><<<ew_grid(n), 256>>>((const T*)src, dst, n)));
+  count_launch();
+  B2V_CUDA_OK(cudaDeviceSynchronize());
+  if (stage) cudaFree(stage);
+  auto it = u->raw.find(name);
+  if (it != u->raw.end()) { cudaFree(it->second.first); u->param_count -= 0; }
+  else u->param_count += n;
+  u->raw[name] = {dst, shp};
+  return 0;
+}
+
+extern "C" int64_t b2v_unet3d_param_count(const b2v_unet3d* u) { return u ? u->param_count : 0; }
+
+extern "C" int b2v_unet3d_finalize(b2v_unet3d* u) {
+  B2V_CHECK(u, "null handle");
+  if (u->finalized) return 0;
+  const b2v_unet3d_config& cfg = u->cfg;
+  Loader L{u};
+  const int* ch = cfg.block_out_channels;
+  const int hd = cfg.attention_head_dim;
+  // stem
+  {
+    const float* w = L.get("conv_in.weight", {ch[0], cfg.in_channels, 3, 3});
+    u->conv_in_w = L.dalloc<float>((size_t)ch[0] * cfg.in_channels * 9);
+    if (w) cudaMemcpy(u->conv_in_w, w, sizeof(float) * (size_t)ch[0] * cfg.in_channels * 9, cudaMemcpyDeviceToDevice);
+    u->conv_in_b = L.vec("conv_in.bias", ch[0]);
+    auto mat = [&](const char* nm, int N, int K) {
+      const float* s = L.get(nm, {N, K});
+      float* d = L.dalloc<float>((size_t)N * K);
+      if (s && d) cudaMemcpy(d, s, sizeof(float) * (size_t)N * K, cudaMemcpyDeviceToDevice);
+      return d;
+    };
+    u->te_w1 = mat("time_embedding.linear_1.weight", u->temb_dim, ch[0]);
+    u->te_b1 = L.vec("time_embedding.linear_1.bias", u->temb_dim);
+    u->te_w2 = mat("time_embedding.linear_2.weight", u->temb_dim, u->temb_dim);
+    u->te_b2 = L.vec("time_embedding.linear_2.bias", u->temb_dim);
+    u->temb_scratch = L.dalloc<float>((size_t)b2v_unet3d::kMaxB * (2 * u->temb_dim + ch[0]));
+    u->transformer_in = L.temporal("transformer_in", ch[0], cfg.transformer_in_heads);
+  }
+  // down: CrossAttnDownBlock3D x3 + DownBlock3D
+  u->down.resize(4);
+  int prev = ch[0];
+  for (int i = 0; i < 4; ++i) {
+    LevelW& lv = u->down[i];
+    const bool attn = i < 3;
+    const std::string p = "down_blocks." + std::to_string(i);
+    for (int j = 0; j < cfg.layers_per_block; ++j) {
+      const std::string js = std::to_string(j);
+      lv.resnets.push_back(L.resnet(p + ".resnets." + js, j == 0 ? prev : ch[i], ch[i]));
+      lv.temp_convs.push_back(L.temp_conv(p + ".temp_convs." + js, ch[i]));
+      if (attn) {
+        lv.attns.push_back(L.spatial(p + ".attentions." + js, ch[i]));
+        lv.tattns.push_back(L.temporal(p + ".temp_attentions." + js, ch[i], ch[i] / hd));
+      }
+    }
+    lv.has_sampler = i < 3;
+    if (lv.has_sampler) lv.sampler = L.conv3x3(p + ".downsamplers.0.conv", ch[i], ch[i]);
+    prev = ch[i];
+  }
+  // mid: UNetMidBlock3DCrossAttn
+  {
+    LevelW& lv = u->mid;
+    for (int j = 0; j < 2; ++j) {
+      lv.resnets.push_back(L.resnet("mid_block.resnets." + std::to_string(j), ch[3], ch[3]));
+      lv.temp_convs.push_back(L.temp_conv("mid_block.temp_convs." + std::to_string(j), ch[3]));
+    }
+    lv.attns.push_back(L.spatial("mid_block.attentions.0", ch[3]));
+    lv.tattns.push_back(L.temporal("mid_block.temp_attentions.0", ch[3], ch[3] / hd));
+  }
+  // up: UpBlock3D + CrossAttnUpBlock3D x3
+  u->up.resize(4);
+  int rev[4] = {ch[3], ch[2], ch[1], ch[0]};
+  int prev_out = rev[0];
+  for (int i = 0; i < 4; ++i) {
+    LevelW& lv = u->up[i];
+    const bool attn = i > 0;
+    const int outc = rev[i], inc = rev[i + 1 < 4 ? i + 1 : 3];
+    const std::string p = "up_blocks." + std::to_string(i);
+    const int nl = cfg.layers_per_block + 1;
+    for (int j = 0; j < nl; ++j) {
+      const std::string js = std::to_string(j);
+      const int skip = (j == nl - 1) ? inc : outc;
+      const int rin = (j == 0) ? prev_out : outc;
+      lv.resnets.push_back(L.resnet(p + ".resnets." + js, rin + skip, outc));
+      lv.temp_convs.push_back(L.temp_conv(p + ".temp_convs." + js, outc));
+      if (attn) {
+        lv.attns.push_back(L.spatial(p + ".attentions." + js, outc));
+        lv.tattns.push_back(L.temporal(p + ".temp_attentions." + js, outc, outc / hd));
+      }
+    }
+    lv.has_sampler = i < 3;
+    if (lv.has_sampler) lv.sampler = L.conv3x3(p + ".upsamplers.0.conv", outc, outc);
+    prev_out = outc;
+  }
+  // head
+  u->norm_out = L.norm("conv_norm_out", ch[0]);
+  {
+    const float* w = L.get("conv_out.weight", {cfg.out_channels, ch[0], 3, 3});
+    u->conv_out_w = L.dalloc<float>((size_t)cfg.out_channels * ch[0] * 9);
+    if (w && u->conv_out_w)
+      permute_taps_kernel<float><<<ew_grid((int64_t)cfg.out_channels * ch[0] * 9), 256>>>(w, u->conv_out_w, cfg.out_channels, ch[0], 9);
+    u->conv_out_b = L.vec("conv_out.bias", cfg.out_channels);
+  }
+  cudaError_t e = cudaDeviceSynchronize();
+  if (!L.err.empty()) return fail(B2V_ERR_STATE, "%s", L.err.c_str());
+  if (e != cudaSuccess) return fail(B2V_ERR_CUDA, "finalize: %s", cudaGetErrorString(e));
+  for (auto& kv : u->raw) cudaFree(kv.second.first);
+  u->raw.clear();
+  u->all_resnets.clear();
+  for (auto* blocks : {&u->down, &u->up})
+    for (auto& lv : *blocks)
+      for (auto& r : lv.resnets) u->all_resnets.push_back(&r);
+  for (auto& r : u->mid.resnets) u->all_resnets.push_back(&r);
+  u->finalized = true;
+  return 0;
+}
+
+static int check_shape(const b2v_unet3d* u, int B, int F, int H, int W) {
+  B2V_CHECK(u && u->finalized, "unet handle not finalised");
+  B2V_CHECK(B >= 1 && B <= b2v_unet3d::kMaxB, "batch %d outside [1,%d]", B, b2v_unet3d::kMaxB);
+  B2V_CHECK(F >= 1 && F <= 32, "frames per chunk %d outside [1,32]", F);
+  B2V_CHECK(H >= 8 && W >= 8 && H % 8 == 0 && W % 8 == 0, "latent %dx%d must be multiples of 8 (three 2x downsamples)", H, W);
+  return 0;
+}
+
+extern "C" size_t b2v_unet3d_workspace_bytes(const b2v_unet3d* u, int B, int F, int H, int W) {
+  if (check_shape(u, B, F, H, W) != 0) return 0;
+  Ctx c;
+  c.u = const_cast<b2v_unet3d*>(u);
+  c.s = 0; c.B = B; c.F = F;
+  c.arena.reset(nullptr, 0, true);
+  forward_impl(c.u, c, nullptr, 0.f, nullptr, nullptr, B2V_F32, H, W);
+  return c.arena.peak() + 4096;
+}
+
+extern "C" double b2v_unet3d_flops(const b2v_unet3d* u, int B, int F, int H, int W) {
+  if (check_shape(u, B, F, H, W) != 0) return 0.0;
+  Ctx c;
+  c.u = const_cast<b2v_unet3d*>(u);
+  c.s = 0; c.B = B; c.F = F;
+  c.arena.reset(nullptr, 0, true);
+  forward_impl(c.u, c, nullptr, 0.f, nullptr, nullptr, B2V_F32, H, W);
+  return c.flops;
+}
+
+extern "C" int b2v_unet3d_forward(b2v_unet3d* u, const void* sample_dev, float timestep, const void* ehs_dev,
+                                  void* out_dev, int io_dtype, int B, int F, int H, int W, void* workspace_dev,
+                                  size_t workspace_bytes, void* stream) {
+  B2V_TRY(check_shape(u, B, F, H, W));
+  B2V_CHECK(sample_dev && ehs_dev && out_dev && workspace_dev, "null argument");
+  B2V_CHECK(dtype_size(io_dtype) != 0, "bad io dtype");
+  B2V_CHECK(((uintptr_t)workspace_dev & 1023) == 0, "workspace must be 1 KiB aligned");
+  Ctx c;
+  c.u = u;
+  c.s = (cudaStream_t)stream; c.B = B; c.F = F;
+  c.arena.reset((uint8_t*)workspace_dev, workspace_bytes, false);
+  return forward_impl(u, c, sample_dev, timestep, ehs_dev, out_dev, io_dtype, H, W);
+}

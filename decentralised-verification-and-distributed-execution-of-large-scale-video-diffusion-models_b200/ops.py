@@ -1,0 +1,245 @@
+"""torch.Tensor -> libb2v plumbing: pointers, dtype tags, current stream. torch supplies device memory and streams
+only; every computation below happens in the CUDA kernels of csrc/."""
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import BF16, F16, F32, check
+
+_DT = {torch.float32: F32, torch.float16: F16, torch.bfloat16: BF16}
+
+
+def dtype_tag(t):
+    try:
+        return _DT[t.dtype]
+    except KeyError:
+        raise TypeError("libb2v supports float32/float16/bfloat16 tensors, got %s" % t.dtype)
+
+
+def _cuda(t, name="tensor"):
+    if not isinstance(t, torch.Tensor) or not t.is_cuda:
+        raise _lib.B2VError("%s must be a CUDA tensor (libb2v has no CPU path)" % name)
+    if not t.is_contiguous():
+        raise ValueError("%s must be contiguous" % name)
+    return t
+
+
+def ptr(t):
+    return C.c_void_p(t.data_ptr()) if t is not None else C.c_void_p(0)
+
+
+def stream():
+    return C.c_void_p(torch.cuda.current_stream().cuda_stream)
+
+
+def launch_count():
+    return int(_lib.load().b2v_launch_count())
+
+
+# ---- step glue -------------------------------------------------------------------------------------------------
+def cfg_ddim_step(lat, eps2, a_t, a_prev, guidance_scale=None, ctx=None, ctx_w=0.0, clip_sample=False,
+                  make_next_input=0, leaf_z=None, leaf_eps=None, out=None, xnext=None):
+    """lat [1,C,F,h,w]; eps2 [2,C,F,h,w] (uncond, cond) when guidance_scale is not None else [1,C,F,h,w].
+    Returns (lat', x_next or None)."""
+    lib = _lib.load()
+    _cuda(lat, "lat"); _cuda(eps2, "eps2")
+    _, Cc, F, h, w = lat.shape
+    cfg = guidance_scale is not None
+    if eps2.shape[0] != (2 if cfg else 1) or eps2.dtype != lat.dtype:
+        raise ValueError("eps2 batch/dtype mismatch")
+    if out is None:
+        out = torch.empty_like(lat)
+    if make_next_input and xnext is None:
+        xnext = torch.empty((make_next_input,) + tuple(lat.shape[1:]), dtype=lat.dtype, device=lat.device)
+    check(lib.b2v_cfg_ddim_step(ptr(lat), ptr(eps2), ptr(ctx), float(ctx_w), int(cfg),
+                                float(guidance_scale or 0.0), float(a_t), float(a_prev), int(bool(clip_sample)),
+                                ptr(out), ptr(xnext), int(make_next_input), ptr(leaf_z), ptr(leaf_eps),
+                                dtype_tag(lat), Cc, F, h * w, stream()))
+    return out, xnext
+
+
+def make_unet_input(lat, n_dup, ctx=None, ctx_w=0.0):
+    lib = _lib.load()
+    _cuda(lat, "lat")
+    _, Cc, F, h, w = lat.shape
+    x = torch.empty((n_dup,) + tuple(lat.shape[1:]), dtype=lat.dtype, device=lat.device)
+    check(lib.b2v_make_unet_input(ptr(lat), ptr(ctx), float(ctx_w), ptr(x), n_dup, dtype_tag(lat), Cc, F, h * w, stream()))
+    return x
+
+
+def context_mean(base):
+    lib = _lib.load()
+    _cuda(base, "base")
+    _, Cc, T, h, w = base.shape
+    ctx = torch.empty((1, Cc, 1, h, w), dtype=base.dtype, device=base.device)
+    check(lib.b2v_context_mean(ptr(base), ptr(ctx), dtype_tag(base), Cc, T, h * w, stream()))
+    return ctx
+
+
+def blend_overlap(chunks, ranges, weights, T, return_full=False):
+    """chunks[i]: CUDA [1,C,len_i,h,w]; ranges[i] = (s,e); weights[i]: python/torch fp32 per-frame weights.
+    Returns fp32 [1,C,T,h,w] (and the accumulator in the chunks' dtype when return_full)."""
+    import numpy as np
+    lib = _lib.load()
+    n = len(chunks)
+    if n == 0:
+        raise ValueError("no chunks")
+    for c in chunks:
+        _cuda(c, "chunk")
+    _, Cc, _, h, w = chunks[0].shape
+    dev, dt = chunks[0].device, chunks[0].dtype
+    ptrs = (C.c_void_p * n)(*[c.data_ptr() for c in chunks])
+    starts = (C.c_int * n)(*[int(s) for s, _ in ranges])
+    ends = (C.c_int * n)(*[int(e) for _, e in ranges])
+    wflat = np.concatenate([np.asarray(wi, dtype=np.float32).reshape(-1) for wi in weights]).astype(np.float32)
+    for (s, e), c in zip(ranges, chunks):
+        if c.shape[2] != e - s or c.dtype != dt:
+            raise ValueError("chunk shape/dtype does not match its range")
+    out = torch.empty((1, Cc, T, h, w), dtype=torch.float32, device=dev)
+    full = torch.empty((1, Cc, T, h, w), dtype=dt, device=dev) if return_full else None
+    check(lib.b2v_blend_overlap(ptrs, starts, ends, n, wflat.ctypes.data_as(C.c_void_p), Cc, T, h * w, _DT[dt],
+                                ptr(out), ptr(full), stream()))
+    return (out, full) if return_full else out
+
+
+# ---- proof -----------------------------------------------------------------------------------------------------
+def sha256_leaves(a_list, b_list=None, prefixes=None, mode=0):
+    """digest[i] = SHA256(prefix_i(2B BE, optional) ‖ bytes(a_i) ‖ bytes(b_i)); tensors are hashed in place on the
+    device as raw bytes. Returns a CUDA uint8 tensor [n,32]."""
+    lib = _lib.load()
+    n = len(a_list)
+    dev = a_list[0].device if n else torch.device("cuda")
+    dig = torch.empty((n, 32), dtype=torch.uint8, device=dev)
+    if n == 0:
+        return dig
+    for t in a_list:
+        _cuda(t, "leaf buffer")
+    ap = (C.c_void_p * n)(*[t.data_ptr() for t in a_list])
+    al = (C.c_uint64 * n)(*[t.numel() * t.element_size() for t in a_list])
+    bp = bl = None
+    if b_list is not None:
+        for t in b_list:
+            _cuda(t, "leaf buffer")
+        bp = (C.c_void_p * n)(*[t.data_ptr() for t in b_list])
+        bl = (C.c_uint64 * n)(*[t.numel() * t.element_size() for t in b_list])
+    pf = None
+    if prefixes is not None:
+        for p in prefixes:
+            if not 0 <= int(p) < 65536:
+                raise OverflowError("int too big to convert")  # same failure as int.to_bytes(2,'big') (miner.py:207)
+        pf = (C.c_uint16 * n)(*[int(p) for p in prefixes])
+    check(lib.b2v_sha256_leaves(pf, ap, al, bp, bl, n, ptr(dig), int(mode), stream()))
+    return dig
+
+
+def merkle_build(leaf_hashes, want_paths=True):
+    """leaf_hashes: CUDA uint8 [n,32] -> (root uint8[32], paths uint8[n,depth,32] or None)."""
+    lib = _lib.load()
+    _cuda(leaf_hashes, "leaf_hashes")
+    n = leaf_hashes.shape[0]
+    depth = lib.b2v_merkle_depth(n)
+    dev = leaf_hashes.device
+    root = torch.empty(32, dtype=torch.uint8, device=dev)
+    paths = torch.empty((n, depth, 32), dtype=torch.uint8, device=dev) if want_paths else None
+    scratch = torch.empty(lib.b2v_merkle_scratch_bytes(n), dtype=torch.uint8, device=dev)
+    check(lib.b2v_merkle_build(ptr(leaf_hashes), n, ptr(root), ptr(paths) if depth > 0 else C.c_void_p(0),
+                               ptr(scratch), stream()))
+    return root, paths
+
+
+def merkle_verify(leaf_hashes, paths, root):
+    lib = _lib.load()
+    _cuda(leaf_hashes); _cuda(paths); _cuda(root)
+    m, depth = paths.shape[0], paths.shape[1]
+    ok = torch.empty(m, dtype=torch.uint8, device=leaf_hashes.device)
+    check(lib.b2v_merkle_verify(ptr(leaf_hashes), ptr(paths), m, depth, ptr(root), ptr(ok), stream()))
+    return ok
+
+
+def spotcheck_ddim(z_list, eps_list, znext_list, a_t, a_prev, C_, F, hw):
+    import numpy as np
+    lib = _lib.load()
+    m = len(z_list)
+    dev = z_list[0].device
+    zp = (C.c_void_p * m)(*[t.data_ptr() for t in z_list])
+    ep = (C.c_void_p * m)(*[t.data_ptr() for t in eps_list])
+    np_ = (C.c_void_p * m)(*[t.data_ptr() for t in znext_list]) if znext_list is not None else None
+    at = np.asarray(a_t, dtype=np.float32)
+    ap = np.asarray(a_prev, dtype=np.float32)
+    flags = torch.empty(m, dtype=torch.uint8, device=dev)
+    check(lib.b2v_spotcheck_ddim(zp, ep, np_, at.ctypes.data_as(C.c_void_p), ap.ctypes.data_as(C.c_void_p), m,
+                                 int(C_), int(F), int(hw), ptr(flags), stream()))
+    return flags
+
+
+# ---- building-block ops (tests) --------------------------------------------------------------------------------
+def gemm(a, w, bias=None, rowbias=None, rows_per_group=0, residual=None, taps=1, tap_row_stride=0, rows_per_batch=0,
+         flags=0):
+    lib = _lib.load()
+    _cuda(a); _cuda(w)
+    M, Kc = a.shape
+    N = w.shape[0]
+    assert w.shape[1] == taps * Kc
+    n_out = N // 2 if flags & _lib.EPI_GEGLU else N
+    out = torch.empty((M, n_out), dtype=torch.bfloat16, device=a.device)
+    check(lib.b2v_op_gemm(ptr(a), ptr(w), ptr(bias), ptr(rowbias), int(rows_per_group), ptr(residual), ptr(out), M, N,
+                          Kc, taps, int(tap_row_stride), int(rows_per_batch), int(flags), stream()))
+    return out
+
+
+def conv3x3(x, w, bias=None, rowbias=None, rows_per_group=0, residual=None, stride=1, mode=0):
+    """x: [N,H,W,Cin] bf16; w: [Cout,3,3,Cin] bf16 -> [N,P,Q,Cout]."""
+    lib = _lib.load()
+    _cuda(x); _cuda(w)
+    N, H, W, Cin = x.shape
+    Cout = w.shape[0]
+    P, Q = (H - 1) // stride + 1, (W - 1) // stride + 1
+    out = torch.empty((N, P, Q, Cout), dtype=torch.bfloat16, device=x.device)
+    sb = lib.b2v_op_conv3x3_scratch_bytes(N, H, W, Cin, stride, mode)
+    scratch = torch.empty(max(sb, 1), dtype=torch.uint8, device=x.device)
+    check(lib.b2v_op_conv3x3(ptr(x), ptr(w), ptr(bias), ptr(rowbias), int(rows_per_group), ptr(residual), ptr(out), N,
+                             H, W, Cin, Cout, stride, mode, ptr(scratch), stream()))
+    return out
+
+
+def group_norm(x, gamma, beta, n_items, groups, eps, silu, x2=None):
+    lib = _lib.load()
+    _cuda(x)
+    rows, C1 = x.shape
+    C2 = x2.shape[1] if x2 is not None else 0
+    y = torch.empty((rows, C1 + C2), dtype=torch.bfloat16, device=x.device)
+    stats = torch.empty(n_items * groups * 2, dtype=torch.float64, device=x.device)
+    check(lib.b2v_op_group_norm(ptr(x), C1, ptr(x2), C2, ptr(gamma), ptr(beta), ptr(y), n_items, rows // n_items,
+                                groups, float(eps), int(silu), ptr(stats), stream()))
+    return y
+
+
+def layer_norm(x, gamma, beta, eps=1e-5):
+    lib = _lib.load()
+    _cuda(x)
+    rows, Cc = x.shape
+    y = torch.empty_like(x)
+    check(lib.b2v_op_layer_norm(ptr(x), ptr(gamma), ptr(beta), ptr(y), rows, Cc, float(eps), stream()))
+    return y
+
+
+def attention(q, k, v, heads, kv_group=1, scale=0.125):
+    """q: [nb,Sq,heads*64] (may be a column slice view base: pass contiguous tensors), k/v: [nb/kv_group,Skv,heads*64]."""
+    lib = _lib.load()
+    nb, Sq, D = q.shape
+    Skv = k.shape[1]
+    out = torch.empty((nb, Sq, D), dtype=torch.bfloat16, device=q.device)
+    check(lib.b2v_op_attention(ptr(q), q.stride(1), ptr(k), ptr(v), k.stride(1), ptr(out), D, nb, heads, Sq, Skv,
+                               kv_group, float(scale), stream()))
+    return out
+
+
+def temporal_attention(qkv, B, F, HW, heads, scale=0.125):
+    """qkv: [B*F*HW, 3*heads*64] fused rows in (b,f,p) order -> [B*F*HW, heads*64]."""
+    lib = _lib.load()
+    D = heads * 64
+    out = torch.empty((qkv.shape[0], D), dtype=torch.bfloat16, device=qkv.device)
+    check(lib.b2v_op_temporal_attention(ptr(qkv), qkv.shape[1], 0, D, 2 * D, ptr(out), D, B, F, HW, heads,
+                                        float(scale), stream()))
+    return out

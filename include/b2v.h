@@ -1,0 +1,218 @@
+/*
+ * b2v.h — C-ABI of libb2v.so, the B200 (sm_100a) implementation of one hot path of
+ * noorgme/Decentralised-Verification-and-Distributed-Execution-of-Large-Scale-Video-Diffusion-Models:
+ * the chunked-coherent Zeroscope (UNet3D) denoising loop of Distribution/strategies and the
+ * Proof-of-Inference Merkle commit / verify of InferNet/template/validator/proof.py.
+ *
+ * The reference has no FFI (it is pure Python on torch/diffusers/hashlib); each entry point below cites
+ * the reference call site (file:line, relative to the reference root) whose work it replaces.
+ * INTEGRATION.md shows the ctypes binding a reference maintainer would add.
+ *
+ * Conventions
+ *   - every function returns 0 on success or a negative B2V_ERR_* code; b2v_last_error() gives the
+ *     thread-local message. Nothing here falls back to the CPU: without an sm_100 device the calls fail.
+ *   - pointers named *_dev are device pointers on the current CUDA device, *_host are host pointers.
+ *   - `stream` is a cudaStream_t passed as void* (NULL = default stream). Launches are asynchronous.
+ *   - no hidden device allocation in the per-step calls: the caller passes workspaces.
+ *   - tensors use the reference's layouts at the boundary: latents are contiguous NCFHW [B,4,F,h,w]
+ *     (chunk_only.py:110-113), text embeddings [B,77,1024] (chunk_only.py:62), leaf bytes are the
+ *     C-order little-endian fp16 image of the latent (neurons/miner.py:203-204).
+ */
+#ifndef B2V_H_
+#define B2V_H_
+
+#include <stddef.h>
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define B2V_VERSION 1
+
+/* status codes */
+#define B2V_OK 0
+#define B2V_ERR_ARG (-1)     /* bad argument / unsupported shape */
+#define B2V_ERR_CUDA (-2)    /* CUDA runtime / driver error */
+#define B2V_ERR_DEVICE (-3)  /* no sm_100 device: there is no CPU fallback */
+#define B2V_ERR_STATE (-4)   /* handle not finalised, missing weight ... */
+#define B2V_ERR_WORKSPACE (-5)
+
+/* dtype tags */
+#define B2V_F32 0
+#define B2V_F16 1
+#define B2V_BF16 2
+
+int b2v_version(void);
+const char* b2v_last_error(void);
+/* 0 when the current device is compute capability 10.x, B2V_ERR_DEVICE otherwise. */
+int b2v_device_check(void);
+/* number of kernels launched by this library in this process so far (bench.py: gpu_launches). */
+uint64_t b2v_launch_count(void);
+
+/* ------------------------------------------------------------------------------------------------
+ * Proof-of-Inference commitment  (InferNet/neurons/miner.py:180-264, template/validator/proof.py:250-304)
+ * ------------------------------------------------------------------------------------------------ */
+
+/* Leaf hashing. digest[i] = SHA256( prefix_i ‖ A_i ‖ B_i ) where prefix_i is the 2-byte big-endian
+ * timestep (miner.py:207 `t.to_bytes(2,'big') + z_bytes + eps_bytes`) when prefix_be16_host != NULL, or
+ * empty (proof.py:256 `hashlib.sha256(leaf)` on a raw leaf). A_i / B_i are device buffers (B may be
+ * NULL / 0 bytes). One independent Merkle–Damgård chain per leaf; mode 0 = auto, 1 = one CTA per chain
+ * (few long leaves), 2 = one lane per chain (thousands of leaves).
+ * a_ptrs_host/b_ptrs_host: host arrays of n device pointers; lens in bytes; digests_dev: [n][32]. */
+int b2v_sha256_leaves(const uint16_t* prefix_be16_host, const void* const* a_ptrs_host,
+                      const uint64_t* a_lens_host, const void* const* b_ptrs_host,
+                      const uint64_t* b_lens_host, int n, uint8_t* digests_dev, int mode, void* stream);
+
+/* Tree levels + sibling paths (miner.py:216-249 == proof.py:260-286): parent = SHA256(min(l,r)‖max(l,r))
+ * with byte-wise comparison, an odd tail node is paired with itself, the sibling of a missing node is
+ * the node itself. depth = b2v_merkle_depth(n) = number of levels below the root (0 for n==1).
+ * leaf_hashes_dev [n][32] -> root_dev [32], paths_dev [n][depth][32] (may be NULL).
+ * scratch_dev: at least b2v_merkle_scratch_bytes(n) bytes. */
+int b2v_merkle_depth(int n);
+size_t b2v_merkle_scratch_bytes(int n);
+int b2v_merkle_build(const uint8_t* leaf_hashes_dev, int n, uint8_t* root_dev, uint8_t* paths_dev,
+                     void* scratch_dev, void* stream);
+
+/* Batched leaf verification (proof.py:291-304 verify_merkle_leaf): for each of m leaves fold
+ * cur = SHA256(min(cur,sib)‖max(cur,sib)) over `depth` siblings and compare with root.
+ * ok_dev[i] = 1/0. */
+int b2v_merkle_verify(const uint8_t* leaf_hashes_dev, const uint8_t* paths_dev, int m, int depth,
+                      const uint8_t* root_dev, uint8_t* ok_dev, void* stream);
+
+/* Spot-check DDIM re-check on device (proof.py:307-392 run_unet_step and proof.py:419-626
+ * verify_temporal_coherence_spot_check, default-config DDIMScheduler branch, Appendix C of SURVEY.md).
+ * For each of m leaf pairs: z_i/eps_i/z_j are fp16 [1,C,F,h,w] device buffers of which only frame 0 is
+ * examined (proof.py:330-338); prev = sqrt(a_prev)*clamp((z-sqrt(1-a_t)*eps)/sqrt(a_t),-1,1)
+ * + sqrt(1-a_prev)*eps evaluated with the reference's per-op fp16 rounding.
+ * flags_dev[i] bit0 = all finite, bit1 = max|prev| < 10 (run_unet_step verdict = bit0&bit1),
+ * bit2 = allclose(prev, z_j, rtol=1, atol=1) (temporal-coherence verdict; z_j may be NULL -> bit2=1). */
+int b2v_spotcheck_ddim(const void* const* z_ptrs_host, const void* const* eps_ptrs_host,
+                       const void* const* znext_ptrs_host, const float* a_t_host,
+                       const float* a_prev_host, int m, int C, int F, int64_t hw, uint8_t* flags_dev,
+                       void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * Denoising step glue  (Distribution/strategies/chunk_only.py:65-74, fsdp_chunked_coherent.py:129-143)
+ * ------------------------------------------------------------------------------------------------ */
+
+/* Fused classifier-free-guidance combine + DDIM(eta=0) update + next UNet input.
+ *   eps   = cfg ? u + gs*(c-u) : eps2[0]          (chunk_only.py:72-73; miner.py:581-586 has no CFG)
+ *   x0    = (lat - sqrt(1-a_t)*eps)/sqrt(a_t) ; clip to [-1,1] when clip_sample
+ *   lat'  = sqrt(a_prev)*x0 + sqrt(1-a_prev)*eps  (diffusers DDIMScheduler.step, eta=0)
+ *   x'    = [lat' (+ ctx_w*ctx broadcast over frames)] duplicated n_dup times   (chunk_only.py:68,
+ *           fsdp_chunked_coherent.py:134-137) — the next step's UNet input, may be NULL
+ *   leaf_z_f16 / leaf_eps_f16 (may be NULL): fp16 images of lat (the step's input) and eps, i.e. the
+ *           bytes miner.py:203-204 hashes.
+ * lat/lat_out: [1,C,F,h,w]; eps2: [2 or 1,C,F,h,w]; ctx: [1,C,1,h,w] or NULL; all of dtype `dtype`.
+ * Math is fp32 with one rounding at the store. */
+int b2v_cfg_ddim_step(const void* lat_dev, const void* eps2_dev, const void* ctx_dev, float ctx_w,
+                      int cfg, float guidance_scale, float a_t, float a_prev, int clip_sample,
+                      void* lat_out_dev, void* unet_in_next_dev, int n_dup, void* leaf_z_f16_dev,
+                      void* leaf_eps_f16_dev, int dtype, int C, int F, int64_t hw, void* stream);
+
+/* First UNet input of a chunk: x = dup(lat (+ ctx_w*ctx)) (fsdp_chunked_coherent.py:133-137). */
+int b2v_make_unet_input(const void* lat_dev, const void* ctx_dev, float ctx_w, void* unet_in_dev,
+                        int n_dup, int dtype, int C, int F, int64_t hw, void* stream);
+
+/* Global context = mean over frames of the base noise (fsdp_chunked_coherent.py:112-118).
+ * base [1,C,T,h,w] -> ctx [1,C,1,h,w], fp32 accumulate, one rounding. */
+int b2v_context_mean(const void* base_dev, void* ctx_dev, int dtype, int C, int T, int64_t hw, void* stream);
+
+/* Overlap blend (chunk_only.py:136-150), reproduced exactly: `full` is an accumulator of the latents'
+ * own dtype that is rounded after every chunk's `+= latc*w` in gather order, weight is fp32, the result
+ * is full/clamp(weight,1e-6) in fp32. chunk_ptrs_host[i] -> device (or peer-mapped) [1,C,len_i,h,w];
+ * w_host: concatenated per-chunk per-frame fp32 weights (sum len_i entries, built by the host from
+ * torch.linspace like the reference). Outputs: lat_out_f32_dev [1,C,T,h,w] fp32 and, optionally,
+ * full_out_dev (dtype) for inspection. */
+int b2v_blend_overlap(const void* const* chunk_ptrs_host, const int* starts_host, const int* ends_host,
+                      int n_chunks, const float* w_host, int C, int T, int64_t hw, int dtype,
+                      float* lat_out_f32_dev, void* full_out_dev, void* stream);
+
+/* ------------------------------------------------------------------------------------------------
+ * UNet3DConditionModel forward  ([UPSTREAM diffusers] pipe.unet(x, t, encoder_hidden_states=emb).sample,
+ * chunk_only.py:71, fsdp_chunked_coherent.py:140, miner.py:581)
+ * ------------------------------------------------------------------------------------------------ */
+
+typedef struct b2v_unet3d_config {
+  int in_channels;            /* 4 */
+  int out_channels;           /* 4 */
+  int block_out_channels[4];  /* 320,640,1280,1280 */
+  int layers_per_block;       /* 2 */
+  int cross_attention_dim;    /* 1024 */
+  int attention_head_dim;     /* 64 (heads = C/64) */
+  int norm_num_groups;        /* 32 */
+  float norm_eps;             /* 1e-5 */
+  int transformer_in_heads;   /* 8 */
+  int text_len;               /* 77 */
+} b2v_unet3d_config;
+
+typedef struct b2v_unet3d b2v_unet3d;
+
+int b2v_unet3d_create(const b2v_unet3d_config* cfg, b2v_unet3d** out);
+void b2v_unet3d_destroy(b2v_unet3d* h);
+/* Feed one tensor of the diffusers state_dict (name as in the checkpoint, e.g.
+ * "down_blocks.0.resnets.0.conv1.weight"); data may be host or device memory of dtype `dtype`.
+ * The library repacks it for its kernels (bf16 GEMM operands, fp32 biases / norm affine). */
+int b2v_unet3d_load_tensor(b2v_unet3d* h, const char* name, const void* data, int dtype, int ndim,
+                           const int64_t* shape);
+/* Verify that every parameter was supplied and freeze the weight set. */
+int b2v_unet3d_finalize(b2v_unet3d* h);
+/* number of parameters loaded (sanity anchor: 1 411 2xx xxx for Zeroscope). */
+int64_t b2v_unet3d_param_count(const b2v_unet3d* h);
+size_t b2v_unet3d_workspace_bytes(const b2v_unet3d* h, int B, int F, int H, int W);
+/* sample/out: [B,Cin,F,H,W] NCFHW of `io_dtype`; ehs: [B,text_len,cross_attention_dim] of `io_dtype`
+ * (replicated over frames internally, never materialised). */
+int b2v_unet3d_forward(b2v_unet3d* h, const void* sample_dev, float timestep, const void* ehs_dev,
+                       void* out_dev, int io_dtype, int B, int F, int H, int W, void* workspace_dev,
+                       size_t workspace_bytes, void* stream);
+/* algorithmic FLOPs of one forward (GEMM/conv/attention only, MAC = 2), the roofline numerator. */
+double b2v_unet3d_flops(const b2v_unet3d* h, int B, int F, int H, int W);
+
+/* ------------------------------------------------------------------------------------------------
+ * Building-block ops (used by the UNet; exported so tests/ can check each kernel against the oracle).
+ * Activations are channels-last bf16: [rows, C] with rows = (b, f, y, x) flattened.
+ * ------------------------------------------------------------------------------------------------ */
+
+/* epilogue flags for b2v_op_gemm */
+#define B2V_EPI_GEGLU 1      /* W rows are [value | gate] interleaved per 128-column tile pair; out has N/2 columns */
+#define B2V_EPI_GELU 2
+
+/* out[M,N] = A[M,K] · W[N,K]^T (+bias[N]) (+rowbias[row/rows_per_group, N]) (+residual[M,N]); bf16 in/out,
+ * fp32 accumulate on tcgen05. taps/tap_row_stride: 1 tap = plain GEMM; 3 taps = temporal (3,1,1) conv
+ * where tap t reads row r+(t-1)*tap_row_stride inside a group of rows_per_batch rows, zero outside
+ * (K = taps*Kc, W laid out [N][tap][Kc]). */
+int b2v_op_gemm(const void* a_dev, const void* w_dev, const float* bias_dev, const float* rowbias_dev,
+                int64_t rows_per_group, const void* residual_dev, void* out_dev, int64_t M, int N, int Kc,
+                int taps, int64_t tap_row_stride, int64_t rows_per_batch, int flags, void* stream);
+
+/* 3x3 convolution, padding 1, stride 1 or 2, NHWC bf16, weights [Cout][3][3][Cin] bf16, implicit GEMM
+ * (TMA im2col -> tcgen05). mode 0 = TMA im2col, 1 = explicit im2col matrix in `scratch_dev` then GEMM. */
+size_t b2v_op_conv3x3_scratch_bytes(int N, int H, int W, int Cin, int stride, int mode);
+int b2v_op_conv3x3(const void* x_dev, const void* w_dev, const float* bias_dev, const float* rowbias_dev,
+                   int64_t rows_per_group, const void* residual_dev, void* out_dev, int N, int H, int W,
+                   int Cin, int Cout, int stride, int mode, void* scratch_dev, void* stream);
+
+/* GroupNorm (+SiLU) over channels-last rows: stats per (batch item, group) over rows_per_item rows x
+ * C/groups channels, then y = (x-mean)*rstd*gamma+beta (silu optional). x may be the channel concat of
+ * two tensors (x2_dev != NULL, C = C1 + C2). stats_dev: >= n_items*groups*2 doubles. */
+int b2v_op_group_norm(const void* x_dev, int C1, const void* x2_dev, int C2, const float* gamma_dev,
+                      const float* beta_dev, void* y_dev, int64_t n_items, int64_t rows_per_item,
+                      int groups, float eps, int silu, void* stats_dev, void* stream);
+int b2v_op_layer_norm(const void* x_dev, const float* gamma_dev, const float* beta_dev, void* y_dev,
+                      int64_t rows, int C, float eps, void* stream);
+
+/* softmax(Q K^T * scale) V, head_dim 64, bf16. q: [nb, Sq, ldq] rows, head h at column h*64;
+ * k/v: [nb / kv_group, Skv, ldk]; out [nb, Sq, ldo]. (tcgen05 flash attention.) */
+int b2v_op_attention(const void* q_dev, int64_t ldq, const void* k_dev, const void* v_dev, int64_t ldkv,
+                     void* out_dev, int64_t ldo, int nb, int heads, int Sq, int Skv, int kv_group,
+                     float scale, void* stream);
+/* attention over the frame axis: tokens [B, F, HW, *], sequence = F (<= 32), head_dim 64. */
+int b2v_op_temporal_attention(const void* qkv_dev, int64_t ld, int q_off, int k_off, int v_off,
+                              void* out_dev, int64_t ldo, int B, int F, int64_t HW, int heads,
+                              float scale, void* stream);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* B2V_H_ */
