@@ -1,0 +1,104 @@
+"""-m gpu: integer / byte kernels of the Proof-of-Inference path through the C-ABI: bit-exact against hashlib
+(the reference's own primitive, InferNet/neurons/miner.py:207-233, template/validator/proof.py:250-304)."""
+import hashlib
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _sorted_pair(l, r):
+    return hashlib.sha256(l + r if l < r else r + l).digest()
+
+
+def _tree(leaf_hashes):
+    tree = [list(leaf_hashes)]
+    while len(tree[-1]) > 1:
+        cur = tree[-1]
+        tree.append([_sorted_pair(cur[i], cur[i + 1] if i + 1 < len(cur) else cur[i]) for i in range(0, len(cur), 2)])
+    paths = []
+    for idx in range(len(leaf_hashes)):
+        p, i = [], idx
+        for level in tree[:-1]:
+            s = i ^ 1
+            p.append(level[s] if s < len(level) else level[i])
+            i //= 2
+        paths.append(p)
+    return tree[-1][0], paths
+
+
+@pytest.mark.parametrize("mode", [1, 2])
+@pytest.mark.parametrize("lens", [[0], [1], [55], [56], [63], [64], [65], [119], [120], [128], [1000, 3, 64, 0, 4096],
+                                  [2048] * 7, [100003]])
+def test_sha256_raw(cuda, mode, lens):
+    from b2v import ops
+    g = torch.Generator().manual_seed(sum(lens) + len(lens))
+    bufs = [torch.randint(0, 256, (n,), dtype=torch.uint8, generator=g) for n in lens]
+    dev = [b.to(cuda) if b.numel() else torch.empty(0, dtype=torch.uint8, device=cuda) for b in bufs]
+    dig = ops.sha256_leaves(dev, mode=mode).cpu().numpy()
+    for i, b in enumerate(bufs):
+        assert dig[i].tobytes() == hashlib.sha256(b.numpy().tobytes()).digest(), (mode, lens[i])
+
+
+@pytest.mark.parametrize("mode", [0, 1, 2])
+@pytest.mark.parametrize("shape", [(1, 4, 2, 8, 8), (1, 4, 5, 32, 32), (1, 4, 3, 5, 7)])
+def test_sha256_leaf_prefix_z_eps(cuda, mode, shape):
+    """leaf = t.to_bytes(2,'big') + z_bytes + eps_bytes (miner.py:207), z/eps hashed in place on the device."""
+    from b2v import ops
+    g = torch.Generator().manual_seed(shape[2])
+    ts = [981, 1, 65535, 0, 256]
+    zs = [torch.randn(shape, generator=g).half() for _ in ts]
+    es = [torch.randn(shape, generator=g).half() for _ in ts]
+    dig = ops.sha256_leaves([z.to(cuda) for z in zs], [e.to(cuda) for e in es], prefixes=ts, mode=mode).cpu().numpy()
+    for i, t in enumerate(ts):
+        want = hashlib.sha256(t.to_bytes(2, "big") + zs[i].numpy().tobytes() + es[i].numpy().tobytes()).digest()
+        assert dig[i].tobytes() == want
+
+
+def test_sha256_unaligned_views(cuda):
+    from b2v import ops
+    g = torch.Generator().manual_seed(9)
+    big = torch.randint(0, 256, (5000,), dtype=torch.uint8, generator=g)
+    d = big.to(cuda)
+    views = [(1, 1001), (3, 130), (2, 2), (7, 4999)]
+    dig = ops.sha256_leaves([d[a:b] for a, b in views], [d[a + 1:b] for a, b in views], mode=1).cpu().numpy()
+    for i, (a, b) in enumerate(views):
+        raw = big.numpy().tobytes()
+        assert dig[i].tobytes() == hashlib.sha256(raw[a:b] + raw[a + 1:b]).digest()
+
+
+def test_sha256_prefix_range_error(cuda):
+    from b2v import ops
+    z = torch.zeros(8, dtype=torch.float16, device=cuda)
+    with pytest.raises(OverflowError):
+        ops.sha256_leaves([z], [z], prefixes=[70000])
+
+
+@pytest.mark.parametrize("n", [1, 2, 3, 5, 8, 50, 51, 400, 1000])
+def test_merkle_build_verify(cuda, n):
+    from b2v import ops
+    leaves = [hashlib.sha256(bytes([i % 256, i // 256]) * 16).digest() for i in range(n)]
+    lh = torch.tensor(list(b"".join(leaves)), dtype=torch.uint8).reshape(n, 32).to(cuda)
+    root, paths = ops.merkle_build(lh)
+    want_root, want_paths = _tree(leaves)
+    assert bytes(root.cpu().numpy().tobytes()) == want_root
+    p = paths.cpu().numpy()
+    for i in range(n):
+        assert [p[i, k].tobytes() for k in range(p.shape[1])] == want_paths[i]
+    ok = ops.merkle_verify(lh, paths, root).cpu()
+    assert bool(ok.all())
+    if n > 1:
+        bad = lh.clone()
+        bad[n // 2, 5] ^= 1
+        ok = ops.merkle_verify(bad, paths, root).cpu()
+        assert int(ok.sum()) == n - 1 and ok[n // 2] == 0
+
+
+def test_merkle_duplicate_leaves_and_ties(cuda):
+    """equal siblings (left == right) take the `else` branch of `if left < right` (proof.py:266): right+left."""
+    from b2v import ops
+    leaves = [hashlib.sha256(b"same").digest()] * 6
+    lh = torch.tensor(list(b"".join(leaves)), dtype=torch.uint8).reshape(6, 32).to(cuda)
+    root, _ = ops.merkle_build(lh)
+    assert root.cpu().numpy().tobytes() == _tree(leaves)[0]
