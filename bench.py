@@ -1,0 +1,479 @@
+#!/usr/bin/env python3
+"""Headline benchmark: ZeroscopeXL denoise steps/s (BASELINE.json `metric`) + Merkle commit GB/s.
+
+    python bench.py --gpus N --steps K --warmup W            (N>1: launched per rank by torch.distributed.run)
+    python bench.py --impl reference ...                      (CPU arm: the oracle port of the reference's path)
+
+A "step" = ONE scheduler timestep advanced for the WHOLE T-frame video: every frame window of the plan goes through
+one UNet3D forward (CFG batch 2) and one fused CFG+DDIM(+context) kernel on the rank that owns it
+(SURVEY.md §8d). Workload: BASELINE.json configs[2] — ZeroscopeXL 1024x576, 24 frames, fsdp_chunked_coherent
+(hybrid_ctx: context injection + ramp smoothing), random-init weights, synthetic prompt embeddings and latents.
+Window plan = the reference's own planner for the world size (fsdp_chunked_coherent.py:149-177); at N=8 its defaults do
+not terminate, so N=8 runs `--chunk_size 4 --overlap 1` and says so in `config.plan`.
+Total work is fixed as N grows -> "scaling": "strong".
+"""
+import argparse
+import json
+import os
+import statistics
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+HEIGHT, WIDTH, FRAMES, TOTAL_STEPS = 576, 1024, 24, 50
+GUIDANCE, CTX_W = 7.5, 0.35
+METRIC = "ZeroscopeXL denoise steps/sec (1024x576, 24 frames, fsdp_chunked_coherent hybrid_ctx)"
+
+
+def measured_peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        d = json.load(open(p))
+        return {"hbm_gbs": d["hbm_gbs"], "bf16_burst": d["bf16_tflops"], "bf16_sustained": d["bf16_tflops_sustained"],
+                "source": "measured (MEASURED_PEAKS.json)"}
+    return {"hbm_gbs": 6650.0, "bf16_burst": 1590.0, "bf16_sustained": 1400.0, "source": "fallback (B200_PROFILING.md)"}
+
+
+def plan_for(world):
+    """(chunk_size, overlap, note) handed to the coherent planner."""
+    if world >= 8:
+        return 4, 1, "explicit --chunk_size 4 --overlap 1 (reference defaults loop forever at W=8)"
+    return 0, 4, "reference defaults (--chunk_size 0 --overlap 4)"
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons DURING the timed region (B200_PROFILING.md recipe)."""
+    Q = "index,clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown," \
+        "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown," \
+        "clocks_event_reasons.sw_power_cap"
+
+    def __init__(self, index):
+        self.index, self.rows, self.proc = index, [], None
+
+    def start(self):
+        try:
+            self.proc = subprocess.Popen(["nvidia-smi", "--query-gpu=" + self.Q, "--format=csv,noheader,nounits",
+                                          "-lms", "100", "-i", str(self.index)], stdout=subprocess.PIPE,
+                                         stderr=subprocess.DEVNULL, text=True)
+            self.t = threading.Thread(target=self._read, daemon=True)
+            self.t.start()
+        except Exception:
+            self.proc = None
+
+    def _read(self):
+        for line in self.proc.stdout:
+            f = [x.strip() for x in line.split(",")]
+            if len(f) >= 8:
+                self.rows.append(f)
+
+    def stop(self):
+        if not self.proc:
+            return {"sm_mhz": None, "sm_max_mhz": None, "reasons": ["nvidia-smi unavailable"]}
+        self.proc.terminate()
+        try:
+            self.proc.wait(timeout=2)
+        except Exception:
+            self.proc.kill()
+        sm = [float(r[1]) for r in self.rows if r[1].replace(".", "").isdigit()]
+        mx = [float(r[2]) for r in self.rows if r[2].replace(".", "").isdigit()]
+        pw = [float(r[3]) for r in self.rows if r[3].replace(".", "").isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = [n for i, n in enumerate(names) if any(r[4 + i].lower().startswith("active") for r in self.rows)]
+        return {"sm_mhz": statistics.median(sm) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "power_w_max": max(pw) if pw else None, "samples": len(self.rows), "reasons": reasons}
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# CPU arm: the oracle port of the reference's path on the host cores (cpu_baseline leg and --impl reference)
+# ---------------------------------------------------------------------------------------------------------------
+def unet_flops(F, h, w, B=2):
+    """Algorithmic FLOPs of one UNet3D forward (same formula as b2v_unet3d_flops), host-side."""
+    ch, xd, TL, hd = (320, 640, 1280, 1280), 1024, 77, 64
+    N = B * F
+    fl = 0.0
+
+    def conv(M, ci, co, k=9):
+        return 2.0 * M * ci * co * k
+
+    def block(M, dim, cross, seq, nbatch):
+        f = 2.0 * M * dim * dim * 3 + 2.0 * M * dim * dim            # qkv1 + o1
+        f += 4.0 * nbatch * (dim // hd) * seq * seq * hd
+        if cross:
+            f += 2.0 * M * dim * dim + 2.0 * B * TL * xd * 2 * dim + 2.0 * M * dim * dim
+            f += 4.0 * nbatch * (dim // hd) * seq * TL * hd
+        else:
+            f += 2.0 * M * dim * dim * 3 + 2.0 * M * dim * dim
+            f += 4.0 * nbatch * (dim // hd) * seq * seq * hd
+        f += 2.0 * M * dim * 8 * dim + 2.0 * M * 4 * dim * dim        # GEGLU FF
+        return f
+
+    def spatial(M, C, S):
+        return 2 * 2.0 * M * C * C + block(M, C, True, S, N)
+
+    def temporal(M, C, inner, S):
+        return 2 * 2.0 * M * C * inner + block(M, inner, False, F, B * S)
+
+    def resnet(M, ci, co):
+        return conv(M, ci, co) + conv(M, co, co) + (conv(M, ci, co, 1) if ci != co else 0.0)
+
+    def tconv(M, C):
+        return 4 * 2.0 * M * C * 3 * C
+
+    hh, ww = h, w
+    M = N * hh * ww
+    fl += conv(M, 4, ch[0]) + temporal(M, ch[0], 512, hh * ww)
+    prev = ch[0]
+    dims = []
+    for i, c in enumerate(ch):
+        M = N * hh * ww
+        for j in range(2):
+            fl += resnet(M, prev if j == 0 else c, c) + tconv(M, c)
+            if i < 3:
+                fl += spatial(M, c, hh * ww) + temporal(M, c, c, hh * ww)
+        dims.append((hh, ww))
+        if i < 3:
+            hh, ww = (hh - 1) // 2 + 1, (ww - 1) // 2 + 1
+            fl += conv(N * hh * ww, c, c)
+        prev = c
+    M = N * hh * ww
+    fl += 2 * resnet(M, ch[3], ch[3]) + 2 * tconv(M, ch[3]) + spatial(M, ch[3], hh * ww) + temporal(M, ch[3], ch[3], hh * ww)
+    rev = ch[::-1]
+    prev_out = rev[0]
+    for i, c in enumerate(rev):
+        hh, ww = dims[3 - i]
+        M = N * hh * ww
+        inc = rev[min(i + 1, 3)]
+        for j in range(3):
+            skip = inc if j == 2 else c
+            fl += resnet(M, (prev_out if j == 0 else c) + skip, c) + tconv(M, c)
+            if i > 0:
+                fl += spatial(M, c, hh * ww) + temporal(M, c, c, hh * ww)
+        if i < 3:
+            fl += conv(N * 4 * hh * ww, c, c)
+        prev_out = c
+    fl += conv(N * h * w, ch[0], 4)
+    return fl
+
+
+def video_step_flops(ranges, h, w):
+    return sum(unet_flops(e - s, h, w) for s, e in ranges)
+
+
+class CpuOracleArm:
+    """The reference's denoise step restated on the CPU (oracle/unet3d_ref.py + oracle/ddim_ref.py), all host threads.
+    One timed "sample" = UNet forward (CFG batch 2) + CFG combine + DDIM update on a reduced window; steps/s is
+    extrapolated by the algorithmic FLOP ratio sample / whole-video step."""
+
+    def __init__(self, budget_s):
+        import torch
+        from oracle import unet3d_ref as R
+        from oracle.ddim_ref import pipeline_scheduler
+        self.torch, self.R = torch, R
+        self.cores = os.cpu_count() or 1
+        torch.set_num_threads(self.cores)
+        t0 = time.time()
+        self.net = R.random_init_(R.UNet3DConditionModel(R.ZEROSCOPE), seed=1234).eval()
+        self.sched = pipeline_scheduler()
+        self.sched.set_timesteps(TOTAL_STEPS)
+        self.build_s = time.time() - t0
+        self.budget_s = budget_s
+        g = torch.Generator().manual_seed(1)
+        self.emb = torch.randn(2, 77, 1024, generator=g)
+
+    def one(self, F, h, w, t):
+        torch = self.torch
+        g = torch.Generator().manual_seed(0)
+        lat = torch.randn(1, 4, F, h, w, generator=g)
+        t0 = time.time()
+        with torch.no_grad():
+            x = torch.cat([lat] * 2)
+            noise = self.net(x, t, self.emb)
+            u, c = noise.chunk(2)
+            out = self.sched.step(u + GUIDANCE * (c - u), t, lat).prev_sample
+        assert bool(torch.isfinite(out).all())
+        return time.time() - t0
+
+    def choose_sample(self, n_iters):
+        """Calibrate on a tiny window, then take the largest of the candidate samples whose n_iters fit the budget."""
+        t_cal = self.one(1, 16, 16, 981)
+        rate = unet_flops(1, 16, 16) / t_cal
+        cands = [(1, 72, 128), (1, 40, 72), (1, 24, 32), (1, 16, 16)]
+        for F, h, w in cands:
+            if unet_flops(F, h, w) / rate * n_iters <= self.budget_s:
+                return F, h, w
+        return cands[-1]
+
+
+def cpu_line(args, ranges, h, w, as_reference):
+    arm = CpuOracleArm(budget_s=120.0 if as_reference else 25.0)
+    iters = (args.steps + args.warmup) if as_reference else 1
+    F, sh, sw = arm.choose_sample(iters)
+    ts = [int(t) for t in arm.sched.timesteps]
+    if as_reference:
+        for i in range(args.warmup):
+            arm.one(F, sh, sw, ts[i % len(ts)])
+        t0 = time.time()
+        for i in range(args.steps):
+            arm.one(F, sh, sw, ts[(args.warmup + i) % len(ts)])
+        per = (time.time() - t0) / args.steps
+    else:
+        per = arm.one(F, sh, sw, ts[0])
+    ratio = video_step_flops(ranges, h, w) / unet_flops(F, sh, sw)
+    value = 1.0 / (per * ratio)
+    sample = ("oracle port (torch fp32 CPU restatement; diffusers not installable here): UNet3D forward CFG batch 2 on a "
+              "%d-frame %dx%d latent window + CFG + DDIM update = %.3f TFLOP, %.2f s; extrapolated to the whole-video "
+              "step (%.1f TFLOP) by the algorithmic FLOP ratio %.1f" % (F, sh, sw, unet_flops(F, sh, sw) / 1e12, per,
+                                                                        video_step_flops(ranges, h, w) / 1e12, ratio))
+    return value, per, {"value": value, "unit": "steps/s", "cores": arm.cores, "kind": "port", "sample": sample}
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# GPU arm
+# ---------------------------------------------------------------------------------------------------------------
+def gpu_main(args):
+    import torch
+    import torch.distributed as dist
+    import b2v  # noqa: F401
+    from b2v import ops, planner, proof
+    from b2v.pipeline import VideoPipeline
+    from b2v.strategies.common import CudaDenoiser, base_noise
+
+    rank, world = int(os.getenv("RANK", 0)), int(os.getenv("WORLD_SIZE", 1))
+    local = int(os.getenv("LOCAL_RANK", 0))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("bench.py --gpus %d must be launched with torch.distributed.run (one rank per GPU)" % args.gpus)
+    torch.cuda.set_device(local)
+    dev = torch.device("cuda", local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=dev)
+    peaks = measured_peaks()
+    h, w = HEIGHT // 8, WIDTH // 8
+    cs, ov, plan_note = plan_for(world)
+    plan = planner.plan(FRAMES, world, cs, ov, variant="coherent")
+    mine = plan.of_rank(rank)
+
+    dtype = torch.bfloat16
+    pipe = VideoPipeline.from_random("cerspense/zeroscope_v2_XL", device=dev, seed=1234, dtype=dtype)
+    pipe.scheduler.set_timesteps(TOTAL_STEPS, device="cuda")
+    ts = pipe.scheduler.host_timesteps()
+    toks = pipe.tokenizer(["a rocket in space, 4k", ""])
+    emb = pipe.text_encoder(toks.input_ids)[0]
+    cond, uncond = emb[:1], emb[1:]
+    base = base_noise(4, FRAMES, h, w, dtype, dev)
+    ctx = ops.context_mean(base)
+    den = CudaDenoiser(pipe, uncond, cond, GUIDANCE, ctx=ctx, context_weight=CTX_W)
+    unet, sched = pipe.unet, pipe.scheduler
+
+    # per-window resident state: latent, UNet input (CFG-duplicated, context injected), eps buffer
+    state = []
+    for s, e in mine:
+        lat = base[:, :, s:e].clone()
+        x = ops.make_unet_input(lat, 2, ctx=ctx, ctx_w=CTX_W)
+        state.append([lat, x, torch.empty_like(x)])
+
+    def video_step(i):
+        t = ts[i % len(ts)]
+        for st in state:
+            unet.forward_into(st[1], t, den.emb, st[2])
+            st[0], st[1] = sched.fused_cfg_step(st[0], st[2], t, GUIDANCE, ctx=ctx, ctx_w=CTX_W, n_dup=2, xnext=st[1])
+
+    def sync_all():
+        torch.cuda.synchronize(dev)
+        if world > 1:
+            dist.barrier()
+            torch.cuda.synchronize(dev)
+
+    for i in range(args.warmup):
+        video_step(i)
+    sync_all()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    l0 = ops.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        video_step(args.warmup + i)
+    e1.record()
+    sync_all()
+    launches = ops.launch_count() - l0
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    total_ms = float(ms.item())
+    clocks = sampler.stop() if rank == 0 else None
+    value = args.steps / (total_ms / 1e3)
+
+    # ---- e2e: the same step through the public per-step API with HOST buffers (pinned), copies inside the timing ----
+    host_lat = [st[0].to("cpu").pin_memory() for st in state]
+    host_emb = den.emb.to("cpu").pin_memory()
+    host_out = [torch.empty_like(hl).pin_memory() for hl in host_lat]
+
+    def e2e_step(i):
+        t = ts[i % len(ts)]
+        embd = host_emb.to(dev, non_blocking=True)
+        for k in range(len(state)):
+            lat = host_lat[k].to(dev, non_blocking=True)
+            x = ops.make_unet_input(lat, 2, ctx=ctx, ctx_w=CTX_W)
+            eps2 = unet(x, t, encoder_hidden_states=embd).sample
+            out, _ = sched.fused_cfg_step(lat, eps2, t, GUIDANCE)
+            host_out[k].copy_(out, non_blocking=True)
+        torch.cuda.synchronize(dev)  # the caller holds the step's result on the host
+
+    e2e_step(0)
+    sync_all()
+    t0 = time.perf_counter()
+    for i in range(args.steps):
+        e2e_step(i)
+    sync_all()
+    e2e_s = torch.tensor([time.perf_counter() - t0], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(e2e_s, op=dist.ReduceOp.MAX)
+    e2e_value = args.steps / float(e2e_s.item())
+    bi = sum(hl.numel() * hl.element_size() for hl in host_lat) + host_emb.numel() * host_emb.element_size()
+    bo = sum(ho.numel() * ho.element_size() for ho in host_out)
+    if world > 1:
+        tb = torch.tensor([bi, bo], device=dev, dtype=torch.float64)
+        dist.all_reduce(tb)
+        bi, bo = int(tb[0].item()), int(tb[1].item())
+
+    if rank != 0:
+        if world > 1:
+            dist.barrier()
+            dist.destroy_process_group()
+        return
+
+    # ---- rank 0 only: rooflines, Merkle commit, CPU baseline ------------------------------------------------------
+    flops_rank = [sum(unet.flops(2, e - s, h, w) for s, e in plan.of_rank(r)) for r in range(world)]
+    step_flops = max(flops_rank)  # the bottleneck rank paces the step
+    per_step_ms = total_ms / args.steps
+    achieved_step = step_flops / (per_step_ms / 1e3) / 1e12
+    roofline_step = {"bound": "tensor", "achieved": achieved_step, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
+                     "frac": achieved_step / peaks["bf16_sustained"], "traffic": None,
+                     "what": "whole UNet3D forward(s) of the bottleneck rank per video-step: algorithmic FLOPs "
+                             "(b2v_unet3d_flops, MAC=2) / CUDA-event time; peak = sustained cuBLAS bf16, " + peaks["source"]}
+    roofline = dominant_kernel_roofline(torch, ops, dev, peaks, mine)
+    merkle = merkle_bench(torch, ops, proof, dev, peaks, h, w)
+    cpu = None
+    if world == 1 and not args.no_cpu_baseline:
+        try:
+            _, _, cpu = cpu_line(args, plan.ranges, h, w, as_reference=False)
+        except Exception as ex:  # the baseline is a report, never a reason to lose the GPU line
+            cpu = {"value": None, "unit": "steps/s", "cores": os.cpu_count(), "kind": "port", "sample": "failed: %r" % (ex,)}
+    line = {
+        "metric": METRIC, "value": value, "unit": "steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": per_step_ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "bf16", "data": "synthetic (random-init weights seed 1234, seeded prompt embeddings, seed-0 base noise)",
+        "config": {"workload": "ZeroscopeXL 1024x576x24f fsdp_chunked_coherent hybrid_ctx, CFG 7.5, DDIM 50-step schedule",
+                   "plan": {"note": plan_note, "chunk_size": plan.chunk_size, "overlap": plan.overlap,
+                            "windows": plan.ranges, "windows_per_rank": len(mine)},
+                   "latent": [1, 4, FRAMES, h, w], "unet_flops_per_step_bottleneck_rank": step_flops,
+                   "l2": "no flush: each step streams 2.8 GB of weights + >2 GB of activations (>> 126 MB L2)"},
+        "e2e": {"value": e2e_value, "unit": "steps/s", "h2d_bytes_per_step": bi, "d2h_bytes_per_step": bo},
+        "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "roofline_step": roofline_step,
+        "merkle": merkle, "cpu_baseline": cpu,
+    }
+    print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def _time_cuda(torch, fn, iters=3, warm=2):
+    for _ in range(warm):
+        fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for _ in range(iters):
+        fn()
+    e1.record()
+    torch.cuda.synchronize()
+    return e0.elapsed_time(e1) / iters
+
+
+def dominant_kernel_roofline(torch, ops, dev, peaks, mine):
+    """The kernel with the largest share of a step (profiles/: attn_kernel at UNet level 0, spatial self-attention,
+    seq 9216, 5 heads, batch 2*F) timed live, alone, with CUDA events; burst peak because it is timed in isolation."""
+    F = max(e - s for s, e in mine)
+    nb, heads, S = 2 * F, 5, (HEIGHT // 8) * (WIDTH // 8)
+    g = torch.Generator(device=dev).manual_seed(0)
+    q, k, v = (torch.randn(nb, S, heads * 64, device=dev, generator=g).to(torch.bfloat16) for _ in range(3))
+    ms = _time_cuda(torch, lambda: ops.attention(q, k, v, heads))
+    flops = 4.0 * nb * heads * S * S * 64
+    ach = flops / (ms / 1e3) / 1e12
+    return {"bound": "tensor", "achieved": ach, "peak": peaks["bf16_burst"], "unit": "TFLOP/s",
+            "frac": ach / peaks["bf16_burst"], "traffic": None, "kernel": "attn_kernel (spatial self-attention L0)",
+            "shape": {"batch": nb, "heads": heads, "seq": S, "head_dim": 64}, "ms_per_launch": ms,
+            "flops_per_launch": flops, "peak_source": "burst cuBLAS bf16, " + peaks["source"]}
+
+
+def merkle_bench(torch, ops, proof, dev, peaks, h, w):
+    """Merkle commit GB/s (BASELINE.json metric, second half): leaves of a 50-step XL trajectory (miner path: batch 1,
+    24 frames; leaf = be16(t) ‖ z fp16 ‖ eps fp16 = 3 538 946 B) hashed in place + tree, device resident."""
+    out = {}
+    elems = 4 * FRAMES * h * w
+    for n in (50, 400):
+        g = torch.Generator(device=dev).manual_seed(n)
+        zs = torch.randn(n, elems, device=dev, generator=g).half()
+        es = torch.randn(n, elems, device=dev, generator=g).half()
+        zl, el = [zs[i] for i in range(n)], [es[i] for i in range(n)]
+        ts = [(981 - 20 * i) % 1000 for i in range(n)]
+        ms = _time_cuda(torch, lambda: proof.commit_trajectory_device(zl, el, ts), iters=2, warm=1)
+        msg = 2 + 4 * elems
+        alg = n * ((msg + 9 + 63) // 64) * 64 + (n - 1) * 128
+        out["leaves_%d" % n] = {"gb_per_s": alg / (ms / 1e3) / 1e9, "ms": ms, "bytes": alg}
+        if n == 50:
+            t0 = time.perf_counter()
+            root, leaf = proof.build_merkle_tree(zl, el, ts)
+            torch.cuda.synchronize()
+            out["e2e_build_merkle_tree_50"] = {"gb_per_s": alg / (time.perf_counter() - t0) / 1e9,
+                                               "note": "drop-in call incl. D2H of every leaf's bytes (return value)"}
+        del zs, es, zl, el
+    best = max(out["leaves_50"]["gb_per_s"], out["leaves_400"]["gb_per_s"])
+    out["roofline"] = {"bound": "hbm", "achieved": best, "peak": peaks["hbm_gbs"], "unit": "GB/s",
+                       "frac": best / peaks["hbm_gbs"], "traffic": None,
+                       "note": "SHA-256 is a serial chain per leaf: bounded by integer-pipe latency x number of leaves, "
+                               "not by HBM (SURVEY.md §8d); HBM peak shown as the contract's denominator"}
+    out["metric"] = "Merkle commit GB/s"
+    return out
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b2v", choices=["b2v", "reference"])
+    ap.add_argument("--no-cpu-baseline", dest="no_cpu_baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        if int(os.getenv("RANK", 0)) != 0:
+            return
+        import b2v  # noqa: F401  (host-side planner only; no GPU work on this arm)
+        from b2v import planner
+        world = int(os.getenv("WORLD_SIZE", args.gpus))
+        cs, ov, note = plan_for(world)
+        plan = planner.plan(FRAMES, world, cs, ov, variant="coherent")
+        h, w = HEIGHT // 8, WIDTH // 8
+        # the CPU arm has one host: it executes every rank's windows, i.e. the whole-video step
+        value, per, cpu = cpu_line(args, plan.ranges, h, w, as_reference=True)
+        print(json.dumps({
+            "impl": "reference", "metric": METRIC, "value": value, "unit": "steps/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / value, "higher_is_better": True,
+            "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": "ZeroscopeXL 1024x576x24f fsdp_chunked_coherent hybrid_ctx, CFG 7.5 (CPU oracle port)",
+                       "plan": {"note": note, "windows": plan.ranges}},
+            "cpu_baseline": cpu, "e2e": {"value": value, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+            "gpu_launches": 0}), flush=True)
+        return
+    gpu_main(args)
+
+
+if __name__ == "__main__":
+    main()

@@ -50,7 +50,11 @@ extern "C" int b2v_op_group_norm(const void* x_dev, int C1, const void* x2_dev, 
   B2V_CHECK(x_dev && gamma_dev && beta_dev && y_dev && stats_dev, "null argument");
   B2V_TRY(b2v_device_check());
   return group_norm(x_dev, C1, x2_dev, C2, gamma_dev, beta_dev, y_dev, n_items, rows_per_item, groups, eps, silu,
-                    (double*)stats_dev, (cudaStream_t)stream);
+                    stats_dev, (cudaStream_t)stream);
+}
+
+extern "C" size_t b2v_op_group_norm_scratch_bytes(int64_t n_items, int64_t rows_per_item, int groups) {
+  return group_norm_scratch_bytes(n_items, rows_per_item, groups);
 }
 
 extern "C" int b2v_op_layer_norm(const void* x_dev, const float* gamma_dev, const float* beta_dev, void* y_dev,

@@ -14,22 +14,22 @@ namespace {
 // ---------------- GroupNorm ----------------
 // pass 1: per-(item, group) sum / sum of squares. grid = (row_splits, n_items); block = 64 x 4 threads:
 // threadIdx.x walks the 8-channel vectors of a row (coalesced 1 KiB per 64 threads), threadIdx.y the rows.
-// C/groups is always even, so a bf16 pair never straddles two groups: partial sums are kept per pair in
-// registers, flushed once per thread through shared-memory atomics, then one fp64 atomic per (CTA, group).
+// C/groups is always even, so a bf16 pair never straddles two groups. DETERMINISTIC on purpose (the commitment
+// re-executes steps bit-for-bit): per-thread pair partials go to shared memory, one thread per group folds them in a
+// fixed order, each CTA writes its partial to its own slot, and gn_finalize_kernel folds the slots sequentially in
+// fp64 — no atomics anywhere.
 constexpr int GN_TX = 64, GN_TY = 4, GN_THREADS = GN_TX * GN_TY;
 
 template <int ITERS>
 __global__ void __launch_bounds__(GN_THREADS)
 gn_stats_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat16* __restrict__ x2, int C2,
-                int64_t rows_per_item, int groups, double* __restrict__ stats) {
-  extern __shared__ float sh[];  // [2][groups]
+                int64_t rows_per_item, int groups, float* __restrict__ partial /*[item][split][group][2]*/) {
+  extern __shared__ float sh[];  // [2][GN_TY][C/2]
   const int C = C1 + C2;
-  const int vecs = C >> 3;
+  const int pairs = C >> 1;
   const int cpg = C / groups;
   const int item = blockIdx.y;
   const int tx = threadIdx.x & (GN_TX - 1), ty = threadIdx.x / GN_TX;
-  for (int i = threadIdx.x; i < 2 * groups; i += GN_THREADS) sh[i] = 0.f;
-  __syncthreads();
   const int64_t rows_per_cta = (rows_per_item + gridDim.x - 1) / gridDim.x;
   const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta;
   int64_t r1 = r0 + rows_per_cta;
@@ -58,35 +58,62 @@ gn_stats_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat1
       }
     }
   }
+  float* shs = sh;
+  float* shq = sh + GN_TY * pairs;
 #pragma unroll
   for (int i = 0; i < ITERS; ++i) {
     const int c = (tx + i * GN_TX) << 3;
     if (c < C) {
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const int g = (c + 2 * j) / cpg;
-        atomicAdd(&sh[g], s[i][j]);
-        atomicAdd(&sh[groups + g], ss[i][j]);
+        shs[ty * pairs + (c >> 1) + j] = s[i][j];
+        shq[ty * pairs + (c >> 1) + j] = ss[i][j];
       }
     }
   }
   __syncthreads();
-  for (int i = threadIdx.x; i < groups; i += GN_THREADS) {
-    atomicAdd(&stats[((int64_t)item * groups + i) * 2], (double)sh[i]);
-    atomicAdd(&stats[((int64_t)item * groups + i) * 2 + 1], (double)sh[groups + i]);
+  const int ppg = cpg >> 1;
+  for (int g = threadIdx.x; g < groups; g += GN_THREADS) {
+    float a = 0.f, q = 0.f;
+    for (int y = 0; y < GN_TY; ++y)
+      for (int k = 0; k < ppg; ++k) {
+        a += shs[y * pairs + g * ppg + k];
+        q += shq[y * pairs + g * ppg + k];
+      }
+    float* dst = partial + ((((int64_t)item * gridDim.x + blockIdx.x) * groups + g) << 1);
+    dst[0] = a;
+    dst[1] = q;
   }
+}
+
+// fold the per-CTA partials in a fixed order: stats[item][group] = {mean, rstd}
+__global__ void gn_finalize_kernel(const float* __restrict__ partial, int splits, int groups, int64_t n_items,
+                                   double cnt, float eps, float2* __restrict__ stats) {
+  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+  if (i >= n_items * groups) return;
+  const int64_t item = i / groups;
+  const int g = (int)(i % groups);
+  double a = 0.0, q = 0.0;
+  for (int sp = 0; sp < splits; ++sp) {
+    const float* p = partial + (((item * splits + sp) * groups + g) << 1);
+    a += (double)p[0];
+    q += (double)p[1];
+  }
+  const double m = a / cnt;
+  double var = q / cnt - m * m;
+  if (var < 0.0) var = 0.0;
+  stats[i] = make_float2((float)m, (float)(1.0 / sqrt(var + (double)eps)));
 }
 
 // pass 2: y = (x - mean) * rstd * gamma + beta, optional SiLU. One thread per 8-channel vector.
 __global__ void __launch_bounds__(256)
 gn_apply_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat16* __restrict__ x2, int C2,
                 const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
-                int64_t total_rows, int64_t rows_per_item, int groups, float eps, int silu,
-                const double* __restrict__ stats) {
+                int64_t total_rows, int64_t rows_per_item, int groups, int silu,
+                const float2* __restrict__ stats) {
   const int C = C1 + C2;
   const int vecs = C >> 3;
   const int cpg = C / groups;
-  const double cnt = (double)rows_per_item * (double)cpg;
   const int64_t total = total_rows * vecs;
   for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < total; w += (int64_t)gridDim.x * blockDim.x) {
     const int64_t grow = w / vecs;
@@ -112,12 +139,9 @@ gn_apply_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat1
     for (int j = 0; j < 8; ++j) {
       const int g = (c + j) / cpg;
       if (g != last_g) {
-        const double sm = stats[(item * groups + g) * 2], sq = stats[(item * groups + g) * 2 + 1];
-        const double m = sm / cnt;
-        double var = sq / cnt - m * m;
-        if (var < 0.0) var = 0.0;
-        mean = (float)m;
-        rstd = (float)(1.0 / sqrt(var + (double)eps));
+        const float2 st = __ldg(stats + item * groups + g);
+        mean = st.x;
+        rstd = st.y;
         last_g = g;
       }
       float v = (f[j] - mean) * rstd * gm[j] + bt[j];
@@ -240,24 +264,36 @@ inline int grid_1d(int64_t work_items, int block, int per_sm) {
 
 }  // namespace
 
-int group_norm(const void* x1, int C1, const void* x2, int C2, const float* gamma, const float* beta, void* y,
-               int64_t n_items, int64_t rows_per_item, int groups, float eps, int silu, double* stats,
-               cudaStream_t s) {
-  const int C = C1 + C2;
-  B2V_CHECK(C % 8 == 0 && C1 % 8 == 0 && C % groups == 0 && (C / groups) % 2 == 0, "group_norm: C=%d (C1=%d) groups=%d unsupported", C, C1, groups);
-  B2V_CHECK(n_items > 0 && n_items < 65536 && rows_per_item > 0, "group_norm: bad item count");
-  B2V_CUDA_OK(cudaMemsetAsync(stats, 0, sizeof(double) * 2 * (size_t)n_items * groups, s));
+int gn_splits(int64_t n_items, int64_t rows_per_item) {
   // enough CTAs per item to fill the machine ~4x, at least 32 rows each
   int64_t splits = ((int64_t)sm_count() * 4 + n_items - 1) / n_items;
   const int64_t max_splits = (rows_per_item + 31) / 32;
   if (splits > max_splits) splits = max_splits;
   if (splits < 1) splits = 1;
+  return (int)splits;
+}
+
+size_t group_norm_scratch_bytes(int64_t n_items, int64_t rows_per_item, int groups) {
+  const size_t partial = sizeof(float) * 2 * (size_t)n_items * gn_splits(n_items, rows_per_item) * groups;
+  return ((partial + 255) & ~(size_t)255) + sizeof(float2) * (size_t)n_items * groups;
+}
+
+int group_norm(const void* x1, int C1, const void* x2, int C2, const float* gamma, const float* beta, void* y,
+               int64_t n_items, int64_t rows_per_item, int groups, float eps, int silu, void* scratch,
+               cudaStream_t s) {
+  const int C = C1 + C2;
+  B2V_CHECK(C % 8 == 0 && C1 % 8 == 0 && C % groups == 0 && (C / groups) % 2 == 0, "group_norm: C=%d (C1=%d) groups=%d unsupported", C, C1, groups);
+  B2V_CHECK(n_items > 0 && n_items < 65536 && rows_per_item > 0, "group_norm: bad item count");
+  const int splits = gn_splits(n_items, rows_per_item);
+  float* partial = (float*)scratch;
+  const size_t pbytes = sizeof(float) * 2 * (size_t)n_items * splits * groups;
+  float2* stats = (float2*)((uint8_t*)scratch + ((pbytes + 255) & ~(size_t)255));
   dim3 grid((unsigned)splits, (unsigned)n_items);
   const int iters = ((C >> 3) + GN_TX - 1) / GN_TX;
-  const size_t shb = sizeof(float) * 2 * groups;
+  const size_t shb = sizeof(float) * 2 * GN_TY * (C >> 1);
 #define B2V_GN_STATS(I)                                                                                     \
   gn_stats_kernel<I><<<grid, GN_THREADS, shb, s>>>((const __nv_bfloat16*)x1, C1, (const __nv_bfloat16*)x2, C2, \
-                                                   rows_per_item, groups, stats)
+                                                   rows_per_item, groups, partial)
   switch (iters) {
     case 1: B2V_GN_STATS(1); break;
     case 2: B2V_GN_STATS(2); break;
@@ -268,10 +304,15 @@ int group_norm(const void* x1, int C1, const void* x2, int C2, const float* gamm
   }
 #undef B2V_GN_STATS
   count_launch();
+  const int64_t ng = n_items * groups;
+  gn_finalize_kernel<<<(unsigned)((ng + 127) / 128), 128, 0, s>>>(partial, splits, groups, n_items,
+                                                                   (double)rows_per_item * (double)(C / groups), eps,
+                                                                   stats);
+  count_launch();
   const int64_t total_rows = n_items * rows_per_item;
   gn_apply_kernel<<<grid_1d(total_rows * (C >> 3), 256, 8), 256, 0, s>>>(
       (const __nv_bfloat16*)x1, C1, (const __nv_bfloat16*)x2, C2, gamma, beta, (__nv_bfloat16*)y, total_rows,
-      rows_per_item, groups, eps, silu, stats);
+      rows_per_item, groups, silu, stats);
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;

@@ -9,8 +9,9 @@ namespace b2v {
 
 // norm.cu
 int group_norm(const void* x1, int C1, const void* x2, int C2, const float* gamma, const float* beta, void* y,
-               int64_t n_items, int64_t rows_per_item, int groups, float eps, int silu, double* stats,
+               int64_t n_items, int64_t rows_per_item, int groups, float eps, int silu, void* scratch,
                cudaStream_t s);
+size_t group_norm_scratch_bytes(int64_t n_items, int64_t rows_per_item, int groups);
 int layer_norm(const void* x, const float* gamma, const float* beta, void* y, int64_t rows, int C, float eps,
                cudaStream_t s);
 int upsample2x(const void* x, void* y, int N, int H, int W, int C, cudaStream_t s);

@@ -383,7 +383,7 @@ void gemm(Ctx& c, const bf16* a, int64_t M, const Lin& l, const bf16* residual, 
 
 void gn(Ctx& c, const bf16* x1, int C1, const bf16* x2, int C2, const Norm& n, bf16* y, int64_t items, int64_t rows_per,
         float eps, int silu) {
-  double* stats = (double*)c.bytes(sizeof(double) * 2 * (size_t)items * c.u->cfg.norm_num_groups);
+  void* stats = c.bytes(group_norm_scratch_bytes(items, rows_per, c.u->cfg.norm_num_groups));
   if (c.live()) c.run(group_norm(x1, C1, x2, C2, n.g, n.b, y, items, rows_per, c.u->cfg.norm_num_groups, eps, silu, stats, c.s));
   c.free(stats);
 }

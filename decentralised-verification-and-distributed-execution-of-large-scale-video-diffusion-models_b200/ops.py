@@ -209,7 +209,8 @@ def group_norm(x, gamma, beta, n_items, groups, eps, silu, x2=None):
     rows, C1 = x.shape
     C2 = x2.shape[1] if x2 is not None else 0
     y = torch.empty((rows, C1 + C2), dtype=torch.bfloat16, device=x.device)
-    stats = torch.empty(n_items * groups * 2, dtype=torch.float64, device=x.device)
+    stats = torch.empty(lib.b2v_op_group_norm_scratch_bytes(n_items, rows // n_items, groups) + 256, dtype=torch.uint8,
+                        device=x.device)
     check(lib.b2v_op_group_norm(ptr(x), C1, ptr(x2), C2, ptr(gamma), ptr(beta), ptr(y), n_items, rows // n_items,
                                 groups, float(eps), int(silu), ptr(stats), stream()))
     return y

@@ -1,0 +1,39 @@
+#!/usr/bin/env python3
+"""Drop-in for Distribution/strategies/fsdp.py (FSDP-only baseline): the full latent on every rank, no chunking,
+guidance hard-coded to 7.5 (fsdp.py:151), no --guidance_scale/--chunk_size/--overlap/--fps flags, legacy ``--out``.
+CLI parity only: the parameter sharding it benchmarks does not exist on replicated weights."""
+import argparse
+import logging
+
+from .common import WindowedDiffuser, add_common_args, run_cli
+
+
+class FSDPBenchmark(WindowedDiffuser):
+    variant = "coherent"
+    mode_name = "fsdp"
+
+    def __init__(self, cfg, **kw):
+        cfg.no_chunking, cfg.use_ctx, cfg.guidance_scale = True, False, 7.5
+        cfg.chunk_size, cfg.overlap, cfg.fps = 0, 0, 8
+        super().__init__(cfg, **kw)
+
+    run = WindowedDiffuser.__call__
+
+
+def parse_args(argv=None):
+    p = add_common_args(argparse.ArgumentParser(), num_frames=25, chunking=False)
+    p.add_argument("--out", default=None, help="legacy alias of --out_csv")
+    cfg = p.parse_args(argv)
+    if cfg.out:
+        cfg.out_csv = cfg.out
+    return cfg
+
+
+def main(argv=None):
+    logging.basicConfig(level=logging.INFO, format="%(asctime)s %(levelname)s: %(message)s")
+    cfg = parse_args(argv)
+    return run_cli(FSDPBenchmark, cfg, "fsdp")
+
+
+if __name__ == "__main__":
+    main()

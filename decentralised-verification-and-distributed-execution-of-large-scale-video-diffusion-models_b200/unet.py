@@ -116,8 +116,10 @@ class UNet3DConditionModel:
         if need == 0:
             raise _lib.B2VError("unsupported UNet shape B=%d F=%d H=%d W=%d: %s" % (B, F, H, W, _lib.last_error()))
         if self._ws is None or self._ws.numel() < need:
-            self._ws = None
-            self._ws = torch.empty(need, dtype=torch.uint8, device=self.device)
+            self._ws = self._ws_raw = None
+            self._ws_raw = torch.empty(need + 1024, dtype=torch.uint8, device=self.device)
+            off = (-self._ws_raw.data_ptr()) % 1024  # the C-ABI wants a 1 KiB aligned workspace
+            self._ws = self._ws_raw[off:off + need]
         return self._ws
 
     def forward_into(self, sample, timestep, encoder_hidden_states, out):

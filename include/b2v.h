@@ -195,10 +195,12 @@ int b2v_op_conv3x3(const void* x_dev, const void* w_dev, const float* bias_dev, 
 
 /* GroupNorm (+SiLU) over channels-last rows: stats per (batch item, group) over rows_per_item rows x
  * C/groups channels, then y = (x-mean)*rstd*gamma+beta (silu optional). x may be the channel concat of
- * two tensors (x2_dev != NULL, C = C1 + C2). stats_dev: >= n_items*groups*2 doubles. */
+ * two tensors (x2_dev != NULL, C = C1 + C2). scratch_dev: >= b2v_op_group_norm_scratch_bytes() bytes (per-CTA
+ * partial sums; the reduction uses no atomics, so results are bit-reproducible run to run). */
+size_t b2v_op_group_norm_scratch_bytes(int64_t n_items, int64_t rows_per_item, int groups);
 int b2v_op_group_norm(const void* x_dev, int C1, const void* x2_dev, int C2, const float* gamma_dev,
                       const float* beta_dev, void* y_dev, int64_t n_items, int64_t rows_per_item,
-                      int groups, float eps, int silu, void* stats_dev, void* stream);
+                      int groups, float eps, int silu, void* scratch_dev, void* stream);
 int b2v_op_layer_norm(const void* x_dev, const float* gamma_dev, const float* beta_dev, void* y_dev,
                       int64_t rows, int C, float eps, void* stream);
 

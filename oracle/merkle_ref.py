@@ -105,11 +105,14 @@ def spotcheck_indices(num_leaves, num_to_reveal, seed):
     return out
 
 
-def _frame0(buf, cfg):
-    x = torch.from_numpy(np.frombuffer(buf, dtype=np.float16))
+def _frame0(buf, cfg, shape_from=None):
+    """fp16 frame 0 of a leaf buffer. The reference derives the 5-D view from the z buffer and applies the same view
+    to eps (proof.py:330-343): pass shape_from=z_bytes for eps. A size mismatch raises, as `.view` does there."""
+    x = torch.from_numpy(np.frombuffer(bytearray(buf), dtype=np.float16))
     C, H, W = cfg["latent_channels"], cfg["latent_height"], cfg["latent_width"]
-    if x.numel() > C * H * W:
-        return x.view(1, C, x.numel() // (C * H * W), H, W)[0, :, 0]
+    n = x.numel() if shape_from is None else len(shape_from) // 2
+    if n > C * H * W:
+        return x.view(1, C, n // (C * H * W), H, W)[0, :, 0]
     return x.view(C, H, W)
 
 
@@ -117,7 +120,7 @@ def run_unet_step_scheduler(z_bytes, eps_bytes, config, step_i):
     if step_i >= len(config["alphas"]):
         return False
     try:
-        z, eps = _frame0(z_bytes, config), _frame0(eps_bytes, config)
+        z, eps = _frame0(z_bytes, config), _frame0(eps_bytes, config, z_bytes)
         s = DDIMSchedulerRef()
         s.set_timesteps(len(config["alphas"]))
         prev = s.step(eps, s.timesteps[step_i], z).prev_sample
@@ -130,7 +133,7 @@ def run_unet_step_fallback(z_bytes, eps_bytes, config, step_i):
     if step_i >= len(config["alphas"]):
         return False
     try:
-        z, eps = _frame0(z_bytes, config), _frame0(eps_bytes, config)
+        z, eps = _frame0(z_bytes, config), _frame0(eps_bytes, config, z_bytes)
         a = torch.tensor(config["alphas"][step_i], dtype=torch.float16)
         pred = (z - torch.sqrt(1.0 - a) * eps) / torch.sqrt(a)
         return bool(torch.isfinite(pred).all() and torch.abs(pred).max() < 10.0)
@@ -163,7 +166,7 @@ def temporal_coherence(spot_check_indices, leaves_result, timestep_to_step, proo
         if si is None or sj is None:
             return False
         try:
-            prev = s.step(_frame0(e_i, unet_config), s.timesteps[si], _frame0(z_i, unet_config)).prev_sample
+            prev = s.step(_frame0(e_i, unet_config, z_i), s.timesteps[si], _frame0(z_i, unet_config)).prev_sample
             if not torch.allclose(prev, _frame0(z_j, unet_config), rtol=1, atol=1):
                 return False
         except Exception:

@@ -91,7 +91,7 @@ def test_gemm_temporal_taps(cuda, B, F, HW, C):
     assert rel_l2(out, ref) < 4e-3, rel_l2(out, ref)
 
 
-@pytest.mark.parametrize("mode", [1, 0])
+@pytest.mark.parametrize("mode", [1, 0], ids=["explicit", "tmaim2col"])
 @pytest.mark.parametrize("N,H,W,Cin,Cout,stride", [(2, 16, 16, 64, 64, 1), (3, 20, 36, 128, 320, 1),
                                                    (2, 16, 24, 64, 128, 2), (1, 8, 8, 640, 1280, 1),
                                                    (2, 40, 72, 320, 320, 1), (2, 10, 18, 320, 320, 2)])

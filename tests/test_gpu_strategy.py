@@ -1,0 +1,194 @@
+"""-m gpu: denoising-loop glue kernels and the whole strategy path through the C-ABI vs the CPU oracle
+(oracle/strategy_ref.py, oracle/ddim_ref.py) on the same seeded inputs.
+  * CFG+DDIM fused step: within 1 ulp of the storage dtype of the fp32 evaluation (tolerance stated per assert)
+  * overlap blend: BIT-EXACT against the verbatim torch-CPU procedure (fp16 accumulator quirk, Q1/Q2)
+  * strategy end to end (config[0]-shaped: chunk_only, 2 segments, 8 frames, 4 DDIM steps, TINY-width UNet3D):
+    per-step latents within the Appendix-D tolerance of the fp32 oracle trajectory
+"""
+import argparse
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+
+def _ulp(dtype):
+    return {torch.float32: 2.0 ** -23, torch.float16: 2.0 ** -10, torch.bfloat16: 2.0 ** -7}[dtype]
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.float16, torch.bfloat16])
+@pytest.mark.parametrize("cfg,ctx,clip", [(True, False, False), (True, True, False), (False, False, True)])
+def test_cfg_ddim_step(cuda, dtype, cfg, ctx, clip):
+    from b2v import ops
+    from oracle.ddim_ref import pipeline_scheduler
+    g = torch.Generator().manual_seed(3)
+    C, F, h, w = 4, 5, 12, 20
+    lat = torch.randn(1, C, F, h, w, generator=g).to(dtype)
+    eps2 = torch.randn(2 if cfg else 1, C, F, h, w, generator=g).to(dtype)
+    cx = torch.randn(1, C, 1, h, w, generator=g).to(dtype) if ctx else None
+    s = pipeline_scheduler()
+    s.set_timesteps(4)
+    a_t, a_p = s.alpha_pair(501)
+    gs = 7.5 if cfg else None
+    leaf_z = torch.empty(lat.shape, dtype=torch.float16, device=cuda)
+    leaf_e = torch.empty(lat.shape, dtype=torch.float16, device=cuda)
+    out, xn = ops.cfg_ddim_step(lat.to(cuda), eps2.to(cuda), a_t, a_p, guidance_scale=gs,
+                                ctx=cx.to(cuda) if ctx else None, ctx_w=0.35, clip_sample=clip,
+                                make_next_input=2 if cfg else 1, leaf_z=leaf_z, leaf_eps=leaf_e)
+    lf, ef = lat.double(), eps2.double()
+    e = ef[:1] + 7.5 * (ef[1:] - ef[:1]) if cfg else ef
+    x0 = (lf - (1 - a_t) ** 0.5 * e) / a_t ** 0.5
+    if clip:
+        x0 = x0.clamp(-1, 1)
+    want = a_p ** 0.5 * x0 + (1 - a_p) ** 0.5 * e
+    tol = _ulp(dtype) * (want.abs() + 1.0) + 1e-6  # 1 ulp of the stored value (+1 absolute ulp near zero)
+    assert bool(((out.cpu().double() - want).abs() <= tol * (8 if cfg else 2)).all())
+    # next UNet input = stored lat' (+ 0.35 ctx), duplicated
+    nxt = out.cpu().float() + (0.35 * cx.float() if ctx else 0.0)
+    assert torch.allclose(xn[0].cpu().float(), nxt[0], atol=2 * _ulp(dtype) * float(nxt.abs().max()), rtol=0)
+    if cfg:
+        assert torch.equal(xn[0], xn[1])
+    assert torch.equal(leaf_z.cpu(), lat.float().half())
+    assert torch.allclose(leaf_e.cpu().float(), e.float(), atol=2.0 ** -10 * float(e.abs().max()) * 2, rtol=0)
+
+
+def test_scheduler_step_matches_oracle(cuda):
+    from b2v.scheduler import DDIMScheduler
+    from oracle.ddim_ref import pipeline_scheduler, default_scheduler
+    g = torch.Generator().manual_seed(5)
+    z, e = torch.randn(1, 4, 3, 8, 8, generator=g), torch.randn(1, 4, 3, 8, 8, generator=g)
+    for mine, ref in ((DDIMScheduler.from_pipeline_config(), pipeline_scheduler()), (DDIMScheduler(), default_scheduler())):
+        mine.set_timesteps(8, device="cuda")
+        ref.set_timesteps(8)
+        assert mine.host_timesteps() == [int(t) for t in ref.timesteps]
+        assert torch.equal(mine.alphas_cumprod, ref.alphas_cumprod)
+        for t in ref.timesteps[[0, 3, 7]]:
+            got = mine.step(e.to(cuda), t, z.to(cuda)).prev_sample.cpu()
+            want = ref.step(e, t, z).prev_sample
+            assert torch.allclose(got, want, atol=2e-6, rtol=2e-6)
+
+
+def test_context_mean(cuda):
+    from b2v import ops
+    from oracle.strategy_ref import context_mean
+    g = torch.Generator().manual_seed(1)
+    for dt in (torch.float32, torch.float16, torch.bfloat16):
+        base = torch.randn(1, 4, 24, 9, 16, generator=g).to(dt)
+        got = ops.context_mean(base.to(cuda)).cpu()
+        want = context_mean(base.float()).to(dt)  # fp32 accumulate, one rounding
+        assert torch.allclose(got.float(), want.float(), atol=_ulp(dt), rtol=_ulp(dt))
+
+
+PLANS = [(8, 2, 0, 4, False), (24, 1, 0, 4, False), (24, 4, 0, 4, False), (24, 4, 0, 4, True), (24, 8, 0, 4, False),
+         (96, 8, 0, 4, False), (24, 2, 16, 4, True), (25, 3, 7, 3, False), (8, 2, 6, 4, True)]
+
+
+@pytest.mark.parametrize("dtype", [torch.float16, torch.bfloat16, torch.float32])
+@pytest.mark.parametrize("T,world,cs,ov,coherent", PLANS)
+def test_blend_bit_exact(cuda, dtype, T, world, cs, ov, coherent):
+    from b2v import planner
+    from b2v.strategies.common import cuda_blend
+    from oracle import strategy_ref as S
+    p = planner.plan(T, world, cs, ov, variant="coherent" if coherent else "chunk_only")
+    g = torch.Generator().manual_seed(T * 10 + world)
+    base = torch.randn(1, 4, T, 6, 10, generator=g).to(dtype)
+    gathered, flat = [], []
+    for r in range(world):
+        mine = [(s, e, (torch.randn(1, 4, e - s, 6, 10, generator=g) * 3).to(dtype)) for s, e in p.of_rank(r)]
+        gathered.append(mine)
+        flat += mine
+    want, full, weight = S.blend(gathered, T, p.overlap, base)
+    got = cuda_blend([(s, e, t.to(cuda)) for s, e, t in flat], T, p.overlap).cpu()
+    assert got.dtype == torch.float32 and want.dtype == torch.float32
+    assert torch.equal(got, want), float((got - want).abs().max())
+    # reference quirk Q1: frames covered only by ramp-zero weights come out exactly 0
+    if p.overlap > 0:
+        assert float(got[:, :, 0].abs().max()) == 0.0 and float(got[:, :, T - 1].abs().max()) == 0.0
+
+
+def _tiny_setup(cuda, seed=1234):
+    from oracle import unet3d_ref as R
+    from b2v.unet import UNet3DConditionModel
+    from b2v.pipeline import VideoPipeline
+    from b2v.scheduler import DDIMScheduler
+    ref = R.random_init_(R.UNet3DConditionModel(R.TINY), seed=seed, round_bf16=True).eval()
+    net = UNet3DConditionModel(R.TINY.to_dict(), device=cuda).load_state_dict(ref.state_dict())
+    pipe = VideoPipeline(net, DDIMScheduler.from_pipeline_config(), text_dim=128, dtype=torch.float32)
+    return ref, pipe
+
+
+def _cfg(**kw):
+    d = dict(model_id="tiny", prompt="a rocket in space, 4k", num_frames=8, steps=4, guidance_scale=7.5, chunk_size=0,
+             overlap=4, fps=8, height=128, width=128, device="cuda", out_csv="/tmp/b2v_test.csv", emu_bw_mbps=0,
+             emu_rtt_ms=0, emu_jitter_ms=0, seed=1234, dtype="fp32")
+    d.update(kw)
+    return argparse.Namespace(**d)
+
+
+@pytest.mark.parametrize("coherent", [False, True])
+def test_strategy_single_process_vs_oracle(cuda, coherent):
+    """config[0] shape with the TINY-width UNet: world = 1 process plays both ranks' windows (plan for world=2 is
+    injected), every per-step latent is compared with the fp32 oracle trajectory."""
+    from b2v import planner
+    from b2v.strategies import chunk_only, fsdp_chunked_coherent
+    from b2v.strategies.common import CudaDenoiser, cuda_blend, base_noise
+    from oracle import strategy_ref as S
+    from oracle.ddim_ref import pipeline_scheduler
+    ref, pipe = _tiny_setup(cuda)
+    T, h, w, world = 8, 16, 16, 2
+    cfg = _cfg(use_ctx=coherent, context_weight=0.35, overlap=2 if coherent else 4, chunk_size=5 if coherent else 0)
+    base = base_noise(4, T, h, w, torch.float32, torch.device("cpu"))
+    g = torch.Generator().manual_seed(1)
+    cond, uncond = torch.randn(1, 77, 128, generator=g), torch.randn(1, 77, 128, generator=g)
+    sched_ref = pipeline_scheduler()
+    sched_ref.set_timesteps(4)
+    traj = {}
+    want = S.run_strategy(ref, sched_ref, base, uncond, cond, world, 7.5, cfg.chunk_size, cfg.overlap,
+                          coherent=coherent, record=lambda r, s, e, i, t, a, b, c: traj.__setitem__((s, e, i), c))
+    # product side
+    pipe.scheduler.set_timesteps(4, device="cuda")
+    p = planner.plan(T, world, cfg.chunk_size, cfg.overlap, variant="coherent" if coherent else "chunk_only")
+    assert p.ranges == want["ranges"] and p.overlap == want["ov"]
+    from b2v import ops
+    based = base.to(cuda)
+    ctx = ops.context_mean(based) if coherent else None
+    got_steps = {}
+    windows = []
+    for s, e in p.gather_order():
+        den = CudaDenoiser(pipe, uncond.to(cuda), cond.to(cuda), 7.5, ctx=ctx, context_weight=0.35 if coherent else 0.0)
+        lat = based[:, :, s:e].clone()
+        # step-by-step so each intermediate latent can be compared
+        x = ops.make_unet_input(lat, 2, ctx=ctx, ctx_w=den.ctx_w)
+        for i, t in enumerate(pipe.scheduler.host_timesteps()):
+            eps2 = pipe.unet(x, t, encoder_hidden_states=den.emb).sample
+            lat, x = pipe.scheduler.fused_cfg_step(lat, eps2, t, 7.5, ctx=ctx, ctx_w=den.ctx_w, n_dup=2)
+            got_steps[(s, e, i)] = lat.cpu()
+        windows.append((s, e, lat))
+    # per-step relative L2 (<= 1e-2 at step 4)
+    worst = 0.0
+    for k, v in traj.items():
+        rel = float((got_steps[k] - v).norm() / v.norm())
+        worst = max(worst, rel)
+    print("strategy coherent=%s worst per-step rel-l2 %.3e" % (coherent, worst))
+    assert worst <= 1e-2, worst
+    got = cuda_blend(windows, T, p.overlap).cpu()
+    rel = float((got - want["lat"]).norm() / want["lat"].norm())
+    assert rel <= 1e-2, rel
+    # the engine's own loop gives the same final window latents as the stepwise loop above
+    den = CudaDenoiser(pipe, uncond.to(cuda), cond.to(cuda), 7.5, ctx=ctx, context_weight=0.35 if coherent else 0.0)
+    s, e = p.ranges[0]
+    again = den(based[:, :, s:e].clone())
+    assert torch.equal(again.cpu(), got_steps[(s, e, 3)])
+
+
+def test_windowed_diffuser_world1(cuda, tmp_path):
+    from b2v.strategies.chunk_only import ChunkedVideoDiffuser
+    from b2v.strategies.common import run_cli, CSV_HEADER
+    ref, pipe = _tiny_setup(cuda)
+    cfg = _cfg(out_csv=str(tmp_path / "m.csv"))
+    d = ChunkedVideoDiffuser(cfg, pipe=pipe)
+    res = d()
+    assert res["world_size"] == 1 and res["num_frames"] == 8 and res["chunk_size"] == 8 and res["overlap"] == 2
+    assert d.latents.shape == (1, 4, 8, 16, 16) and bool(torch.isfinite(d.latents).all())
+    assert res["steps_per_s"] > 0

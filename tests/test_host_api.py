@@ -1,0 +1,144 @@
+"""not-gpu: the C-ABI library loads and exports every symbol include/b2v.h declares (no compute calls), the host-side
+mirror of the reference interface (names, flags, CSV schema, error behaviour), and that nothing silently falls back to
+the CPU when no GPU is present."""
+import ctypes
+import inspect
+import logging
+import os
+import re
+
+import pytest
+import torch
+
+import b2v
+from b2v import _lib, planner, proof
+from b2v.strategies import chunk_only, common, fsdp, fsdp_chunked, fsdp_chunked_coherent
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+NO_GPU = not torch.cuda.is_available()
+
+
+def header_symbols():
+    src = open(os.path.join(ROOT, "include", "b2v.h")).read()
+    src = re.sub(r"/\*.*?\*/", "", src, flags=re.S)
+    return sorted(set(re.findall(r"\b(b2v_[a-z0-9_]+)\s*\(", src)))
+
+
+def test_library_exports_every_declared_symbol():
+    lib = _lib.load()
+    syms = header_symbols()
+    assert len(syms) >= 29
+    raw = ctypes.CDLL(_lib.LIB_PATH)
+    for s in syms:
+        assert hasattr(raw, s), "libb2v.so does not export %s" % s
+    assert set(syms) == set(_lib.EXPORTED_SYMBOLS), set(syms) ^ set(_lib.EXPORTED_SYMBOLS)
+    assert lib.b2v_version() == 1
+    assert lib.b2v_merkle_depth(1) == 0 and lib.b2v_merkle_depth(5) == 3 and lib.b2v_merkle_depth(50) == 6
+    assert lib.b2v_merkle_scratch_bytes(5) >= (5 + 3 + 2 + 1) * 32
+
+
+def test_no_extern_c_signature_uses_torch_types():
+    src = re.sub(r"/\*.*?\*/", "", open(os.path.join(ROOT, "include", "b2v.h")).read(), flags=re.S)
+    assert "torch" not in src and "at::" not in src and "#include <cuda" not in src
+
+
+@pytest.mark.skipif(not NO_GPU, reason="checks the no-GPU failure mode")
+def test_compute_fails_loudly_without_gpu():
+    lib = _lib.load()
+    assert lib.b2v_device_check() == -3  # B2V_ERR_DEVICE
+    assert b"no CPU fallback" in lib.b2v_last_error() or b"no CUDA device" in lib.b2v_last_error()
+    from b2v.unet import UNet3DConditionModel
+    with pytest.raises(Exception):
+        UNet3DConditionModel(device="cuda")
+    with pytest.raises(b2v.B2VError):
+        UNet3DConditionModel(device="cpu")
+    # verify-side functions never raise: they log and return False (proof.py:302-304, 390-392)
+    assert proof.verify_merkle_leaf(b"\0" * 32, [b"\1" * 32], b"\2" * 32) is False
+    cfg = {"latent_channels": 4, "latent_height": 2, "latent_width": 2, "alphas": [0.5]}
+    assert proof.run_unet_step(b"\0" * 32, b"\0" * 32, cfg, 0) is False
+    with pytest.raises(b2v.B2VError):
+        proof.build_merkle_root([b"x"])
+
+
+def test_proof_host_functions():
+    assert proof.derive_seed(b"\x01" * 32, "5Fwallet") == 8605131804522081524
+    assert proof.commit_then_reveal_merkle_spotcheck(b"r", 50, 5, 1234) == [28, 29, 7, 8, 0, 1, 5, 6, 37, 38]
+    assert proof.commit_then_reveal_merkle_spotcheck(b"r", 1, 3, 1) == [0]
+    assert proof.commit_then_reveal_merkle_spotcheck(b"r", 0, 3, 1) == []
+    assert proof.build_merkle_root([]) == (b"", [])
+    msg = proof.signed_message(b"C" * 32, 7, b"video", b"R" * 32)
+    assert msg[:32] == b"C" * 32 and msg[32:40] == (7).to_bytes(8, "little") and len(msg) == 32 + 8 + 32 + 32
+    # signature check is a host callback; without bittensor it logs and returns False, with a hook it is used
+    assert proof.verify_proof_signature("5F", b"c", 1, b"v", b"r", b"s") is False
+    assert proof.verify_proof_signature("5F", b"c", 1, b"v", b"r", b"s", signature_verifier=lambda h, m, s: s == b"s") is True
+    assert proof.verify_temporal_coherence_spot_check([5], {}, {}, [0.5], {}) is True  # < 2 timesteps -> skip
+
+
+def test_proof_signatures_mirror_reference():
+    want = {"derive_seed": ["challenge", "wallet_address"],
+            "build_merkle_root": ["leaves"],
+            "verify_merkle_leaf": ["leaf_hash", "proof_path", "root"],
+            "run_unet_step": ["z_bytes", "eps_bytes", "config", "step_i"],
+            "commit_then_reveal_merkle_spotcheck": ["merkle_root", "num_leaves", "num_to_reveal", "random_seed"],
+            "verify_temporal_coherence_spot_check": ["spot_check_indices", "leaves_result", "timestep_to_step",
+                                                     "proof_alphas", "unet_config", "request_id", "logger"],
+            "verify_proof_signature": ["miner_hotkey_ss58", "challenge", "seed", "video_bytes", "merkle_root", "signature"],
+            "verify_proof_of_inference": ["miner_hotkey_ss58", "video_bytes", "proof", "config_for_unet"]}
+    for name, params in want.items():
+        got = list(inspect.signature(getattr(proof, name)).parameters)
+        assert got[:len(params)] == params, name
+
+
+def test_cli_flags_and_defaults():
+    c = chunk_only.parse_args([])
+    assert (c.model_id, c.num_frames, c.steps, c.guidance_scale, c.chunk_size, c.overlap, c.fps, c.height, c.width,
+            c.device, c.out_csv, c.emu_bw_mbps, c.emu_rtt_ms, c.emu_jitter_ms) == \
+        ("cerspense/zeroscope_v2_XL", 32, 50, 7.5, 0, 4, 8, 576, 1024, "cuda", "benchmarks.csv", 0, 0, 0)
+    h = fsdp_chunked_coherent.parse_args([])
+    assert (h.mode, h.context_weight, h.out_csv, h.use_ctx, h.no_chunking, h.use_fsdp) == \
+        ("hybrid_ctx", 0.35, "results.csv", True, False, True)
+    assert fsdp_chunked_coherent.parse_args(["--mode", "fsdp"]).no_chunking is True
+    assert fsdp_chunked_coherent.parse_args(["--mode", "chunk"]).use_fsdp is False
+    with pytest.raises(SystemExit):
+        fsdp_chunked_coherent.parse_args(["--mode", "bogus"])
+    s = fsdp_chunked.parse_args([])
+    assert (s.num_frames, s.mode, s.context_weight) == (25, "split", 0.35)
+    f = fsdp.parse_args(["--out", "legacy.csv"])
+    assert f.num_frames == 25 and f.out_csv == "legacy.csv" and not hasattr(f, "guidance_scale")
+    with pytest.raises(SystemExit):
+        fsdp.parse_args(["--overlap", "2"])
+    # the experiment driver's command line (full_experiments_ZeroscopeXL.sh:25) parses
+    chunk_only.parse_args("--emu_bw_mbps 500 --emu_rtt_ms 3.01 --emu_jitter_ms 3.53 --model_id cerspense/zeroscope_v2_XL "
+                          "--out_csv ZeroscopeXL/wifi_results.csv".split())
+
+
+def test_csv_schema(tmp_path):
+    assert common.CSV_HEADER == ["timestamp", "host", "mode", "world_size", "num_frames", "chunk_size", "overlap",
+                                 "latency_s", "throughput_fps", "peak_vram_mb", "end_vram_mb", "network_bytes",
+                                 "net_gather_s", "net_reduce_s", "temp_instab", "flow_err"]
+    p = str(tmp_path / "r.csv")
+    row = {"world_size": 2, "chunk_size": 5, "overlap": 1, "num_frames": 8, "denoise_s": 1.0, "extra": 9}
+    common.finish_row(row, "chunk", 8, __import__("time").time() - 2.0)
+    common.append_csv(p, row)
+    common.append_csv(p, row)
+    lines = open(p).read().strip().split("\n")
+    assert lines[0].split(",") == common.CSV_HEADER and len(lines) == 3
+    assert "extra" not in lines[0] and lines[1].split(",")[2] == "chunk"
+
+
+def test_planner_errors_instead_of_hanging():
+    with pytest.raises(planner.PlanError):
+        planner.plan(24, 8, variant="coherent")      # reference: infinite loop
+    assert planner.plan(24, 8, 4, 1, variant="coherent").ranges == planner.plan(24, 8).ranges
+    assert planner.plan(24, 2, variant="coherent", no_chunking=True).ranges == [(0, 24), (0, 24)]
+
+
+def test_pipeline_host_pieces():
+    from b2v.pipeline import SyntheticTokenizer, parameter_shapes, ZEROSCOPE_CONFIG
+    shapes = parameter_shapes(ZEROSCOPE_CONFIG)
+    assert sum(torch.Size(s).numel() for s in shapes.values()) == 1411233860      # Zeroscope's 1.41 B
+    assert shapes["down_blocks.0.attentions.0.transformer_blocks.0.attn2.to_k.weight"] == (320, 1024)
+    assert shapes["up_blocks.1.resnets.2.conv1.weight"] == (1280, 1920, 3, 3)
+    assert shapes["transformer_in.proj_in.weight"] == (512, 320)
+    t = SyntheticTokenizer()(["a rocket", ""])
+    assert t.input_ids.shape == (2, 77) and t.input_ids.dtype == torch.int64
