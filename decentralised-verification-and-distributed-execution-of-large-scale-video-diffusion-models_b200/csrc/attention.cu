@@ -24,14 +24,19 @@ __device__ __forceinline__ float ex2(float x) {
 }
 
 // ------------------------------------------------------------------------------------------------
-// flash attention, head_dim 64, q tile 128, kv tile 128, 2 CTAs / SM
+// flash attention, head_dim 64, q tile 128, kv tile 128, 2 CTAs / SM (the co-resident CTA's MMAs run under this
+// CTA's softmax and vice versa)
 //   warp 0: TMA producer   warp 1: MMA issuer   warps 2-5: softmax (thread = query row)
-// smem: Q 16K | K 2x16K | V 2x16K | P 32K   TMEM: S cols [0,128)  O_blk cols [128,192)
+// smem: Q 16K | K 2x16K | V 2x16K | P 32K      TMEM: S cols [0,128)   O cols [128,192) (accumulates over kv tiles)
+// Softmax is single pass: the S row (128 fp32) is held in registers; the exponent uses a *stale* running maximum
+// that is only refreshed (and O rescaled in TMEM) when the true maximum has moved by more than 2^8 — the final
+// O / l is exact either way, and O never round-trips through registers in the steady state.
 // ------------------------------------------------------------------------------------------------
 constexpr int AT_THREADS = 192;
 constexpr int AT_TILE = 16384;  // 128 rows x 64 bf16
-constexpr int AT_SMEM = AT_TILE * (1 + 2 + 2 + 2) + 128 + 1024;
+constexpr int AT_SMEM = AT_TILE * (1 + 2 + 2 + 2) + 128;  // 2 CTAs/SM: 2 x (this + 1 KiB system) <= 227 KiB
 constexpr int AT_TMEM_COLS = 256;
+constexpr float AT_RESCALE_LOG2 = 8.0f;
 
 struct AttnParams {
   __nv_bfloat16* out;
@@ -43,8 +48,7 @@ struct AttnParams {
 __global__ void __launch_bounds__(AT_THREADS, 2)
 attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
             const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
-  extern __shared__ uint8_t smem_raw[];
-  uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
+  extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sQ = smem;
   uint8_t* sK = smem + AT_TILE;
   uint8_t* sV = smem + 3 * AT_TILE;
@@ -60,6 +64,10 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
   const int nkv = p.nkv;
 
   if (warp == 0 && lane == 0) {
+    if (smem_u32(smem) & 1023u) {  // the 128B-swizzled tiles need a 1 KiB aligned base (no slack bytes are reserved)
+      printf("b2v: attention shared memory base is not 1 KiB aligned\n");
+      __trap();
+    }
     prefetch_tmap(&tmQ); prefetch_tmap(&tmK); prefetch_tmap(&tmV);
     mbar_init(q_full, 1);
     for (int i = 0; i < 2; ++i) { mbar_init(k_full0 + 8 * i, 1); mbar_init(v_full0 + 8 * i, 1); mbar_init(kv_empty0 + 8 * i, 1); }
@@ -108,7 +116,7 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     issue_qk(0);
     for (int j = 0; j < nkv; ++j) {
       const int st = j & 1;
-      mbar_wait(p_full, j & 1);
+      mbar_wait(p_full, j & 1);   // P(j) is in smem, S(j) has been consumed, O has been rescaled if it had to be
       mbar_wait(v_full0 + 8 * st, (j >> 1) & 1);
       tc_fence_after();
       if (elect_one()) {
@@ -117,7 +125,7 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
           // A = P: two 64-wide K blocks of 16 KiB; B = V: 16 kv rows (2 KiB) per k-step, MN-major
           const uint64_t a = umma_desc_sw128(smem_u32(sP + (k >> 2) * AT_TILE)) + 2 * (k & 3);
           const uint64_t bd = umma_desc_sw128(smem_u32(sV + st * AT_TILE + k * 2048));
-          umma_bf16_ss(tO, a, bd, idesc_pv, k != 0);
+          umma_bf16_ss(tO, a, bd, idesc_pv, (j | k) != 0);
         }
         umma_commit(o_full);
         umma_commit(kv_empty0 + 8 * st);
@@ -129,84 +137,99 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
-    float m = -INFINITY, l = 0.f;
-    float o[64];
-#pragma unroll
-    for (int i = 0; i < 64; ++i) o[i] = 0.f;
     const float sl2 = p.scale_log2;
+    float m_used = -INFINITY;  // maximum the exponents are taken against (raw score units)
+    float l = 0.f;
     uint8_t* prow = sP + row * 128;
     const int sw = row & 7;
     for (int j = 0; j < nkv; ++j) {
       mbar_wait(s_full, j & 1);
       tc_fence_after();
+      uint32_t sv[128];
+      tmem_ld32(tS + lane_off, sv);
+      tmem_ld32(tS + lane_off + 32, sv + 32);
+      tmem_ld32(tS + lane_off + 64, sv + 64);
+      tmem_ld32(tS + lane_off + 96, sv + 96);
+      tmem_wait_ld();
       const int kv_left = p.Skv - j * 128;  // valid kv columns in this block
-      float mx = -INFINITY;
-#pragma unroll 1
-      for (int c = 0; c < 128; c += 32) {
-        uint32_t v[32];
-        tmem_ld32(tS + lane_off + c, v);
-        tmem_wait_ld();
+      if (kv_left < 128) {
 #pragma unroll
-        for (int i = 0; i < 32; ++i)
-          if (c + i < kv_left) mx = fmaxf(mx, __uint_as_float(v[i]));
+        for (int i = 0; i < 128; ++i)
+          if (i >= kv_left) sv[i] = 0xff800000u;  // -inf: exp2 -> 0, never the maximum
       }
-      const float m_new = fmaxf(m, mx);
-      const float alpha = ex2((m - m_new) * sl2);  // m = -inf -> 0
-      const float mb = m_new * sl2;
-      float sum = 0.f;
-#pragma unroll 1
-      for (int c = 0; c < 128; c += 32) {
-        uint32_t v[32];
-        tmem_ld32(tS + lane_off + c, v);
-        tmem_wait_ld();
-        float pr[32];
+      float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-        for (int i = 0; i < 32; ++i) {
-          const float e = (c + i < kv_left) ? ex2(__uint_as_float(v[i]) * sl2 - mb) : 0.f;
-          pr[i] = e;
-          sum += e;
-        }
-        // 4 x 16-byte chunks of the row (8 bf16 each) into the 128B-swizzled K-major P tile
-        uint8_t* blk = prow + (c >> 6) * AT_TILE;
+      for (int i = 0; i < 128; i += 4) {
+        mx0 = fmaxf(mx0, __uint_as_float(sv[i]));
+        mx1 = fmaxf(mx1, __uint_as_float(sv[i + 1]));
+        mx2 = fmaxf(mx2, __uint_as_float(sv[i + 2]));
+        mx3 = fmaxf(mx3, __uint_as_float(sv[i + 3]));
+      }
+      const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
+      // refresh the reference maximum only when it is stale by more than 2^AT_RESCALE_LOG2 (always on the first tile)
+      const bool stale = (mx - m_used) * sl2 > AT_RESCALE_LOG2;
+      float alpha = 1.0f;
+      if (stale) {
+        alpha = ex2((m_used - mx) * sl2);  // m_used = -inf -> 0
+        m_used = mx;
+      }
+      const float mb = m_used * sl2;
+      float sum0 = 0.f, sum1 = 0.f;
+      uint32_t pk[64];
 #pragma unroll
-        for (int q = 0; q < 4; ++q) {
-          uint4 u;
-          u.x = pack_bf16x2(pr[8 * q], pr[8 * q + 1]);
-          u.y = pack_bf16x2(pr[8 * q + 2], pr[8 * q + 3]);
-          u.z = pack_bf16x2(pr[8 * q + 4], pr[8 * q + 5]);
-          u.w = pack_bf16x2(pr[8 * q + 6], pr[8 * q + 7]);
-          const int chunk = ((c & 63) >> 3) + q;
-          *reinterpret_cast<uint4*>(blk + ((chunk ^ sw) << 4)) = u;
+      for (int i = 0; i < 64; ++i) {
+        const float e0 = ex2(fmaf(__uint_as_float(sv[2 * i]), sl2, -mb));
+        const float e1 = ex2(fmaf(__uint_as_float(sv[2 * i + 1]), sl2, -mb));
+        sum0 += e0;
+        sum1 += e1;
+        pk[i] = pack_bf16x2(e0, e1);
+      }
+      l = l * alpha + (sum0 + sum1);
+      if (j > 0) {
+        mbar_wait(o_full, (j - 1) & 1);  // PV(j-1) retired: sP may be overwritten, O may be touched
+        tc_fence_after();
+        if (__any_sync(0xffffffffu, stale)) {
+          // rescale this row of the O accumulator in TMEM (rare after the first few kv tiles)
+#pragma unroll
+          for (int c = 0; c < 64; c += 32) {
+            uint32_t ov[32];
+            tmem_ld32(tO + lane_off + c, ov);
+            tmem_wait_ld();
+#pragma unroll
+            for (int i = 0; i < 32; ++i) ov[i] = __float_as_uint(__uint_as_float(ov[i]) * alpha);
+            tmem_st16(tO + lane_off + c, ov);
+            tmem_st16(tO + lane_off + c + 16, ov + 16);
+          }
+          tmem_wait_st();
         }
+      }
+      // 16 x 16-byte chunks of the row (8 bf16 each) into the two 128B-swizzled K-major P tiles
+#pragma unroll
+      for (int q = 0; q < 16; ++q) {
+        const uint4 u = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
+        *reinterpret_cast<uint4*>(prow + (q >> 3) * AT_TILE + (((q & 7) ^ sw) << 4)) = u;
       }
       fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(p_full);
-      l = l * alpha + sum;
-      m = m_new;
-      mbar_wait(o_full, j & 1);
-      tc_fence_after();
-#pragma unroll
-      for (int c = 0; c < 64; c += 32) {
-        uint32_t v[32];
-        tmem_ld32(tO + lane_off + c, v);
-        tmem_wait_ld();
-#pragma unroll
-        for (int i = 0; i < 32; ++i) o[c + i] = o[c + i] * alpha + __uint_as_float(v[i]);
-      }
-      tc_fence_before();
     }
+    mbar_wait(o_full, (nkv - 1) & 1);
+    tc_fence_after();
+    const float inv = 1.0f / l;
+    uint32_t ov[64];
+    tmem_ld32(tO + lane_off, ov);
+    tmem_ld32(tO + lane_off + 32, ov + 32);
+    tmem_wait_ld();
     if (q0 + row < p.Sq) {
-      const float inv = 1.0f / l;
       uint4* dst = reinterpret_cast<uint4*>(p.out + ((int64_t)b * p.Sq + q0 + row) * p.ldo + h * 64);
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
         uint4 u;
-        u.x = pack_bf16x2(o[8 * q] * inv, o[8 * q + 1] * inv);
-        u.y = pack_bf16x2(o[8 * q + 2] * inv, o[8 * q + 3] * inv);
-        u.z = pack_bf16x2(o[8 * q + 4] * inv, o[8 * q + 5] * inv);
-        u.w = pack_bf16x2(o[8 * q + 6] * inv, o[8 * q + 7] * inv);
+        u.x = pack_bf16x2(__uint_as_float(ov[8 * q]) * inv, __uint_as_float(ov[8 * q + 1]) * inv);
+        u.y = pack_bf16x2(__uint_as_float(ov[8 * q + 2]) * inv, __uint_as_float(ov[8 * q + 3]) * inv);
+        u.z = pack_bf16x2(__uint_as_float(ov[8 * q + 4]) * inv, __uint_as_float(ov[8 * q + 5]) * inv);
+        u.w = pack_bf16x2(__uint_as_float(ov[8 * q + 6]) * inv, __uint_as_float(ov[8 * q + 7]) * inv);
         dst[q] = u;
       }
     }
@@ -218,93 +241,155 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
 }
 
 // ------------------------------------------------------------------------------------------------
-// temporal attention: one warp per (batch, pixel, head); lane f = query frame f
+// temporal attention: sequence = frames (F <= 32), head_dim 64, batch = B*h*w*heads. HBM-bound (0.2 % of the FLOPs):
+// one warp per (batch, pixel, head) item, mma.sync m16n8k16 straight on registers loaded from global memory
+// (tcgen05 needs M >= 64 per CTA tile and shared-memory operands: wrong shape for 16x16x64 problems).
+// No shared memory, no permute copies: frame f of a pixel is row0 + f*HW of the [B,F,H,W,C] activation.
+// The contraction index of an MMA may be permuted freely as long as A and B agree, so every lane loads whole
+// 16/32-byte pieces of a row:
+//   S = Q K^T : lane (g, tg) holds d in [16 tg, 16 tg + 16) of frames g / g+8 (Q) and of kv frames 8 nt + g (K)
+//   O = P V   : P is the S accumulator re-packed (FA2 register trick); lane (g, tg) holds d in [8 g, 8 g + 8) of
+//               kv frames 2 tg, 2 tg + 1, 2 tg + 8, 2 tg + 9 (V), byte-permuted into (frame, frame+1) pairs
 // ------------------------------------------------------------------------------------------------
-constexpr int TA_WARPS = 4;
+__device__ __forceinline__ void mma_bf16_16816(float* d, const uint32_t* a, uint32_t b0, uint32_t b1) {
+  asm volatile(
+      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+}
 
+constexpr int TA_WARPS = 8;
+
+template <int FT>  // number of 16-frame tiles: F <= 16 * FT
 __global__ void __launch_bounds__(TA_WARPS * 32)
 temporal_attn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int q_off, int k_off, int v_off,
                      __nv_bfloat16* __restrict__ out, int64_t ldo, int B, int F, int64_t HW, int heads,
                      float scale_log2) {
-  __shared__ __align__(16) __nv_bfloat16 sK[TA_WARPS][32][64];
-  __shared__ __align__(16) __nv_bfloat16 sV[TA_WARPS][32][64];
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int g = lane >> 2, tg = lane & 3;
   const int64_t total = (int64_t)B * HW * heads;
+  const uint4 zero4 = make_uint4(0, 0, 0, 0);
   for (int64_t item = (int64_t)blockIdx.x * TA_WARPS + warp; item < total; item += (int64_t)gridDim.x * TA_WARPS) {
     const int h = (int)(item % heads);
     const int64_t bp = item / heads;
     const int64_t pix = bp % HW;
     const int b = (int)(bp / HW);
-    const int64_t row0 = (int64_t)b * F * HW + pix;  // frame f -> row0 + f*HW
-    __syncwarp();
-    // cooperative K/V load: 8 lanes x 16 B per frame row, 4 frames per pass
-    for (int f = lane >> 3; f < F; f += 4) {
-      const __nv_bfloat16* src = qkv + (row0 + (int64_t)f * HW) * ld + h * 64 + (lane & 7) * 8;
-      *reinterpret_cast<uint4*>(&sK[warp][f][(lane & 7) * 8]) = __ldg(reinterpret_cast<const uint4*>(src + k_off));
-      *reinterpret_cast<uint4*>(&sV[warp][f][(lane & 7) * 8]) = __ldg(reinterpret_cast<const uint4*>(src + v_off));
+    const __nv_bfloat16* base = qkv + ((int64_t)b * F * HW + pix) * ld + h * 64;  // frame f at base + f*HW*ld
+    const int64_t fstride = HW * ld;
+    // ---- K: kv frames 8 nt + g, d in [16 tg, 16 tg + 16) ; V: kv frames 16 ks + {2tg, 2tg+1, 2tg+8, 2tg+9}, d in [8g, 8g+8)
+    uint32_t kr[2 * FT][8];
+    uint4 vr[FT][4];
+#pragma unroll
+    for (int nt = 0; nt < 2 * FT; ++nt) {
+      const int f = nt * 8 + g;
+      uint4 u0 = zero4, u1 = zero4;
+      if (f < F) {
+        const uint4* p = reinterpret_cast<const uint4*>(base + f * fstride + k_off + tg * 16);
+        u0 = __ldg(p);
+        u1 = __ldg(p + 1);
+      }
+      kr[nt][0] = u0.x; kr[nt][1] = u0.y; kr[nt][2] = u0.z; kr[nt][3] = u0.w;
+      kr[nt][4] = u1.x; kr[nt][5] = u1.y; kr[nt][6] = u1.z; kr[nt][7] = u1.w;
     }
-    __syncwarp();
-    if (lane < F) {
-      float q[64];
-      const uint4* qs = reinterpret_cast<const uint4*>(qkv + (row0 + (int64_t)lane * HW) * ld + q_off + h * 64);
 #pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        const uint4 u = __ldg(qs + i);
-        const float2 a = unpack_bf16x2(u.x), bb = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
-        q[8 * i] = a.x; q[8 * i + 1] = a.y; q[8 * i + 2] = bb.x; q[8 * i + 3] = bb.y;
-        q[8 * i + 4] = c.x; q[8 * i + 5] = c.y; q[8 * i + 6] = d.x; q[8 * i + 7] = d.y;
+    for (int ks = 0; ks < FT; ++ks) {
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int f = ks * 16 + tg * 2 + (r & 1) + (r >> 1) * 8;
+        vr[ks][r] = f < F ? __ldg(reinterpret_cast<const uint4*>(base + f * fstride + v_off + g * 8)) : zero4;
       }
-      float sc[32];
-      float mx = -INFINITY;
+    }
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        sc[j] = -INFINITY;
-        if (j < F) {
-          const uint4* kr = reinterpret_cast<const uint4*>(&sK[warp][j][0]);
-          float acc = 0.f;
+    for (int mt = 0; mt < FT; ++mt) {
+      if (mt * 16 >= F) break;
+      // ---- Q rows: frames 16 mt + g and + 8
+      uint32_t q0[8], q1[8];
+      {
+        const int f0 = mt * 16 + g, f1 = f0 + 8;
+        uint4 a0 = zero4, a1 = zero4, c0 = zero4, c1 = zero4;
+        if (f0 < F) {
+          const uint4* p = reinterpret_cast<const uint4*>(base + f0 * fstride + q_off + tg * 16);
+          a0 = __ldg(p); a1 = __ldg(p + 1);
+        }
+        if (f1 < F) {
+          const uint4* p = reinterpret_cast<const uint4*>(base + f1 * fstride + q_off + tg * 16);
+          c0 = __ldg(p); c1 = __ldg(p + 1);
+        }
+        q0[0] = a0.x; q0[1] = a0.y; q0[2] = a0.z; q0[3] = a0.w; q0[4] = a1.x; q0[5] = a1.y; q0[6] = a1.z; q0[7] = a1.w;
+        q1[0] = c0.x; q1[1] = c0.y; q1[2] = c0.z; q1[3] = c0.w; q1[4] = c1.x; q1[5] = c1.y; q1[6] = c1.z; q1[7] = c1.w;
+      }
+      // ---- S = Q K^T
+      float sacc[2 * FT][4];
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const uint4 u = kr[i];
-            const float2 a = unpack_bf16x2(u.x), bb = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
-            acc += q[8 * i] * a.x + q[8 * i + 1] * a.y + q[8 * i + 2] * bb.x + q[8 * i + 3] * bb.y +
-                   q[8 * i + 4] * c.x + q[8 * i + 5] * c.y + q[8 * i + 6] * d.x + q[8 * i + 7] * d.y;
-          }
-          sc[j] = acc;
-          mx = fmaxf(mx, acc);
+      for (int nt = 0; nt < 2 * FT; ++nt) {
+        sacc[nt][0] = sacc[nt][1] = sacc[nt][2] = sacc[nt][3] = 0.f;
+#pragma unroll
+        for (int s = 0; s < 4; ++s) {
+          const uint32_t a[4] = {q0[2 * s], q1[2 * s], q0[2 * s + 1], q1[2 * s + 1]};
+          mma_bf16_16816(sacc[nt], a, kr[nt][2 * s], kr[nt][2 * s + 1]);
         }
       }
-      float sum = 0.f;
+      // ---- softmax over kv frames (row g: [0],[1]; row g+8: [2],[3]); columns nt*8 + 2 tg + {0,1}
+      float m0 = -INFINITY, m1 = -INFINITY;
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const float e = (j < F) ? ex2((sc[j] - mx) * scale_log2) : 0.f;
-        sc[j] = e;
-        sum += e;
+      for (int nt = 0; nt < 2 * FT; ++nt) {
+        const int c = nt * 8 + tg * 2;
+        if (c >= F) { sacc[nt][0] = -INFINITY; sacc[nt][2] = -INFINITY; }
+        if (c + 1 >= F) { sacc[nt][1] = -INFINITY; sacc[nt][3] = -INFINITY; }
+        m0 = fmaxf(m0, fmaxf(sacc[nt][0], sacc[nt][1]));
+        m1 = fmaxf(m1, fmaxf(sacc[nt][2], sacc[nt][3]));
       }
-      const float inv = 1.0f / sum;
-      float o[64];
+      m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 1)); m0 = fmaxf(m0, __shfl_xor_sync(0xffffffffu, m0, 2));
+      m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 1)); m1 = fmaxf(m1, __shfl_xor_sync(0xffffffffu, m1, 2));
+      float l0 = 0.f, l1 = 0.f;
 #pragma unroll
-      for (int i = 0; i < 64; ++i) o[i] = 0.f;
+      for (int nt = 0; nt < 2 * FT; ++nt) {
+        sacc[nt][0] = ex2((sacc[nt][0] - m0) * scale_log2); sacc[nt][1] = ex2((sacc[nt][1] - m0) * scale_log2);
+        sacc[nt][2] = ex2((sacc[nt][2] - m1) * scale_log2); sacc[nt][3] = ex2((sacc[nt][3] - m1) * scale_log2);
+        l0 += sacc[nt][0] + sacc[nt][1];
+        l1 += sacc[nt][2] + sacc[nt][3];
+      }
+      l0 += __shfl_xor_sync(0xffffffffu, l0, 1); l0 += __shfl_xor_sync(0xffffffffu, l0, 2);
+      l1 += __shfl_xor_sync(0xffffffffu, l1, 1); l1 += __shfl_xor_sync(0xffffffffu, l1, 2);
+      const float i0 = 1.0f / l0, i1 = 1.0f / l1;
+      // ---- O = P V
+      float oacc[8][4];
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        if (j < F) {
-          const float pj = sc[j] * inv;
-          const uint4* vr = reinterpret_cast<const uint4*>(&sV[warp][j][0]);
+      for (int nt = 0; nt < 8; ++nt) oacc[nt][0] = oacc[nt][1] = oacc[nt][2] = oacc[nt][3] = 0.f;
 #pragma unroll
-          for (int i = 0; i < 8; ++i) {
-            const uint4 u = vr[i];
-            const float2 a = unpack_bf16x2(u.x), bb = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
-            o[8 * i] += pj * a.x; o[8 * i + 1] += pj * a.y; o[8 * i + 2] += pj * bb.x; o[8 * i + 3] += pj * bb.y;
-            o[8 * i + 4] += pj * c.x; o[8 * i + 5] += pj * c.y; o[8 * i + 6] += pj * d.x; o[8 * i + 7] += pj * d.y;
-          }
+      for (int ks = 0; ks < FT; ++ks) {
+        const uint32_t a[4] = {pack_bf16x2(sacc[2 * ks][0] * i0, sacc[2 * ks][1] * i0),
+                               pack_bf16x2(sacc[2 * ks][2] * i1, sacc[2 * ks][3] * i1),
+                               pack_bf16x2(sacc[2 * ks + 1][0] * i0, sacc[2 * ks + 1][1] * i0),
+                               pack_bf16x2(sacc[2 * ks + 1][2] * i1, sacc[2 * ks + 1][3] * i1)};
+        const uint32_t v0[4] = {vr[ks][0].x, vr[ks][0].y, vr[ks][0].z, vr[ks][0].w};
+        const uint32_t v1[4] = {vr[ks][1].x, vr[ks][1].y, vr[ks][1].z, vr[ks][1].w};
+        const uint32_t v2[4] = {vr[ks][2].x, vr[ks][2].y, vr[ks][2].z, vr[ks][2].w};
+        const uint32_t v3[4] = {vr[ks][3].x, vr[ks][3].y, vr[ks][3].z, vr[ks][3].w};
+#pragma unroll
+        for (int nt = 0; nt < 8; ++nt) {
+          const uint32_t sel = (nt & 1) ? 0x7632u : 0x5410u;  // (frame, frame+1) pair of element nt
+          const uint32_t b0 = __byte_perm(v0[nt >> 1], v1[nt >> 1], sel);
+          const uint32_t b1 = __byte_perm(v2[nt >> 1], v3[nt >> 1], sel);
+          mma_bf16_16816(oacc[nt], a, b0, b1);
         }
       }
-      uint4* dst = reinterpret_cast<uint4*>(out + (row0 + (int64_t)lane * HW) * ldo + h * 64);
-#pragma unroll
-      for (int i = 0; i < 8; ++i) {
-        uint4 u;
-        u.x = pack_bf16x2(o[8 * i], o[8 * i + 1]); u.y = pack_bf16x2(o[8 * i + 2], o[8 * i + 3]);
-        u.z = pack_bf16x2(o[8 * i + 4], o[8 * i + 5]); u.w = pack_bf16x2(o[8 * i + 6], o[8 * i + 7]);
-        dst[i] = u;
+      // ---- store: row g holds d = 16 tg + nt ([0]) and 16 tg + 8 + nt ([1]); row g+8: [2], [3]
+      const int f0 = mt * 16 + g, f1 = f0 + 8;
+      const int64_t orow = ((int64_t)b * F * HW + pix) * ldo + h * 64 + tg * 16;
+      if (f0 < F) {
+        uint4* dst = reinterpret_cast<uint4*>(out + orow + f0 * HW * ldo);
+        dst[0] = make_uint4(pack_bf16x2(oacc[0][0], oacc[1][0]), pack_bf16x2(oacc[2][0], oacc[3][0]),
+                            pack_bf16x2(oacc[4][0], oacc[5][0]), pack_bf16x2(oacc[6][0], oacc[7][0]));
+        dst[1] = make_uint4(pack_bf16x2(oacc[0][1], oacc[1][1]), pack_bf16x2(oacc[2][1], oacc[3][1]),
+                            pack_bf16x2(oacc[4][1], oacc[5][1]), pack_bf16x2(oacc[6][1], oacc[7][1]));
+      }
+      if (f1 < F) {
+        uint4* dst = reinterpret_cast<uint4*>(out + orow + f1 * HW * ldo);
+        dst[0] = make_uint4(pack_bf16x2(oacc[0][2], oacc[1][2]), pack_bf16x2(oacc[2][2], oacc[3][2]),
+                            pack_bf16x2(oacc[4][2], oacc[5][2]), pack_bf16x2(oacc[6][2], oacc[7][2]));
+        dst[1] = make_uint4(pack_bf16x2(oacc[0][3], oacc[1][3]), pack_bf16x2(oacc[2][3], oacc[3][3]),
+                            pack_bf16x2(oacc[4][3], oacc[5][3]), pack_bf16x2(oacc[6][3], oacc[7][3]));
       }
     }
   }
@@ -360,9 +445,15 @@ int temporal_attention(const void* qkv, int64_t ld, int q_off, int k_off, int v_
   int64_t grid = (total + TA_WARPS - 1) / TA_WARPS;
   const int64_t cap = (int64_t)sm_count() * 8;
   if (grid > cap) grid = cap;
-  temporal_attn_kernel<<<(unsigned)grid, TA_WARPS * 32, 0, s>>>((const __nv_bfloat16*)qkv, ld, q_off, k_off, v_off,
-                                                                (__nv_bfloat16*)out, ldo, B, F, HW, heads,
-                                                                scale * 1.4426950408889634f);
+  B2V_CHECK(ld % 8 == 0 && ((uintptr_t)qkv & 15) == 0 && ((uintptr_t)out & 15) == 0, "temporal_attention: 16-byte alignment");
+  if (F <= 16)
+    temporal_attn_kernel<1><<<(unsigned)grid, TA_WARPS * 32, 0, s>>>((const __nv_bfloat16*)qkv, ld, q_off, k_off, v_off,
+                                                                    (__nv_bfloat16*)out, ldo, B, F, HW, heads,
+                                                                    scale * 1.4426950408889634f);
+  else
+    temporal_attn_kernel<2><<<(unsigned)grid, TA_WARPS * 32, 0, s>>>((const __nv_bfloat16*)qkv, ld, q_off, k_off, v_off,
+                                                                    (__nv_bfloat16*)out, ldo, B, F, HW, heads,
+                                                                    scale * 1.4426950408889634f);
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;

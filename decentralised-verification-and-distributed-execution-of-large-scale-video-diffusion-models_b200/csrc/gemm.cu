@@ -12,6 +12,8 @@
 //              double-buffered TMEM accumulator; tcgen05.commit releases ring slots / publishes the tile
 //   warps 2-5: epilogue    — tcgen05.ld the accumulator (lane = output row), fused bias / time-embedding
 //              row bias / residual / GEGLU, bf16 pack, 64-byte row-contiguous global stores
+#include <stdlib.h>
+
 #include <mutex>
 
 #include "common.cuh"
@@ -330,8 +332,17 @@ int pick_bn(int N, bool geglu) {
   return 0;
 }
 
+static bool trace_on() {
+  static int on = -1;
+  if (on < 0) on = getenv("B2V_TRACE") != nullptr;
+  return on == 1;
+}
+
 // Generic entry used by the UNet host code and by the exported test ops.
 int gemm_tiled(const GemmArgs& g, cudaStream_t s) {
+  if (trace_on())
+    fprintf(stderr, "B2VTRACE gemm M=%lld N=%d K=%d taps=%d flags=%d res=%d rpb=%lld trs=%lld\n", (long long)g.M, g.N,
+            g.Kc, g.taps, g.flags, g.residual != nullptr, (long long)g.rows_per_batch, (long long)g.tap_row_stride);
   const bool geglu = (g.flags & B2V_EPI_GEGLU) != 0;
   const int bn = pick_bn(g.N, geglu);
   B2V_CHECK(bn != 0, "GEMM N=%d has no supported tile (needs a multiple of 64; GEGLU of 256)", g.N);
@@ -372,6 +383,8 @@ int gemm_tiled(const GemmArgs& g, cudaStream_t s) {
 
 // 3x3 / pad 1 / stride {1,2} convolution over NHWC through the TMA im2col path.
 int conv3x3_im2col(const ConvArgs& c, cudaStream_t s) {
+  if (trace_on())
+    fprintf(stderr, "B2VTRACE conv N=%d H=%d W=%d Cin=%d Cout=%d stride=%d\n", c.N, c.H, c.W, c.Cin, c.Cout, c.stride);
   const int bn = pick_bn(c.Cout, false);
   B2V_CHECK(bn != 0, "conv Cout=%d must be a multiple of 64", c.Cout);
   B2V_CHECK(c.Cin % BK == 0, "conv Cin=%d must be a multiple of 64", c.Cin);

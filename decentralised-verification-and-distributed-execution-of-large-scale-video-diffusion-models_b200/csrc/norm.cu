@@ -86,72 +86,103 @@ gn_stats_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat1
   }
 }
 
-// fold the per-CTA partials in a fixed order: stats[item][group] = {mean, rstd}
-__global__ void gn_finalize_kernel(const float* __restrict__ partial, int splits, int groups, int64_t n_items,
-                                   double cnt, float eps, float2* __restrict__ stats) {
-  const int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x;
+// fold the per-CTA partials in a fixed order: one warp per (item, group); lane k sums splits k, k+32, ... in order,
+// then a fixed butterfly combines the lanes (same tree every run -> bit-reproducible). stats[item][group] = {mean, rstd}
+__global__ void __launch_bounds__(128)
+gn_finalize_kernel(const float* __restrict__ partial, int splits, int groups, int64_t n_items, double cnt, float eps,
+                   float2* __restrict__ stats) {
+  const int lane = threadIdx.x & 31;
+  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   if (i >= n_items * groups) return;
   const int64_t item = i / groups;
   const int g = (int)(i % groups);
   double a = 0.0, q = 0.0;
-  for (int sp = 0; sp < splits; ++sp) {
-    const float* p = partial + (((item * splits + sp) * groups + g) << 1);
-    a += (double)p[0];
-    q += (double)p[1];
+  for (int sp = lane; sp < splits; sp += 32) {
+    const float2 p = __ldg(reinterpret_cast<const float2*>(partial + (((item * splits + sp) * groups + g) << 1)));
+    a += (double)p.x;
+    q += (double)p.y;
   }
-  const double m = a / cnt;
-  double var = q / cnt - m * m;
-  if (var < 0.0) var = 0.0;
-  stats[i] = make_float2((float)m, (float)(1.0 / sqrt(var + (double)eps)));
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    a += __shfl_xor_sync(0xffffffffu, a, o);
+    q += __shfl_xor_sync(0xffffffffu, q, o);
+  }
+  if (lane == 0) {
+    const double m = a / cnt;
+    double var = q / cnt - m * m;
+    if (var < 0.0) var = 0.0;
+    stats[i] = make_float2((float)m, (float)(1.0 / sqrt(var + (double)eps)));
+  }
 }
 
-// pass 2: y = (x - mean) * rstd * gamma + beta, optional SiLU. One thread per 8-channel vector.
-__global__ void __launch_bounds__(256)
+__device__ __forceinline__ float tanh_approx(float x) {
+  float y;
+  asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
+  return y;
+}
+// SiLU with ONE MUFU op per element (x * sigmoid(x) = 0.5 x (1 + tanh(x/2))): with exp + reciprocal the two MUFU ops
+// per element cost more than the HBM traffic of the kernel.
+__device__ __forceinline__ float silu_fast(float x) {
+  const float hx = 0.5f * x;
+  return fmaf(hx, tanh_approx(hx), hx);
+}
+
+// pass 2: y = x * scale + shift with scale = rstd*gamma, shift = beta - mean*rstd*gamma folded once per thread
+// (a thread owns fixed 8-channel vectors and walks rows), optional SiLU. Same grid shape as the stats pass.
+template <int ITERS>
+__global__ void __launch_bounds__(GN_THREADS)
 gn_apply_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat16* __restrict__ x2, int C2,
                 const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
-                int64_t total_rows, int64_t rows_per_item, int groups, int silu,
-                const float2* __restrict__ stats) {
+                int64_t rows_per_item, int groups, int silu, const float2* __restrict__ stats) {
   const int C = C1 + C2;
-  const int vecs = C >> 3;
   const int cpg = C / groups;
-  const int64_t total = total_rows * vecs;
-  for (int64_t w = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; w < total; w += (int64_t)gridDim.x * blockDim.x) {
-    const int64_t grow = w / vecs;
-    const int c = (int)(w % vecs) << 3;
-    const int64_t item = grow / rows_per_item;
-    uint4 u;
-    if (c < C1) u = __ldg(reinterpret_cast<const uint4*>(x1 + grow * C1 + c));
-    else u = __ldg(reinterpret_cast<const uint4*>(x2 + grow * C2 + (c - C1)));
-    const uint32_t uu[4] = {u.x, u.y, u.z, u.w};
-    float f[8];
+  const int item = blockIdx.y;
+  const int tx = threadIdx.x & (GN_TX - 1), ty = threadIdx.x / GN_TX;
+  const int64_t rows_per_cta = (rows_per_item + gridDim.x - 1) / gridDim.x;
+  const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta;
+  int64_t r1 = r0 + rows_per_cta;
+  if (r1 > rows_per_item) r1 = rows_per_item;
+  float sc[ITERS][8], sh[ITERS][8];
 #pragma unroll
-    for (int j = 0; j < 4; ++j) {
-      const float2 t = unpack_bf16x2(uu[j]);
-      f[2 * j] = t.x; f[2 * j + 1] = t.y;
-    }
-    const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + c)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + c + 4));
-    const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + c)), b1 = __ldg(reinterpret_cast<const float4*>(beta + c + 4));
-    const float gm[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
-    const float bt[8] = {b0.x, b0.y, b0.z, b0.w, b1.x, b1.y, b1.z, b1.w};
-    int last_g = -1;
-    float mean = 0.f, rstd = 0.f;
+  for (int i = 0; i < ITERS; ++i) {
+    const int c = (tx + i * GN_TX) << 3;
+    if (c < C) {
 #pragma unroll
-    for (int j = 0; j < 8; ++j) {
-      const int g = (c + j) / cpg;
-      if (g != last_g) {
-        const float2 st = __ldg(stats + item * groups + g);
-        mean = st.x;
-        rstd = st.y;
-        last_g = g;
+      for (int j = 0; j < 8; ++j) {
+        const float2 st = __ldg(stats + (int64_t)item * groups + (c + j) / cpg);
+        const float gm = __ldg(gamma + c + j), bt = __ldg(beta + c + j);
+        sc[i][j] = st.y * gm;
+        sh[i][j] = fmaf(-st.x, st.y * gm, bt);
       }
-      float v = (f[j] - mean) * rstd * gm[j] + bt[j];
-      if (silu) v = silu_f(v);
-      f[j] = v;
     }
-    uint4 o;
-    o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
-    o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
-    *reinterpret_cast<uint4*>(y + grow * C + c) = o;
+  }
+  for (int64_t r = r0 + ty; r < r1; r += GN_TY) {
+    const int64_t grow = (int64_t)item * rows_per_item + r;
+#pragma unroll
+    for (int i = 0; i < ITERS; ++i) {
+      const int c = (tx + i * GN_TX) << 3;
+      if (c < C) {
+        uint4 u;
+        if (c < C1) u = __ldg(reinterpret_cast<const uint4*>(x1 + grow * C1 + c));
+        else u = __ldg(reinterpret_cast<const uint4*>(x2 + grow * C2 + (c - C1)));
+        const uint32_t uu[4] = {u.x, u.y, u.z, u.w};
+        float f[8];
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float2 t = unpack_bf16x2(uu[j]);
+          f[2 * j] = fmaf(t.x, sc[i][2 * j], sh[i][2 * j]);
+          f[2 * j + 1] = fmaf(t.y, sc[i][2 * j + 1], sh[i][2 * j + 1]);
+        }
+        if (silu) {
+#pragma unroll
+          for (int j = 0; j < 8; ++j) f[j] = silu_fast(f[j]);
+        }
+        uint4 o;
+        o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
+        o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
+        *reinterpret_cast<uint4*>(y + grow * C + c) = o;
+      }
+    }
   }
 }
 
@@ -294,6 +325,9 @@ int group_norm(const void* x1, int C1, const void* x2, int C2, const float* gamm
 #define B2V_GN_STATS(I)                                                                                     \
   gn_stats_kernel<I><<<grid, GN_THREADS, shb, s>>>((const __nv_bfloat16*)x1, C1, (const __nv_bfloat16*)x2, C2, \
                                                    rows_per_item, groups, partial)
+#define B2V_GN_APPLY(I)                                                                                      \
+  gn_apply_kernel<I><<<grid, GN_THREADS, 0, s>>>((const __nv_bfloat16*)x1, C1, (const __nv_bfloat16*)x2, C2, gamma, \
+                                                 beta, (__nv_bfloat16*)y, rows_per_item, groups, silu, stats)
   switch (iters) {
     case 1: B2V_GN_STATS(1); break;
     case 2: B2V_GN_STATS(2); break;
@@ -302,17 +336,21 @@ int group_norm(const void* x1, int C1, const void* x2, int C2, const float* gamm
     case 5: B2V_GN_STATS(5); break;
     default: return fail(B2V_ERR_ARG, "group_norm: C=%d too wide (max 2560)", C);
   }
-#undef B2V_GN_STATS
   count_launch();
   const int64_t ng = n_items * groups;
-  gn_finalize_kernel<<<(unsigned)((ng + 127) / 128), 128, 0, s>>>(partial, splits, groups, n_items,
-                                                                   (double)rows_per_item * (double)(C / groups), eps,
-                                                                   stats);
+  gn_finalize_kernel<<<(unsigned)((ng * 32 + 127) / 128), 128, 0, s>>>(partial, splits, groups, n_items,
+                                                                       (double)rows_per_item * (double)(C / groups), eps,
+                                                                       stats);
   count_launch();
-  const int64_t total_rows = n_items * rows_per_item;
-  gn_apply_kernel<<<grid_1d(total_rows * (C >> 3), 256, 8), 256, 0, s>>>(
-      (const __nv_bfloat16*)x1, C1, (const __nv_bfloat16*)x2, C2, gamma, beta, (__nv_bfloat16*)y, total_rows,
-      rows_per_item, groups, silu, stats);
+  switch (iters) {
+    case 1: B2V_GN_APPLY(1); break;
+    case 2: B2V_GN_APPLY(2); break;
+    case 3: B2V_GN_APPLY(3); break;
+    case 4: B2V_GN_APPLY(4); break;
+    default: B2V_GN_APPLY(5); break;
+  }
+#undef B2V_GN_STATS
+#undef B2V_GN_APPLY
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;
