@@ -7,6 +7,7 @@ Mirrors the call surface the reference uses on diffusers' ``UNet3DConditionModel
 Weights are fed under their diffusers ``state_dict`` names (b2v_unet3d_load_tensor) so a real checkpoint loads.
 """
 import ctypes as C
+import threading
 from types import SimpleNamespace
 
 import torch
@@ -63,6 +64,7 @@ class UNet3DConditionModel:
         self._lib = lib
         self._finalized = False
         self._ws = None
+        self._fwd_lock = threading.Lock()
 
     # ---- weights ----
     def load_state_dict(self, state_dict, strict=True):
@@ -131,10 +133,13 @@ class UNet3DConditionModel:
             encoder_hidden_states = encoder_hidden_states.to(sample.dtype)
         if encoder_hidden_states.shape[0] != B:
             raise ValueError("encoder_hidden_states batch %d != sample batch %d" % (encoder_hidden_states.shape[0], B))
-        ws = self._workspace(B, F, H, W)
         t = float(timestep.item()) if isinstance(timestep, torch.Tensor) else float(timestep)
-        check(self._lib.b2v_unet3d_forward(self._h, ops.ptr(sample), t, ops.ptr(encoder_hidden_states), ops.ptr(out),
-                                           ops.dtype_tag(sample), B, F, H, W, ops.ptr(ws), ws.numel(), ops.stream()))
+        # the miner calls from several axon worker threads with no lock of its own (miner.py:571-600): one forward at a
+        # time may enqueue onto this handle's workspace
+        with self._fwd_lock:
+            ws = self._workspace(B, F, H, W)
+            check(self._lib.b2v_unet3d_forward(self._h, ops.ptr(sample), t, ops.ptr(encoder_hidden_states), ops.ptr(out),
+                                               ops.dtype_tag(sample), B, F, H, W, ops.ptr(ws), ws.numel(), ops.stream()))
         return out
 
     def __call__(self, sample, timestep, encoder_hidden_states=None, return_dict=True, **_ignored):
