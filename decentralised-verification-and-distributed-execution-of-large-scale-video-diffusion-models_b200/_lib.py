@@ -5,7 +5,8 @@ import os
 import threading
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libb2v.so")
+# B2V_LIB: A/B a differently built libb2v (tools/gemm_ab.py); the default is the in-tree build
+LIB_PATH = os.environ.get("B2V_LIB") or os.path.join(_HERE, "libb2v.so")
 
 F32, F16, BF16 = 0, 1, 2
 EPI_GEGLU, EPI_GELU = 1, 2

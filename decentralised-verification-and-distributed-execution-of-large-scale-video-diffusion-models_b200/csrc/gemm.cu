@@ -5,13 +5,14 @@
 //   * ResnetBlock2D / Down / Upsample Conv2d 3x3 as an implicit GEMM (TMA im2col)   taps = 9
 // out[M,N] = sum_tap A_tap[M,Kc] · W[N, tap*Kc:(tap+1)*Kc]^T  (+bias, +row-group bias, +residual | GEGLU)
 //
-// Kernel shape (persistent, warp specialised, one CTA per SM, 192 threads):
+// Kernel shape (persistent, warp specialised, one CTA per SM, 320 threads):
 //   warp 0   : TMA producer — A tile {128 rows x 64 ch} + W tile {BN rows x 64 ch} per k-block into a
 //              128B-swizzled shared-memory ring (STAGES deep), completion on `full` mbarriers
 //   warp 1   : MMA issuer  — one elected lane issues 4 x tcgen05.mma (128 x BN x 16) per k-block into a
 //              double-buffered TMEM accumulator; tcgen05.commit releases ring slots / publishes the tile
-//   warps 2-5: epilogue    — tcgen05.ld the accumulator (lane = output row), fused bias / time-embedding
-//              row bias / residual / GEGLU, bf16 pack, 64-byte row-contiguous global stores
+//   warps 2-9: epilogue    — tcgen05.ld the accumulator (lane = output row; two warps per TMEM lane quarter, one per
+//              column half), software-pipelined over 16-column chunks, fused bias / time-embedding row bias /
+//              residual (prefetched) / GEGLU with a branch-free erf, bf16 pack, 32-byte row-contiguous global stores
 #include <stdlib.h>
 
 #include <mutex>
@@ -28,16 +29,33 @@ using namespace ptx;
 constexpr int BM = 128;
 constexpr int BK = 64;
 constexpr int A_BYTES = BM * BK * 2;  // 16 KiB
-constexpr int NUM_THREADS = 192;
+constexpr int NUM_THREADS = 320;  // TMA warp + MMA warp + 8 epilogue warps
 constexpr int TMEM_COLS = 512;
 
-template <int BN>
+constexpr int EPI_WARPS = 8;
+constexpr int SMEM_LIMIT = 227 * 1024;
+
+// Shared-memory plan of one instantiation: [operand ring: STAGES x (A 16 KiB + B)] [epilogue staging: one output panel
+// per epilogue warp] [barriers]. An epilogue warp owns 32 rows x GROUP_COLS columns of the tile and hands them to the
+// TMA store engine in panels of PANEL_COLS columns: 64 (128-byte rows, 128B swizzle, conflict-free writes) when the
+// group width allows it, else the whole group width unswizzled (BN = 160 -> 80 columns, BN = 64 -> 32).
+template <int BN, bool GEGLU>
 struct TileCfg {
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
-  static constexpr int STAGES = (BN >= 256) ? 4 : (BN >= 128 ? 6 : 8);
   static constexpr int ACC_STRIDE = (BN > 128) ? 256 : 128;  // TMEM columns between the two accumulators
-  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + 256 /*barriers*/ + 1024 /*alignment slack*/;
+  static constexpr int OUT_COLS = GEGLU ? BN / 2 : BN;
+  static constexpr int GROUP_COLS = OUT_COLS / 2;
+  static constexpr int PANEL_COLS = (GROUP_COLS % 64 == 0) ? 64 : GROUP_COLS;
+  static constexpr bool PANEL_SWIZZLE = PANEL_COLS == 64;
+  static constexpr int PANEL_BYTES = PANEL_COLS * 2 * 32;
+  static constexpr int EPI_BYTES = EPI_WARPS * PANEL_BYTES;
+  static constexpr int FIXED = EPI_BYTES + 256 /*barriers*/ + 1024 /*alignment slack*/;
+  static constexpr int STAGES_FIT = (SMEM_LIMIT - FIXED) / STAGE_BYTES;
+  static constexpr int STAGES = STAGES_FIT > 8 ? 8 : STAGES_FIT;
+  static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + FIXED;
+  static_assert(STAGES >= 4, "operand ring too shallow");
+  static_assert(PANEL_BYTES % 1024 == 0, "panel buffers must keep the 1 KiB swizzle alignment");
 };
 
 struct GemmParams {
@@ -60,97 +78,190 @@ struct GemmParams {
   __nv_bfloat16* out;
   int64_t ldo;
   int gelu;
+  // EPI_NCFHW (conv_out): out_raw[((b*nc_cout + co)*nc_F + f)*nc_HW + pix] of dtype nc_dtype, row = (b*nc_F + f)*nc_HW + pix
+  void* out_raw;
+  int nc_dtype, nc_cout, nc_F;
+  int64_t nc_HW;
 };
 
+constexpr int EPI_PLAIN = 0, EPI_GEGLU_T = 1, EPI_NCFHW = 2;
+
+// gelu_erf(x) = 0.5 x (1 + erf(x / sqrt 2)) with erf from Abramowitz-Stegun 7.1.26 (|abs err| <= 1.5e-7, far below the
+// bf16 rounding of the output): 2 MUFU + ~12 FMA-pipe instructions and no branches (erff() is ~40 with two branches;
+// the GEGLU epilogue of the L0 feed-forward was bound by it). The negative side uses 1 + erf(z) = P e^{-z^2} directly,
+// so there is no cancellation for x << 0.
+__device__ __forceinline__ float gelu_fast(float x) {
+  const float az = fabsf(x) * 0.70710678118654752440f;
+  float t;
+  asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(t) : "f"(fmaf(0.3275911f, az, 1.0f)));
+  float e;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(e) : "f"(x * x * -0.72134752044448170368f));  // exp(-x^2/2)
+  float pl = fmaf(1.061405429f, t, -1.453152027f);
+  pl = fmaf(pl, t, 1.421413741f);
+  pl = fmaf(pl, t, -0.284496736f);
+  pl = fmaf(pl, t, 0.254829592f);
+  const float pe = pl * t * e;                  // 1 - erf(|z|)
+  const float phi2 = x < 0.f ? pe : 2.0f - pe;  // 1 + erf(z)
+  return 0.5f * x * phi2;
+}
+
+// One epilogue warp handles 32 rows (its TMEM lane quarter) x half of the tile's output columns (group 0 / 1), in
+// 16-column chunks: tcgen05.ld of chunk c+1 and the residual loads of chunk c+1 are in flight while chunk c is
+// computed and stored (the residual of the first chunk is fetched before the accumulator is even complete).
 template <int BN, bool GEGLU>
-__device__ __forceinline__ void epilogue_tile(const GemmParams& p, uint32_t tacc, int64_t grow, bool valid,
-                                              int n_tile) {
-  constexpr int OUT_COLS = GEGLU ? BN / 2 : BN;
-  const int64_t ocol0 = (int64_t)n_tile * OUT_COLS;
-  const int wcol0 = n_tile * BN;  // column in the (packed) weight / bias space
-#pragma unroll 1
-  for (int c = 0; c < OUT_COLS; c += 32) {
-    uint32_t v[32];
-    tmem_ld32(tacc + c, v);
-    uint32_t g[GEGLU ? 32 : 1];
-    if constexpr (GEGLU) tmem_ld32(tacc + BN / 2 + c, g);
+__device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtensorMap* tmO, uint8_t* stage, int lane,
+                                              int row0, int slab, uint32_t tacc, int64_t grow, bool valid, int n_tile,
+                                              int group, uint32_t tfull_bar, uint32_t tfull_phase) {
+  using Cfg = TileCfg<BN, GEGLU>;
+  constexpr int OUT_COLS = Cfg::OUT_COLS;
+  constexpr int NCH = OUT_COLS / 32;  // 16-column chunks per group
+  constexpr int CH_PER_PANEL = Cfg::PANEL_COLS / 16;
+  uint8_t* srow = stage + lane * (Cfg::PANEL_COLS * 2);
+  const int c_base = group * NCH * 16;
+  const int64_t ocol0 = (int64_t)n_tile * OUT_COLS + c_base;
+  const int wcol0 = n_tile * BN + c_base;  // column in the (packed) weight / bias space
+  const bool has_res = p.residual != nullptr && valid;
+  const uint4* res4 = reinterpret_cast<const uint4*>(p.residual + (has_res ? grow * p.ldo + ocol0 : 0));
+  const float* rb = (!GEGLU && p.rowbias) ? p.rowbias + (grow / p.rows_per_group) * (int64_t)p.N + wcol0 : nullptr;
+
+  // the whole residual row-half is fetched up front (before the accumulator is complete): maximum loads in flight, and
+  // no load is outstanding on a 128-byte line when this thread stores to it — with the in-place residual the UNet uses
+  // (out == residual) an interleaved load/store on the same line serialises in the LSU (measured 2x slower).
+  uint4 res[NCH][2];
+  if (has_res) {
+#pragma unroll
+    for (int i = 0; i < NCH; ++i) { res[i][0] = res4[2 * i]; res[i][1] = res4[2 * i + 1]; }
+  }
+  mbar_wait(tfull_bar, tfull_phase);
+  tc_fence_after();
+  uint32_t v[2][16];
+  uint32_t g[GEGLU ? 2 : 1][16];
+  tmem_ld16(tacc + c_base, v[0]);
+  if constexpr (GEGLU) tmem_ld16(tacc + BN / 2 + c_base, g[0]);
+#pragma unroll
+  for (int ch = 0; ch < NCH; ++ch) {
+    const int cur = ch & 1, nxt = cur ^ 1;
+    const int c = ch * 16;
     tmem_wait_ld();
-    if (valid) {
-      float f[32];
+    if (ch + 1 < NCH) {
+      tmem_ld16(tacc + c_base + c + 16, v[nxt]);
+      if constexpr (GEGLU) tmem_ld16(tacc + BN / 2 + c_base + c + 16, g[nxt]);
+    }
+    float f[16];
 #pragma unroll
-      for (int j = 0; j < 32; ++j) f[j] = __uint_as_float(v[j]);
+    for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[cur][j]);
+    if (p.bias) {
+      const float4* b4 = reinterpret_cast<const float4*>(p.bias + wcol0 + c);
+#pragma unroll
+      for (int j = 0; j < 4; ++j) {
+        const float4 b = __ldg(b4 + j);
+        f[4 * j] += b.x; f[4 * j + 1] += b.y; f[4 * j + 2] += b.z; f[4 * j + 3] += b.w;
+      }
+    }
+    if constexpr (GEGLU) {
+      float gt[16];
+#pragma unroll
+      for (int j = 0; j < 16; ++j) gt[j] = __uint_as_float(g[cur][j]);
       if (p.bias) {
-        const float4* b4 = reinterpret_cast<const float4*>(p.bias + wcol0 + c);
+        const float4* b4 = reinterpret_cast<const float4*>(p.bias + wcol0 + BN / 2 + c);
 #pragma unroll
-        for (int j = 0; j < 8; ++j) {
+        for (int j = 0; j < 4; ++j) {
           const float4 b = __ldg(b4 + j);
+          gt[4 * j] += b.x; gt[4 * j + 1] += b.y; gt[4 * j + 2] += b.z; gt[4 * j + 3] += b.w;
+        }
+      }
+#pragma unroll
+      for (int j = 0; j < 16; ++j) f[j] *= gelu_fast(gt[j]);
+    } else {
+      if (rb) {
+        const float4* r4 = reinterpret_cast<const float4*>(rb + c);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float4 b = __ldg(r4 + j);
           f[4 * j] += b.x; f[4 * j + 1] += b.y; f[4 * j + 2] += b.z; f[4 * j + 3] += b.w;
         }
       }
-      if constexpr (GEGLU) {
-        float gt[32];
+      if (p.gelu) {
 #pragma unroll
-        for (int j = 0; j < 32; ++j) gt[j] = __uint_as_float(g[j]);
-        if (p.bias) {
-          const float4* b4 = reinterpret_cast<const float4*>(p.bias + wcol0 + BN / 2 + c);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 b = __ldg(b4 + j);
-            gt[4 * j] += b.x; gt[4 * j + 1] += b.y; gt[4 * j + 2] += b.z; gt[4 * j + 3] += b.w;
-          }
-        }
-#pragma unroll
-        for (int j = 0; j < 32; ++j) f[j] *= gelu_erf_f(gt[j]);
-      } else {
-        if (p.rowbias) {
-          const float4* r4 =
-              reinterpret_cast<const float4*>(p.rowbias + (grow / p.rows_per_group) * (int64_t)p.N + wcol0 + c);
-#pragma unroll
-          for (int j = 0; j < 8; ++j) {
-            const float4 b = __ldg(r4 + j);
-            f[4 * j] += b.x; f[4 * j + 1] += b.y; f[4 * j + 2] += b.z; f[4 * j + 3] += b.w;
-          }
-        }
-        if (p.gelu) {
-#pragma unroll
-          for (int j = 0; j < 32; ++j) f[j] = gelu_erf_f(f[j]);
-        }
+        for (int j = 0; j < 16; ++j) f[j] = gelu_fast(f[j]);
       }
-      if (p.residual) {
-        const uint4* r4 = reinterpret_cast<const uint4*>(p.residual + grow * p.ldo + ocol0 + c);
+    }
+    if (has_res) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const uint4 r = __ldg(r4 + j);
-          const float2 a = unpack_bf16x2(r.x), b = unpack_bf16x2(r.y), cc = unpack_bf16x2(r.z), d = unpack_bf16x2(r.w);
-          f[8 * j] += a.x; f[8 * j + 1] += a.y; f[8 * j + 2] += b.x; f[8 * j + 3] += b.y;
-          f[8 * j + 4] += cc.x; f[8 * j + 5] += cc.y; f[8 * j + 6] += d.x; f[8 * j + 7] += d.y;
-        }
+      for (int j = 0; j < 2; ++j) {
+        const uint4 r = res[ch][j];
+        const float2 a = unpack_bf16x2(r.x), b = unpack_bf16x2(r.y), cc = unpack_bf16x2(r.z), d = unpack_bf16x2(r.w);
+        f[8 * j] += a.x; f[8 * j + 1] += a.y; f[8 * j + 2] += b.x; f[8 * j + 3] += b.y;
+        f[8 * j + 4] += cc.x; f[8 * j + 5] += cc.y; f[8 * j + 6] += d.x; f[8 * j + 7] += d.y;
       }
-      uint4* o4 = reinterpret_cast<uint4*>(p.out + grow * p.ldo + ocol0 + c);
+    }
+    // ---- stage the 16 columns in this warp's panel buffer; a full panel goes out as ONE TMA store (32 rows x
+    // PANEL_COLS, rows outside the tensor / slab are clipped by the tensor map) ----
+    const int k = ch % CH_PER_PANEL;
+    if (k == 0) {
+      if (lane == 0) bulk_wait_read0();  // the previous store from this buffer has been read out
+      __syncwarp();
+    }
 #pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        uint4 o;
-        o.x = pack_bf16x2(f[8 * j], f[8 * j + 1]);
-        o.y = pack_bf16x2(f[8 * j + 2], f[8 * j + 3]);
-        o.z = pack_bf16x2(f[8 * j + 4], f[8 * j + 5]);
-        o.w = pack_bf16x2(f[8 * j + 6], f[8 * j + 7]);
-        o4[j] = o;
+    for (int j = 0; j < 2; ++j) {
+      uint4 o;
+      o.x = pack_bf16x2(f[8 * j], f[8 * j + 1]);
+      o.y = pack_bf16x2(f[8 * j + 2], f[8 * j + 3]);
+      o.z = pack_bf16x2(f[8 * j + 4], f[8 * j + 5]);
+      o.w = pack_bf16x2(f[8 * j + 6], f[8 * j + 7]);
+      const int piece = 2 * k + j;
+      const int pos = Cfg::PANEL_SWIZZLE ? (piece ^ (lane & 7)) : piece;
+      *reinterpret_cast<uint4*>(srow + (pos << 4)) = o;
+    }
+    if (k == CH_PER_PANEL - 1) {
+      fence_proxy_async_smem();
+      __syncwarp();
+      if (lane == 0) {
+        tma_store_3d(tmO, smem_u32(stage), (int)ocol0 + (ch / CH_PER_PANEL) * Cfg::PANEL_COLS, row0, slab);
+        bulk_commit();
       }
     }
   }
 }
 
+// conv_out epilogue: only the first nc_cout (<= 16) accumulator columns are real; thread = pixel writes one element per
+// output channel plane (consecutive lanes -> consecutive pixels: coalesced), fp32 bias add, one rounding to the io dtype.
+__device__ __forceinline__ void epilogue_ncfhw(const GemmParams& p, uint32_t tacc, int64_t grow, bool valid, int group,
+                                               uint32_t tfull_bar, uint32_t tfull_phase) {
+  mbar_wait(tfull_bar, tfull_phase);
+  tc_fence_after();
+  if (group != 0) return;
+  uint32_t v[16];
+  tmem_ld16(tacc, v);
+  tmem_wait_ld();
+  if (!valid) return;
+  const int64_t n = grow / p.nc_HW, pix = grow % p.nc_HW;
+  const int64_t b = n / p.nc_F, f = n % p.nc_F;
+#pragma unroll
+  for (int co = 0; co < 16; ++co) {
+    if (co < p.nc_cout) {
+      const float val = __uint_as_float(v[co]) + (p.bias ? __ldg(p.bias + co) : 0.f);
+      const int64_t idx = ((b * p.nc_cout + co) * p.nc_F + f) * p.nc_HW + pix;
+      if (p.nc_dtype == B2V_F32) reinterpret_cast<float*>(p.out_raw)[idx] = val;
+      else if (p.nc_dtype == B2V_F16) reinterpret_cast<__half*>(p.out_raw)[idx] = __float2half_rn(val);
+      else reinterpret_cast<__nv_bfloat16*>(p.out_raw)[idx] = __float2bfloat16_rn(val);
+    }
+  }
+}
+
 // MODE 0: A through a 3-D tiled tensor map (channels, rows, slabs); MODE 1: A through a 4-D im2col map.
-template <int BN, int MODE, bool GEGLU>
+template <int BN, int MODE, int EPI>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
-gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB, const GemmParams p) {
-  using Cfg = TileCfg<BN>;
+gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
+            const __grid_constant__ CUtensorMap tmO, const GemmParams p) {
+  using Cfg = TileCfg<BN, EPI == EPI_GEGLU_T>;
   constexpr int STAGES = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
   uint8_t* sA = smem;
   uint8_t* sB = smem + STAGES * A_BYTES;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + STAGES * Cfg::STAGE_BYTES);
+  uint8_t* sEpi = smem + STAGES * Cfg::STAGE_BYTES;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(sEpi + Cfg::EPI_BYTES);
   // bars: [0,STAGES) full, [STAGES,2*STAGES) empty, then tmem_full[2], tmem_empty[2], then the TMEM base slot
   const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + STAGES);
   const uint32_t tfull0 = smem_u32(bars + 2 * STAGES), tempty0 = smem_u32(bars + 2 * STAGES + 2);
@@ -164,13 +275,14 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
+    prefetch_tmap(&tmO);
     for (int i = 0; i < STAGES; ++i) {
       mbar_init(full0 + 8 * i, 1);
       mbar_init(empty0 + 8 * i, 1);
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(tfull0 + 8 * i, 1);
-      mbar_init(tempty0 + 8 * i, 4);
+      mbar_init(tempty0 + 8 * i, 8);
     }
     fence_barrier_init();
   }
@@ -250,33 +362,38 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   } else {
-    // ===================== epilogue (warps 2..5 -> TMEM lane quarters 2,3,0,1) =====================
+    // ===================== epilogue (warps 2..9 -> TMEM lane quarters 2,3,0,1,2,3,0,1; column halves 0,0,0,0,1,1,1,1) ====
     const int quarter = warp & 3;
-    const int row = quarter * 32 + lane;
+    const int group = (warp - 2) >> 2;
     int acc = 0;
     uint32_t acc_phase = 0;
     for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
       const int n_tile = tile % p.num_n_tiles, m_tile = tile / p.num_n_tiles;
       int64_t grow;
       bool valid;
+      int slab = 0, row0;  // TMA-store coordinates of this warp's first row: row inside the slab, slab
       if (MODE == 0) {
-        const int slab = m_tile / p.m_tiles_per_batch;
-        const int64_t r = (int64_t)(m_tile % p.m_tiles_per_batch) * BM + row;
+        slab = m_tile / p.m_tiles_per_batch;
+        row0 = (m_tile % p.m_tiles_per_batch) * BM + quarter * 32;
+        const int64_t r = (int64_t)row0 + lane;
         valid = r < p.rows_per_batch;
         grow = (int64_t)slab * p.rows_per_batch + r;
       } else {
-        grow = (int64_t)m_tile * BM + row;
+        row0 = m_tile * BM + quarter * 32;
+        grow = (int64_t)row0 + lane;
         valid = grow < p.M;
       }
-      mbar_wait(tfull0 + 8 * acc, acc_phase);
-      tc_fence_after();
       const uint32_t tacc = tmem_base + acc * Cfg::ACC_STRIDE + ((uint32_t)(quarter * 32) << 16);
-      epilogue_tile<BN, GEGLU>(p, tacc, grow, valid, n_tile);
+      if constexpr (EPI == EPI_NCFHW) epilogue_ncfhw(p, tacc, grow, valid, group, tfull0 + 8 * acc, acc_phase);
+      else
+        epilogue_tile<BN, EPI == EPI_GEGLU_T>(p, &tmO, sEpi + (warp - 2) * Cfg::PANEL_BYTES, lane, row0, slab, tacc, grow,
+                                              valid, n_tile, group, tfull0 + 8 * acc, acc_phase);
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
       if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
+    if (lane == 0) bulk_wait0();  // this warp's TMA stores have drained before its shared memory goes away
   }
 
   tc_fence_before();
@@ -287,19 +404,28 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   }
 }
 
-template <int BN, int MODE, bool GEGLU>
-int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, cudaStream_t s) {
-  using Cfg = TileCfg<BN>;
+template <int BN, int MODE, int EPI>
+int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int64_t out_rows_per_slab,
+                int64_t out_slabs, cudaStream_t s) {
+  using Cfg = TileCfg<BN, EPI == EPI_GEGLU_T>;
+  CUtensorMap tmO = tmA;  // EPI_NCFHW stores with plain instructions
+  if (EPI != EPI_NCFHW) {
+    const int n_out = EPI == EPI_GEGLU_T ? p.N / 2 : p.N;
+    const uint64_t dims[3] = {(uint64_t)n_out, (uint64_t)out_rows_per_slab, (uint64_t)out_slabs};
+    const uint64_t strides[2] = {(uint64_t)p.ldo * 2, (uint64_t)out_rows_per_slab * (uint64_t)p.ldo * 2};
+    const uint32_t box[3] = {(uint32_t)Cfg::PANEL_COLS, 32, 1};
+    B2V_TRY(tmap_tiled_bf16_sw(&tmO, p.out, 3, dims, strides, box, Cfg::PANEL_SWIZZLE));
+  }
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(gemm_kernel<BN, MODE, GEGLU>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    attr_err = cudaFuncSetAttribute(gemm_kernel<BN, MODE, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     Cfg::SMEM_BYTES);
   });
   if (attr_err != cudaSuccess) return fail(B2V_ERR_CUDA, "gemm smem attr: %s", cudaGetErrorString(attr_err));
   const int tiles = p.num_m_tiles * p.num_n_tiles;
   const int grid = tiles < sm_count() ? tiles : sm_count();
-  gemm_kernel<BN, MODE, GEGLU><<<grid, NUM_THREADS, Cfg::SMEM_BYTES, s>>>(tmA, tmB, p);
+  gemm_kernel<BN, MODE, EPI><<<grid, NUM_THREADS, Cfg::SMEM_BYTES, s>>>(tmA, tmB, tmO, p);
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;
@@ -307,16 +433,16 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
 
 template <int MODE>
 int dispatch_gemm(int bn, bool geglu, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
-                  cudaStream_t s) {
+                  int64_t orows, int64_t oslabs, cudaStream_t s) {
   if (geglu) {
-    if (bn == 256) return launch_gemm<256, MODE, true>(tmA, tmB, p, s);
+    if (bn == 256) return launch_gemm<256, MODE, EPI_GEGLU_T>(tmA, tmB, p, orows, oslabs, s);
     return fail(B2V_ERR_ARG, "GEGLU epilogue needs N %% 256 == 0");
   }
   switch (bn) {
-    case 256: return launch_gemm<256, MODE, false>(tmA, tmB, p, s);
-    case 160: return launch_gemm<160, MODE, false>(tmA, tmB, p, s);
-    case 128: return launch_gemm<128, MODE, false>(tmA, tmB, p, s);
-    case 64: return launch_gemm<64, MODE, false>(tmA, tmB, p, s);
+    case 256: return launch_gemm<256, MODE, EPI_PLAIN>(tmA, tmB, p, orows, oslabs, s);
+    case 160: return launch_gemm<160, MODE, EPI_PLAIN>(tmA, tmB, p, orows, oslabs, s);
+    case 128: return launch_gemm<128, MODE, EPI_PLAIN>(tmA, tmB, p, orows, oslabs, s);
+    case 64: return launch_gemm<64, MODE, EPI_PLAIN>(tmA, tmB, p, orows, oslabs, s);
   }
   return fail(B2V_ERR_ARG, "no tile for N");
 }
@@ -378,7 +504,7 @@ int gemm_tiled(const GemmArgs& g, cudaStream_t s) {
   p.out = (__nv_bfloat16*)g.out;
   p.ldo = g.ldo > 0 ? g.ldo : (geglu ? g.N / 2 : g.N);
   p.gelu = (g.flags & B2V_EPI_GELU) ? 1 : 0;
-  return dispatch_gemm<0>(bn, geglu, tmA, tmB, p, s);
+  return dispatch_gemm<0>(bn, geglu, tmA, tmB, p, rpb, slabs, s);
 }
 
 // 3x3 / pad 1 / stride {1,2} convolution over NHWC through the TMA im2col path.
@@ -418,7 +544,15 @@ int conv3x3_im2col(const ConvArgs& c, cudaStream_t s) {
   p.out = (__nv_bfloat16*)c.out;
   p.ldo = c.Cout;
   p.gelu = 0;
-  return dispatch_gemm<1>(bn, false, tmA, tmB, p, s);
+  if (c.ncfhw_out) {
+    B2V_CHECK(c.Cout == 64 && c.ncfhw_cout >= 1 && c.ncfhw_cout <= 16 && c.stride == 1 && c.N % c.ncfhw_F == 0 &&
+                  dtype_size(c.ncfhw_dtype) != 0,
+              "conv NCFHW epilogue: needs a 64-row padded weight, <= 16 real channels, stride 1");
+    p.out_raw = c.ncfhw_out; p.nc_dtype = c.ncfhw_dtype; p.nc_cout = c.ncfhw_cout; p.nc_F = c.ncfhw_F;
+    p.nc_HW = (int64_t)P * Q;
+    return launch_gemm<64, 1, EPI_NCFHW>(tmA, tmB, p, p.M, 1, s);
+  }
+  return dispatch_gemm<1>(bn, false, tmA, tmB, p, p.M, 1, s);
 }
 
 }  // namespace b2v

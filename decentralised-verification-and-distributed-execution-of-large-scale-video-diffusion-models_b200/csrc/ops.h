@@ -37,12 +37,8 @@ int time_embedding(float timestep, int B, int dim0, const float* w1, const float
                    int temb_dim, float* silu_emb_out /*[B,temb_dim] = SiLU(emb)*/, cudaStream_t s);
 // out[b, n] = bias[n] + sum_k W[n,k] * in[b,k]  (fp32, tiny M)
 int small_linear(const float* in, const float* w, const float* bias, float* out, int B, int N, int K, cudaStream_t s);
-// conv_in: NCFHW (io dtype) -> NHWC bf16, 3x3 pad 1, Cin tiny
-int conv_in_3x3(const void* x, int io_dtype, const float* w /*[Cout][Cin][3][3]*/, const float* bias, void* y, int B,
-                int Cin, int F, int H, int W, int Cout, cudaStream_t s);
-// conv_out: NHWC bf16 -> NCFHW (io dtype), 3x3 pad 1, Cout tiny
-int conv_out_3x3(const void* x, const float* w /*[Cout][3][3][Cin]*/, const float* bias, void* y, int io_dtype, int B,
-                 int Cin, int F, int H, int W, int Cout, cudaStream_t s);
+// NCFHW (io dtype) -> channels-last bf16 rows [B*F*HW, Cpad], zero padded channels (input of the tensor-core conv_in)
+int ncfhw_to_rows(const void* x, int io_dtype, void* y, int B, int Cin, int F, int64_t HW, int Cpad, cudaStream_t s);
 // dtype conversion of the text embeddings to bf16 rows
 int to_bf16(const void* x, int dtype, void* y, int64_t n, cudaStream_t s);
 

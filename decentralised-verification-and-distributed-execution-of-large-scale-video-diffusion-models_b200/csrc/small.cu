@@ -1,6 +1,7 @@
 // SIMT kernels for the thin ends of the UNet3D ([UPSTREAM diffusers] UNet3DConditionModel.forward):
 // sinusoidal timestep embedding + time MLP, per-resnet time projections (M = batch, far too small for the
-// tensor cores), conv_in (4 -> 320 channels, NCFHW -> channels-last) and conv_out (320 -> 4, back to NCFHW).
+// tensor cores) and the NCFHW -> channels-last staging of the latent for conv_in (conv_in / conv_out themselves run on
+// the tcgen05 implicit-GEMM kernel with zero-padded channels, gemm.cu).
 #include "common.cuh"
 #include "ops.h"
 
@@ -39,90 +40,29 @@ __global__ void timestep_sinusoid_kernel(float t, int dim, int B, float* __restr
   }
 }
 
-// conv_in: one thread per (pixel, 8 output channels); weights staged in shared memory as [k][Cout]
+// NCFHW (io dtype) -> channels-last bf16 rows [B*F*HW, Cpad] (channels >= Cin are zero): the tensor-core conv_in reads
+// the latent as a 64-channel image. One thread per (pixel, 8-channel vector): 16-byte coalesced stores.
 template <typename T>
-__global__ void __launch_bounds__(256)
-conv_in_kernel(const T* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
-               __nv_bfloat16* __restrict__ y, int B, int Cin, int F, int H, int W, int Cout) {
-  extern __shared__ float sw[];  // [Cin*9][Cout]
-  const int K = Cin * 9;
-  for (int i = threadIdx.x; i < K * Cout; i += blockDim.x) {
-    const int co = i % Cout, k = i / Cout;  // k = ci*9 + tap  (PyTorch [Cout][Cin][3][3])
-    sw[i] = w[(int64_t)co * K + k];
-  }
-  __syncthreads();
-  const int vecs = Cout >> 3;
-  const int64_t total = (int64_t)B * F * H * W * vecs;
+__global__ void ncfhw_to_rows_kernel(const T* __restrict__ x, __nv_bfloat16* __restrict__ y, int B, int Cin, int F,
+                                     int64_t HW, int Cpad) {
+  const int vecs = Cpad >> 3;
+  const int64_t total = (int64_t)B * F * HW * vecs;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int v = (int)(i % vecs);
-    int64_t p = i / vecs;
-    const int xx = (int)(p % W); p /= W;
-    const int yy = (int)(p % H); p /= H;
-    const int f = (int)(p % F);
-    const int b = (int)(p / F);
-    float acc[8];
+    const int64_t row = i / vecs;
+    const int64_t pix = row % HW;
+    const int64_t n = row / HW;
+    const int64_t b = n / F, f = n % F;
+    float e[8];
 #pragma unroll
-    for (int j = 0; j < 8; ++j) acc[j] = bias[v * 8 + j];
-    for (int ci = 0; ci < Cin; ++ci) {
-      const T* plane = x + (((int64_t)b * Cin + ci) * F + f) * H * W;
-#pragma unroll
-      for (int tap = 0; tap < 9; ++tap) {
-        const int iy = yy + tap / 3 - 1, ix = xx + tap % 3 - 1;
-        if (iy < 0 || iy >= H || ix < 0 || ix >= W) continue;
-        const float xv = DT<T>::ld(plane + (int64_t)iy * W + ix);
-        const float* wr = sw + (ci * 9 + tap) * Cout + v * 8;
-#pragma unroll
-        for (int j = 0; j < 8; ++j) acc[j] += xv * wr[j];
-      }
+    for (int j = 0; j < 8; ++j) {
+      const int ci = v * 8 + j;
+      e[j] = ci < Cin ? DT<T>::ld(x + ((b * Cin + ci) * F + f) * HW + pix) : 0.f;
     }
     uint4 o;
-    o.x = pack_bf16x2(acc[0], acc[1]); o.y = pack_bf16x2(acc[2], acc[3]);
-    o.z = pack_bf16x2(acc[4], acc[5]); o.w = pack_bf16x2(acc[6], acc[7]);
-    // row = ((b*F + f)*H + yy)*W + xx  == i / vecs
-    *reinterpret_cast<uint4*>(y + (i / vecs) * Cout + v * 8) = o;
-  }
-}
-
-// conv_out: one warp per output pixel, lanes split the input channels; weights [Cout][9][Cin] in smem
-template <typename T>
-__global__ void __launch_bounds__(256)
-conv_out_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ w, const float* __restrict__ bias,
-                T* __restrict__ y, int B, int Cin, int F, int H, int W, int Cout) {
-  extern __shared__ float sw[];  // [Cout][9][Cin]
-  for (int i = threadIdx.x; i < Cout * 9 * Cin; i += blockDim.x) sw[i] = w[i];
-  __syncthreads();
-  const int lane = threadIdx.x & 31;
-  const int vecs = Cin >> 3;
-  const int64_t npix = (int64_t)B * F * H * W;
-  const int64_t warp0 = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  for (int64_t pix = warp0; pix < npix; pix += nwarps) {
-    int64_t p = pix;
-    const int xx = (int)(p % W); p /= W;
-    const int yy = (int)(p % H); p /= H;
-    const int f = (int)(p % F);
-    const int b = (int)(p / F);
-    float acc[4] = {0.f, 0.f, 0.f, 0.f};  // Cout <= 4
-    for (int tap = 0; tap < 9; ++tap) {
-      const int iy = yy + tap / 3 - 1, ix = xx + tap % 3 - 1;
-      if (iy < 0 || iy >= H || ix < 0 || ix >= W) continue;
-      const __nv_bfloat16* src = x + ((((int64_t)b * F + f) * H + iy) * W + ix) * Cin;
-      for (int v = lane; v < vecs; v += 32) {
-        const uint4 u = __ldg(reinterpret_cast<const uint4*>(src + v * 8));
-        const float2 a = unpack_bf16x2(u.x), bb = unpack_bf16x2(u.y), c = unpack_bf16x2(u.z), d = unpack_bf16x2(u.w);
-        const float xv[8] = {a.x, a.y, bb.x, bb.y, c.x, c.y, d.x, d.y};
-        for (int co = 0; co < Cout; ++co) {
-          const float* wr = sw + ((co * 9 + tap) * Cin) + v * 8;
-#pragma unroll
-          for (int j = 0; j < 8; ++j) acc[co] += xv[j] * wr[j];
-        }
-      }
-    }
-    for (int co = 0; co < Cout; ++co) acc[co] = warp_sum(acc[co]);
-    if (lane == 0) {
-      for (int co = 0; co < Cout; ++co)
-        DT<T>::st(y + ((((int64_t)b * Cout + co) * F + f) * H + yy) * W + xx, acc[co] + bias[co]);
-    }
+    o.x = pack_bf16x2(e[0], e[1]); o.y = pack_bf16x2(e[2], e[3]);
+    o.z = pack_bf16x2(e[4], e[5]); o.w = pack_bf16x2(e[6], e[7]);
+    reinterpret_cast<uint4*>(y)[i] = o;
   }
 }
 
@@ -163,36 +103,14 @@ int time_embedding(float timestep, int B, int dim0, const float* w1, const float
   return 0;
 }
 
-int conv_in_3x3(const void* x, int io_dtype, const float* w, const float* bias, void* y, int B, int Cin, int F,
-                int H, int W, int Cout, cudaStream_t s) {
-  B2V_CHECK(Cout % 8 == 0 && Cin * 9 * Cout * 4 <= 200 * 1024, "conv_in: unsupported channels %d -> %d", Cin, Cout);
-  const size_t shb = sizeof(float) * (size_t)Cin * 9 * Cout;
-  const int64_t total = (int64_t)B * F * H * W * (Cout >> 3);
+int ncfhw_to_rows(const void* x, int io_dtype, void* y, int B, int Cin, int F, int64_t HW, int Cpad, cudaStream_t s) {
+  B2V_CHECK(Cpad % 8 == 0 && Cin <= Cpad, "ncfhw_to_rows: bad channels %d -> %d", Cin, Cpad);
+  const int64_t total = (int64_t)B * F * HW * (Cpad >> 3);
   int64_t grid = (total + 255) / 256;
-  const int64_t cap = (int64_t)sm_count() * 4;
+  const int64_t cap = (int64_t)sm_count() * 16;
   if (grid > cap) grid = cap;
-  B2V_DISPATCH_DTYPE(io_dtype, T, {
-    B2V_CUDA_OK(cudaFuncSetAttribute(conv_in_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shb));
-    conv_in_kernel<T><<<(unsigned)grid, 256, shb, s>>>((const T*)x, w, bias, (__nv_bfloat16*)y, B, Cin, F, H, W, Cout);
-  });
-  count_launch();
-  B2V_CUDA_OK(launch_check());
-  return 0;
-}
-
-int conv_out_3x3(const void* x, const float* w, const float* bias, void* y, int io_dtype, int B, int Cin, int F,
-                 int H, int W, int Cout, cudaStream_t s) {
-  B2V_CHECK(Cin % 8 == 0 && Cout <= 4 && Cout * 9 * Cin * 4 <= 200 * 1024, "conv_out: unsupported channels %d -> %d",
-            Cin, Cout);
-  const size_t shb = sizeof(float) * (size_t)Cout * 9 * Cin;
-  const int64_t npix = (int64_t)B * F * H * W;
-  int64_t grid = (npix + 7) / 8;
-  const int64_t cap = (int64_t)sm_count() * 4;
-  if (grid > cap) grid = cap;
-  B2V_DISPATCH_DTYPE(io_dtype, T, {
-    B2V_CUDA_OK(cudaFuncSetAttribute(conv_out_kernel<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)shb));
-    conv_out_kernel<T><<<(unsigned)grid, 256, shb, s>>>((const __nv_bfloat16*)x, w, bias, (T*)y, B, Cin, F, H, W, Cout);
-  });
+  B2V_DISPATCH_DTYPE(io_dtype, T, (ncfhw_to_rows_kernel<T><<<(unsigned)grid, 256, 0, s>>>((const T*)x, (__nv_bfloat16*)y, B,
+                                                                                     Cin, F, HW, Cpad)));
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;

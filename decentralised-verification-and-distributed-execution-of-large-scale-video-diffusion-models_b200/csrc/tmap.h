@@ -9,6 +9,9 @@ namespace b2v {
 // bf16 tensor, 128-byte swizzle, zero fill out of bounds.
 int tmap_tiled_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                     const uint32_t* box);
+// same, 128-byte swizzle or none (row pitch = box[0] elements; used by the epilogue's TMA stores)
+int tmap_tiled_bf16_sw(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
+                       const uint32_t* box, bool swizzle128);
 int tmap_im2col_bf16(CUtensorMap* out, const void* base, int rank, const uint64_t* dims, const uint64_t* strides_bytes,
                      const int* lower, const int* upper, uint32_t channels_per_pixel, uint32_t pixels_per_column,
                      const uint32_t* elem_strides);
@@ -41,6 +44,10 @@ struct ConvArgs {
   const void* residual = nullptr;
   void* out = nullptr;  // bf16 [N,P,Q,Cout]
   int N = 0, H = 0, W = 0, Cin = 0, Cout = 0, stride = 1;
+  // conv_out: write the first ncfhw_cout channels as [B, ncfhw_cout, F, H, W] of ncfhw_dtype instead of bf16 rows
+  // (N = B*F images; the weight is zero-padded to Cout = 64 rows)
+  void* ncfhw_out = nullptr;
+  int ncfhw_dtype = 0, ncfhw_cout = 0, ncfhw_F = 1;
 };
 
 int pick_bn(int N, bool geglu);

@@ -44,6 +44,18 @@ __global__ void permute_taps_kernel(const float* __restrict__ in, TO* __restrict
     DT<TO>::st(out + i, in[((int64_t)co * Cin + ci) * taps + tap]);
   }
 }
+// [Cout][Cin][taps] fp32 -> [CoutPad][taps][CinPad] bf16, zero padded (conv_in: Cin 4 -> 64; conv_out: Cout 4 -> 64)
+__global__ void permute_taps_pad_kernel(const float* __restrict__ in, bf16* __restrict__ out, int Cout, int Cin,
+                                        int taps, int CoutPad, int CinPad) {
+  const int64_t n = (int64_t)CoutPad * CinPad * taps;
+  for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
+    const int ci = (int)(i % CinPad);
+    const int tap = (int)((i / CinPad) % taps);
+    const int co = (int)(i / ((int64_t)CinPad * taps));
+    const float v = (co < Cout && ci < Cin) ? in[((int64_t)co * Cin + ci) * taps + tap] : 0.f;
+    out[i] = __float2bfloat16_rn(v);
+  }
+}
 // GEGLU: proj.weight rows [0,H) are the value half, [H,2H) the gate half (H = 4*dim).
 // packed row j*256 + i       (i < 128) = value row j*128 + i
 // packed row j*256 + 128 + i (i < 128) = gate  row j*128 + i
@@ -172,13 +184,13 @@ struct b2v_unet3d {
   std::vector<void*> owned;                                             // packed device allocations
 
   // packed
-  float *conv_in_w = nullptr, *conv_in_b = nullptr;
+  Conv conv_in;   // [C0][9][64] bf16, input channels zero padded to one 64-channel TMA block
+  Conv conv_out;  // [64][9][C0] bf16, output channels zero padded to the narrowest MMA tile
   float *te_w1 = nullptr, *te_b1 = nullptr, *te_w2 = nullptr, *te_b2 = nullptr;
   TemporalW transformer_in;
   std::vector<LevelW> down, up;
   LevelW mid;
   Norm norm_out;
-  float *conv_out_w = nullptr, *conv_out_b = nullptr;
   int temb_dim = 0;
   static constexpr int kMaxB = 8;
   float* temb_scratch = nullptr;  // [kMaxB*temb] silu(emb) + sinusoid + hidden
@@ -389,9 +401,9 @@ void gn(Ctx& c, const bf16* x1, int C1, const bf16* x2, int C2, const Norm& n, b
 }
 
 void conv(Ctx& c, const bf16* x, int N, int H, int W, const Conv& w, int stride, const float* rowbias,
-          int64_t rows_per_group, const bf16* residual, bf16* out) {
+          int64_t rows_per_group, const bf16* residual, bf16* out, int real_cin = 0) {
   const int P = (H - 1) / stride + 1, Q = (W - 1) / stride + 1;
-  c.flops += 2.0 * (double)N * P * Q * w.Cout * 9.0 * w.Cin;
+  c.flops += 2.0 * (double)N * P * Q * w.Cout * 9.0 * (real_cin ? real_cin : w.Cin);  // algorithmic: padding not counted
   if (!c.live()) return;
   ConvArgs a;
   a.x = x; a.w = w.w; a.bias = w.b; a.rowbias = rowbias; a.rows_per_group = rows_per_group; a.residual = residual;
@@ -580,8 +592,12 @@ int forward_impl(b2v_unet3d* u, Ctx& c, const void* sample, float timestep, cons
   }
 
   Act x{c.act((int64_t)N * H * W, C0), (int64_t)N * H * W, C0, H, W};
-  if (c.live()) c.run(conv_in_3x3(sample, io_dtype, u->conv_in_w, u->conv_in_b, x.p, B, cfg.in_channels, F, H, W, C0, c.s));
-  c.flops += 2.0 * (double)N * H * W * C0 * 9.0 * cfg.in_channels;
+  {
+    bf16* xin = c.act((int64_t)N * H * W, u->conv_in.Cin);
+    if (c.live()) c.run(ncfhw_to_rows(sample, io_dtype, xin, B, cfg.in_channels, F, (int64_t)H * W, u->conv_in.Cin, c.s));
+    conv(c, xin, N, H, W, u->conv_in, 1, nullptr, 0, nullptr, x.p, cfg.in_channels);
+    c.free(xin);
+  }
   {
     Act y = temporal(c, u->transformer_in, x);
     c.free(x.p);
@@ -665,7 +681,12 @@ int forward_impl(b2v_unet3d* u, Ctx& c, const void* sample, float timestep, cons
   gn(c, x.p, x.C, nullptr, 0, u->norm_out, hn, N, (int64_t)x.H * x.W, cfg.norm_eps, 1);
   c.free(x.p);
   c.flops += 2.0 * (double)N * H * W * cfg.out_channels * 9.0 * C0;
-  if (c.live()) c.run(conv_out_3x3(hn, u->conv_out_w, u->conv_out_b, out, io_dtype, B, C0, F, H, W, cfg.out_channels, c.s));
+  if (c.live()) {
+    ConvArgs a;
+    a.x = hn; a.w = u->conv_out.w; a.bias = u->conv_out.b; a.N = N; a.H = H; a.W = W; a.Cin = C0; a.Cout = u->conv_out.Cout;
+    a.stride = 1; a.ncfhw_out = out; a.ncfhw_dtype = io_dtype; a.ncfhw_cout = cfg.out_channels; a.ncfhw_F = F;
+    c.run(conv3x3_im2col(a, c.s));
+  }
   c.free(hn);
   c.free(text);
   return c.status;
@@ -686,7 +707,8 @@ extern "C" int b2v_unet3d_create(const b2v_unet3d_config* cfg, b2v_unet3d** out)
   B2V_CHECK(cfg->attention_head_dim == 64, "attention_head_dim must be 64");
   B2V_CHECK(cfg->cross_attention_dim % 64 == 0 && cfg->norm_num_groups > 0 && cfg->layers_per_block >= 1,
             "bad config");
-  B2V_CHECK(cfg->out_channels <= 4 && cfg->in_channels >= 1, "in/out channels unsupported");
+  B2V_CHECK(cfg->out_channels >= 1 && cfg->out_channels <= 16 && cfg->in_channels >= 1 && cfg->in_channels <= 64,
+            "in/out channels unsupported");
   auto* u = new b2v_unet3d();
   u->cfg = *cfg;
   cudaGetDevice(&u->device);
@@ -748,9 +770,11 @@ extern "C" int b2v_unet3d_finalize(b2v_unet3d* u) {
   // stem
   {
     const float* w = L.get("conv_in.weight", {ch[0], cfg.in_channels, 3, 3});
-    u->conv_in_w = L.dalloc<float>((size_t)ch[0] * cfg.in_channels * 9);
-    if (w) cudaMemcpy(u->conv_in_w, w, sizeof(float) * (size_t)ch[0] * cfg.in_channels * 9, cudaMemcpyDeviceToDevice);
-    u->conv_in_b = L.vec("conv_in.bias", ch[0]);
+    u->conv_in.Cout = ch[0]; u->conv_in.Cin = 64;
+    u->conv_in.w = L.dalloc<bf16>((size_t)ch[0] * 64 * 9);
+    if (w && u->conv_in.w)
+      permute_taps_pad_kernel<<<ew_grid((int64_t)ch[0] * 64 * 9), 256>>>(w, u->conv_in.w, ch[0], cfg.in_channels, 9, ch[0], 64);
+    u->conv_in.b = L.vec("conv_in.bias", ch[0]);
     auto mat = [&](const char* nm, int N, int K) {
       const float* s = L.get(nm, {N, K});
       float* d = L.dalloc<float>((size_t)N * K);
@@ -823,10 +847,11 @@ extern "C" int b2v_unet3d_finalize(b2v_unet3d* u) {
   u->norm_out = L.norm("conv_norm_out", ch[0]);
   {
     const float* w = L.get("conv_out.weight", {cfg.out_channels, ch[0], 3, 3});
-    u->conv_out_w = L.dalloc<float>((size_t)cfg.out_channels * ch[0] * 9);
-    if (w && u->conv_out_w)
-      permute_taps_kernel<float><<<ew_grid((int64_t)cfg.out_channels * ch[0] * 9), 256>>>(w, u->conv_out_w, cfg.out_channels, ch[0], 9);
-    u->conv_out_b = L.vec("conv_out.bias", cfg.out_channels);
+    u->conv_out.Cout = 64; u->conv_out.Cin = ch[0];
+    u->conv_out.w = L.dalloc<bf16>((size_t)64 * ch[0] * 9);
+    if (w && u->conv_out.w)
+      permute_taps_pad_kernel<<<ew_grid((int64_t)64 * ch[0] * 9), 256>>>(w, u->conv_out.w, cfg.out_channels, ch[0], 9, 64, ch[0]);
+    u->conv_out.b = L.vec("conv_out.bias", cfg.out_channels);
   }
   cudaError_t e = cudaDeviceSynchronize();
   if (!L.err.empty()) return fail(B2V_ERR_STATE, "%s", L.err.c_str());

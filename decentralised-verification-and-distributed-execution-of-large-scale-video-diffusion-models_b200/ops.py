@@ -175,14 +175,15 @@ def spotcheck_ddim(z_list, eps_list, znext_list, a_t, a_prev, C_, F, hw):
 
 # ---- building-block ops (tests) --------------------------------------------------------------------------------
 def gemm(a, w, bias=None, rowbias=None, rows_per_group=0, residual=None, taps=1, tap_row_stride=0, rows_per_batch=0,
-         flags=0):
+         flags=0, out=None):
     lib = _lib.load()
     _cuda(a); _cuda(w)
     M, Kc = a.shape
     N = w.shape[0]
     assert w.shape[1] == taps * Kc
     n_out = N // 2 if flags & _lib.EPI_GEGLU else N
-    out = torch.empty((M, n_out), dtype=torch.bfloat16, device=a.device)
+    if out is None:
+        out = torch.empty((M, n_out), dtype=torch.bfloat16, device=a.device)
     check(lib.b2v_op_gemm(ptr(a), ptr(w), ptr(bias), ptr(rowbias), int(rows_per_group), ptr(residual), ptr(out), M, N,
                           Kc, taps, int(tap_row_stride), int(rows_per_batch), int(flags), stream()))
     return out

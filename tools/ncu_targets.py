@@ -1,0 +1,43 @@
+"""GPU box: launch each hot kernel ONCE on its dominant shape (for `ncu --set full`); prints nothing but timings.
+usage: python tools/ncu_targets.py [gemm|attn|norm|all]"""
+import math
+import sys
+
+import torch
+
+sys.path.insert(0, ".")
+import b2v  # noqa: E402
+from b2v import ops, _lib  # noqa: E402
+
+what = sys.argv[1] if len(sys.argv) > 1 else "all"
+dev = torch.device("cuda:0")
+M = 294912
+
+
+def t(fn, name):
+    fn()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    fn()
+    e1.record()
+    torch.cuda.synchronize()
+    print("%-40s %.3f ms" % (name, e0.elapsed_time(e1)), flush=True)
+
+
+if what in ("gemm", "all"):
+    for (m, n, k, flags, r) in [(M, 960, 320, 0, 0), (M, 320, 320, 0, 1), (M, 2560, 320, 1, 0), (18432, 3840, 1280, 0, 0)]:
+        a = torch.randn(m, k, device=dev).bfloat16()
+        w = (torch.randn(n, k, device=dev) / math.sqrt(k)).bfloat16()
+        bias = torch.zeros(n, device=dev)
+        out = torch.randn(m, n // 2 if flags & 1 else n, device=dev).bfloat16()
+        t(lambda: ops.gemm(a, w, bias=bias, residual=out if r else None, flags=flags, out=out), "gemm %d %d %d f%d r%d" % (m, n, k, flags, r))
+if what in ("attn", "all"):
+    nb, heads, S = 8, 5, 9216
+    q, k, v = (torch.randn(nb, S, heads * 64, device=dev).bfloat16() for _ in range(3))
+    t(lambda: ops.attention(q, k, v, heads), "attention nb=8 h=5 S=9216")
+if what in ("norm", "all"):
+    x = torch.randn(M, 320, device=dev).bfloat16()
+    g, b = torch.ones(320, device=dev), torch.zeros(320, device=dev)
+    t(lambda: ops.group_norm(x, g, b, 32, 32, 1e-5, True), "group_norm+silu L0 (items=32)")
+    t(lambda: ops.layer_norm(x, g, b), "layer_norm L0")
