@@ -39,7 +39,7 @@ constexpr int SMEM_LIMIT = 227 * 1024;
 // per epilogue warp] [barriers]. An epilogue warp owns 32 rows x GROUP_COLS columns of the tile and hands them to the
 // TMA store engine in panels of PANEL_COLS columns: 64 (128-byte rows, 128B swizzle, conflict-free writes) when the
 // group width allows it, else the whole group width unswizzled (BN = 160 -> 80 columns, BN = 64 -> 32).
-template <int BN, bool GEGLU>
+template <int BN, bool GEGLU, bool RES>
 struct TileCfg {
   static constexpr int B_BYTES = BN * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
@@ -49,8 +49,10 @@ struct TileCfg {
   static constexpr int PANEL_COLS = (GROUP_COLS % 64 == 0) ? 64 : GROUP_COLS;
   static constexpr bool PANEL_SWIZZLE = PANEL_COLS == 64;
   static constexpr int PANEL_BYTES = PANEL_COLS * 2 * 32;
-  static constexpr int EPI_BYTES = EPI_WARPS * PANEL_BYTES;
-  static constexpr int FIXED = EPI_BYTES + 256 /*barriers*/ + 1024 /*alignment slack*/;
+  static constexpr int NPANELS = GROUP_COLS / PANEL_COLS;
+  static constexpr int NBUF = (RES && NPANELS == 1) ? 2 : 1;  // residual of the next tile prefetched into the other buffer
+  static constexpr int EPI_BYTES = EPI_WARPS * NBUF * PANEL_BYTES;
+  static constexpr int FIXED = EPI_BYTES + 512 /*barriers*/ + 1024 /*alignment slack*/;
   static constexpr int STAGES_FIT = (SMEM_LIMIT - FIXED) / STAGE_BYTES;
   static constexpr int STAGES = STAGES_FIT > 8 ? 8 : STAGES_FIT;
   static constexpr int SMEM_BYTES = STAGES * STAGE_BYTES + FIXED;
@@ -105,156 +107,214 @@ __device__ __forceinline__ float gelu_fast(float x) {
   return 0.5f * x * phi2;
 }
 
-// One epilogue warp handles 32 rows (its TMEM lane quarter) x half of the tile's output columns (group 0 / 1), in
-// 16-column chunks: tcgen05.ld of chunk c+1 and the residual loads of chunk c+1 are in flight while chunk c is
-// computed and stored (the residual of the first chunk is fetched before the accumulator is even complete).
-template <int BN, bool GEGLU>
-__device__ __forceinline__ void epilogue_tile(const GemmParams& p, const CUtensorMap* tmO, uint8_t* stage, int lane,
-                                              int row0, int slab, uint32_t tacc, int64_t grow, bool valid, int n_tile,
-                                              int group, uint32_t tfull_bar, uint32_t tfull_phase) {
-  using Cfg = TileCfg<BN, GEGLU>;
+// Epilogue warp role. One warp handles 32 rows (its TMEM lane quarter) x half of the tile's output columns (group 0 / 1)
+// in 16-column chunks: tcgen05.ld of chunk c+1 is in flight while chunk c is computed. Results are staged in the warp's
+// own shared-memory panel and leave as TMA stores (full 128-byte lines instead of 16-byte scattered stores: the L0
+// GEMMs were bound by the LSU/L2 request rate of the latter). With RES the residual panel ARRIVES in the same buffer by
+// TMA load and is updated in place; when a tile is one panel wide (all but BN = 256) two buffers alternate so the
+// residual of the NEXT tile is already in flight while this one is processed.
+template <int BN, int MODE, bool GEGLU, bool RES>
+__device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtensorMap* tmO, const CUtensorMap* tmR,
+                                              uint8_t* stage0, uint32_t rbar0, uint32_t tmem_base, uint32_t tfull0,
+                                              uint32_t tempty0, int warp, int lane, int num_tiles) {
+  using Cfg = TileCfg<BN, GEGLU, RES>;
   constexpr int OUT_COLS = Cfg::OUT_COLS;
   constexpr int NCH = OUT_COLS / 32;  // 16-column chunks per group
   constexpr int CH_PER_PANEL = Cfg::PANEL_COLS / 16;
-  uint8_t* srow = stage + lane * (Cfg::PANEL_COLS * 2);
+  constexpr int NBUF = Cfg::NBUF;
+  const int quarter = warp & 3;
+  const int group = (warp - 2) >> 2;
   const int c_base = group * NCH * 16;
-  const int64_t ocol0 = (int64_t)n_tile * OUT_COLS + c_base;
-  const int wcol0 = n_tile * BN + c_base;  // column in the (packed) weight / bias space
-  const bool has_res = p.residual != nullptr && valid;
-  const uint4* res4 = reinterpret_cast<const uint4*>(p.residual + (has_res ? grow * p.ldo + ocol0 : 0));
-  const float* rb = (!GEGLU && p.rowbias) ? p.rowbias + (grow / p.rows_per_group) * (int64_t)p.N + wcol0 : nullptr;
+  const int lane_off = lane * (Cfg::PANEL_COLS * 2);
 
-  // the whole residual row-half is fetched up front (before the accumulator is complete): maximum loads in flight, and
-  // no load is outstanding on a 128-byte line when this thread stores to it — with the in-place residual the UNet uses
-  // (out == residual) an interleaved load/store on the same line serialises in the LSU (measured 2x slower).
-  uint4 res[NCH][2];
-  if (has_res) {
-#pragma unroll
-    for (int i = 0; i < NCH; ++i) { res[i][0] = res4[2 * i]; res[i][1] = res4[2 * i + 1]; }
-  }
-  mbar_wait(tfull_bar, tfull_phase);
-  tc_fence_after();
-  uint32_t v[2][16];
-  uint32_t g[GEGLU ? 2 : 1][16];
-  tmem_ld16(tacc + c_base, v[0]);
-  if constexpr (GEGLU) tmem_ld16(tacc + BN / 2 + c_base, g[0]);
-#pragma unroll
-  for (int ch = 0; ch < NCH; ++ch) {
-    const int cur = ch & 1, nxt = cur ^ 1;
-    const int c = ch * 16;
-    tmem_wait_ld();
-    if (ch + 1 < NCH) {
-      tmem_ld16(tacc + c_base + c + 16, v[nxt]);
-      if constexpr (GEGLU) tmem_ld16(tacc + BN / 2 + c_base + c + 16, g[nxt]);
+  // TMA coordinates of this warp's part of a tile: (first column, first row inside the slab, slab)
+  auto tile_col = [&](int tile) { return (tile % p.num_n_tiles) * OUT_COLS + c_base; };
+  auto tile_row0 = [&](int tile) {
+    const int m_tile = tile / p.num_n_tiles;
+    return (MODE == 0 ? (m_tile % p.m_tiles_per_batch) : m_tile) * BM + quarter * 32;
+  };
+  auto tile_slab = [&](int tile) { return MODE == 0 ? (tile / p.num_n_tiles) / p.m_tiles_per_batch : 0; };
+  auto load_residual = [&](int tile, int panel, int buf) {  // one lane
+    const uint32_t bar = rbar0 + 8 * buf;
+    mbar_expect_tx(bar, Cfg::PANEL_BYTES);
+    tma_load_3d(smem_u32(stage0 + buf * Cfg::PANEL_BYTES), tmR, bar, tile_col(tile) + panel * Cfg::PANEL_COLS,
+                tile_row0(tile), tile_slab(tile));
+  };
+
+  uint32_t q = 0;  // panels processed by this warp so far: buffer q % NBUF, residual barrier parity (q / NBUF) & 1
+  if (RES && NBUF == 2 && lane == 0 && (int)blockIdx.x < num_tiles) load_residual(blockIdx.x, 0, 0);
+  int acc = 0;
+  uint32_t acc_phase = 0;
+  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    const int n_tile = tile % p.num_n_tiles;
+    const int row0 = tile_row0(tile), slab = tile_slab(tile);
+    const int ocol0 = tile_col(tile);
+    const int wcol0 = n_tile * BN + c_base;  // column in the (packed) weight / bias space
+    const float* rb = nullptr;
+    if (!GEGLU && p.rowbias) {
+      const int64_t grow = (MODE == 0 ? (int64_t)slab * p.rows_per_batch : 0) + row0 + lane;
+      const int64_t gclamped = grow < p.M ? grow : p.M - 1;  // rows past the end are clipped by the store
+      rb = p.rowbias + (gclamped / p.rows_per_group) * (int64_t)p.N + wcol0;
     }
-    float f[16];
+    const uint32_t tacc = tmem_base + acc * Cfg::ACC_STRIDE + ((uint32_t)(quarter * 32) << 16);
+    uint32_t v[2][16];
+    uint32_t g[GEGLU ? 2 : 1][16];
 #pragma unroll
-    for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[cur][j]);
-    if (p.bias) {
-      const float4* b4 = reinterpret_cast<const float4*>(p.bias + wcol0 + c);
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        const float4 b = __ldg(b4 + j);
-        f[4 * j] += b.x; f[4 * j + 1] += b.y; f[4 * j + 2] += b.z; f[4 * j + 3] += b.w;
+    for (int ch = 0; ch < NCH; ++ch) {
+      const int cur = ch & 1, nxt = cur ^ 1;
+      const int c = ch * 16;
+      const int k = ch % CH_PER_PANEL, panel = ch / CH_PER_PANEL;
+      const int buf = q % NBUF;
+      uint8_t* srow = stage0 + buf * Cfg::PANEL_BYTES + lane_off;
+      if (k == 0) {
+        // ---- panel start: the buffer(s) about to be (over)written must have been read out by their TMA store ----
+        if (lane == 0) {
+          bulk_wait_read0();
+          if (RES) {
+            if (NBUF == 2) {
+              if (tile + (int)gridDim.x < num_tiles) load_residual(tile + gridDim.x, 0, buf ^ 1);
+            } else {
+              load_residual(tile, panel, 0);
+            }
+          }
+        }
+        __syncwarp();
+        if (ch == 0) {
+          mbar_wait(tfull0 + 8 * acc, acc_phase);
+          tc_fence_after();
+          tmem_ld16(tacc + c_base, v[0]);
+          if constexpr (GEGLU) tmem_ld16(tacc + BN / 2 + c_base, g[0]);
+        }
+        if (RES) mbar_wait(rbar0 + 8 * buf, (q / NBUF) & 1);
       }
-    }
-    if constexpr (GEGLU) {
-      float gt[16];
+      tmem_wait_ld();
+      if (ch + 1 < NCH) {
+        tmem_ld16(tacc + c_base + c + 16, v[nxt]);
+        if constexpr (GEGLU) tmem_ld16(tacc + BN / 2 + c_base + c + 16, g[nxt]);
+      }
+      float f[16];
 #pragma unroll
-      for (int j = 0; j < 16; ++j) gt[j] = __uint_as_float(g[cur][j]);
+      for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[cur][j]);
       if (p.bias) {
-        const float4* b4 = reinterpret_cast<const float4*>(p.bias + wcol0 + BN / 2 + c);
+        const float4* b4 = reinterpret_cast<const float4*>(p.bias + wcol0 + c);
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const float4 b = __ldg(b4 + j);
-          gt[4 * j] += b.x; gt[4 * j + 1] += b.y; gt[4 * j + 2] += b.z; gt[4 * j + 3] += b.w;
-        }
-      }
-#pragma unroll
-      for (int j = 0; j < 16; ++j) f[j] *= gelu_fast(gt[j]);
-    } else {
-      if (rb) {
-        const float4* r4 = reinterpret_cast<const float4*>(rb + c);
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const float4 b = __ldg(r4 + j);
           f[4 * j] += b.x; f[4 * j + 1] += b.y; f[4 * j + 2] += b.z; f[4 * j + 3] += b.w;
         }
       }
-      if (p.gelu) {
+      if constexpr (GEGLU) {
+        float gt[16];
 #pragma unroll
-        for (int j = 0; j < 16; ++j) f[j] = gelu_fast(f[j]);
+        for (int j = 0; j < 16; ++j) gt[j] = __uint_as_float(g[cur][j]);
+        if (p.bias) {
+          const float4* b4 = reinterpret_cast<const float4*>(p.bias + wcol0 + BN / 2 + c);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float4 b = __ldg(b4 + j);
+            gt[4 * j] += b.x; gt[4 * j + 1] += b.y; gt[4 * j + 2] += b.z; gt[4 * j + 3] += b.w;
+          }
+        }
+#pragma unroll
+        for (int j = 0; j < 16; ++j) f[j] *= gelu_fast(gt[j]);
+      } else {
+        if (rb) {
+          const float4* r4 = reinterpret_cast<const float4*>(rb + c);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float4 b = __ldg(r4 + j);
+            f[4 * j] += b.x; f[4 * j + 1] += b.y; f[4 * j + 2] += b.z; f[4 * j + 3] += b.w;
+          }
+        }
+        if (p.gelu) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) f[j] = gelu_fast(f[j]);
+        }
       }
-    }
-    if (has_res) {
+      // ---- the 16 columns are two 16-byte pieces of this lane's panel row (128B-swizzled when the panel is 64 wide) ----
 #pragma unroll
       for (int j = 0; j < 2; ++j) {
-        const uint4 r = res[ch][j];
-        const float2 a = unpack_bf16x2(r.x), b = unpack_bf16x2(r.y), cc = unpack_bf16x2(r.z), d = unpack_bf16x2(r.w);
-        f[8 * j] += a.x; f[8 * j + 1] += a.y; f[8 * j + 2] += b.x; f[8 * j + 3] += b.y;
-        f[8 * j + 4] += cc.x; f[8 * j + 5] += cc.y; f[8 * j + 6] += d.x; f[8 * j + 7] += d.y;
+        const int piece = 2 * k + j;
+        const int pos = Cfg::PANEL_SWIZZLE ? (piece ^ (lane & 7)) : piece;
+        uint4* dst = reinterpret_cast<uint4*>(srow + (pos << 4));
+        if (RES) {
+          const uint4 r = *dst;
+          const float2 a = unpack_bf16x2(r.x), b = unpack_bf16x2(r.y), cc = unpack_bf16x2(r.z), d = unpack_bf16x2(r.w);
+          f[8 * j] += a.x; f[8 * j + 1] += a.y; f[8 * j + 2] += b.x; f[8 * j + 3] += b.y;
+          f[8 * j + 4] += cc.x; f[8 * j + 5] += cc.y; f[8 * j + 6] += d.x; f[8 * j + 7] += d.y;
+        }
+        uint4 o;
+        o.x = pack_bf16x2(f[8 * j], f[8 * j + 1]);
+        o.y = pack_bf16x2(f[8 * j + 2], f[8 * j + 3]);
+        o.z = pack_bf16x2(f[8 * j + 4], f[8 * j + 5]);
+        o.w = pack_bf16x2(f[8 * j + 6], f[8 * j + 7]);
+        *dst = o;
+      }
+      if (k == CH_PER_PANEL - 1) {
+        // ---- panel complete: ONE TMA store of 32 rows x PANEL_COLS (rows outside the tensor / slab are clipped) ----
+        fence_proxy_async_smem();
+        __syncwarp();
+        if (lane == 0) {
+          tma_store_3d(tmO, smem_u32(stage0 + buf * Cfg::PANEL_BYTES), ocol0 + panel * Cfg::PANEL_COLS, row0, slab);
+          bulk_commit();
+        }
+        ++q;
       }
     }
-    // ---- stage the 16 columns in this warp's panel buffer; a full panel goes out as ONE TMA store (32 rows x
-    // PANEL_COLS, rows outside the tensor / slab are clipped by the tensor map) ----
-    const int k = ch % CH_PER_PANEL;
-    if (k == 0) {
-      if (lane == 0) bulk_wait_read0();  // the previous store from this buffer has been read out
-      __syncwarp();
-    }
-#pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      uint4 o;
-      o.x = pack_bf16x2(f[8 * j], f[8 * j + 1]);
-      o.y = pack_bf16x2(f[8 * j + 2], f[8 * j + 3]);
-      o.z = pack_bf16x2(f[8 * j + 4], f[8 * j + 5]);
-      o.w = pack_bf16x2(f[8 * j + 6], f[8 * j + 7]);
-      const int piece = 2 * k + j;
-      const int pos = Cfg::PANEL_SWIZZLE ? (piece ^ (lane & 7)) : piece;
-      *reinterpret_cast<uint4*>(srow + (pos << 4)) = o;
-    }
-    if (k == CH_PER_PANEL - 1) {
-      fence_proxy_async_smem();
-      __syncwarp();
-      if (lane == 0) {
-        tma_store_3d(tmO, smem_u32(stage), (int)ocol0 + (ch / CH_PER_PANEL) * Cfg::PANEL_COLS, row0, slab);
-        bulk_commit();
-      }
-    }
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
+    if (++acc == 2) { acc = 0; acc_phase ^= 1; }
   }
+  if (lane == 0) bulk_wait0();  // this warp's TMA stores have drained before its shared memory goes away
 }
 
 // conv_out epilogue: only the first nc_cout (<= 16) accumulator columns are real; thread = pixel writes one element per
 // output channel plane (consecutive lanes -> consecutive pixels: coalesced), fp32 bias add, one rounding to the io dtype.
-__device__ __forceinline__ void epilogue_ncfhw(const GemmParams& p, uint32_t tacc, int64_t grow, bool valid, int group,
-                                               uint32_t tfull_bar, uint32_t tfull_phase) {
-  mbar_wait(tfull_bar, tfull_phase);
-  tc_fence_after();
-  if (group != 0) return;
-  uint32_t v[16];
-  tmem_ld16(tacc, v);
-  tmem_wait_ld();
-  if (!valid) return;
-  const int64_t n = grow / p.nc_HW, pix = grow % p.nc_HW;
-  const int64_t b = n / p.nc_F, f = n % p.nc_F;
+template <int ACC_STRIDE>
+__device__ __forceinline__ void epilogue_loop_ncfhw(const GemmParams& p, uint32_t tmem_base, uint32_t tfull0,
+                                                    uint32_t tempty0, int warp, int lane, int num_tiles) {
+  const int quarter = warp & 3;
+  const int group = (warp - 2) >> 2;
+  int acc = 0;
+  uint32_t acc_phase = 0;
+  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+    const int m_tile = tile / p.num_n_tiles;
+    const int64_t grow = (int64_t)m_tile * BM + quarter * 32 + lane;
+    mbar_wait(tfull0 + 8 * acc, acc_phase);
+    tc_fence_after();
+    if (group == 0) {
+      uint32_t v[16];
+      tmem_ld16(tmem_base + acc * ACC_STRIDE + ((uint32_t)(quarter * 32) << 16), v);
+      tmem_wait_ld();
+      if (grow < p.M) {
+        const int64_t n = grow / p.nc_HW, pix = grow % p.nc_HW;
+        const int64_t b = n / p.nc_F, f = n % p.nc_F;
 #pragma unroll
-  for (int co = 0; co < 16; ++co) {
-    if (co < p.nc_cout) {
-      const float val = __uint_as_float(v[co]) + (p.bias ? __ldg(p.bias + co) : 0.f);
-      const int64_t idx = ((b * p.nc_cout + co) * p.nc_F + f) * p.nc_HW + pix;
-      if (p.nc_dtype == B2V_F32) reinterpret_cast<float*>(p.out_raw)[idx] = val;
-      else if (p.nc_dtype == B2V_F16) reinterpret_cast<__half*>(p.out_raw)[idx] = __float2half_rn(val);
-      else reinterpret_cast<__nv_bfloat16*>(p.out_raw)[idx] = __float2bfloat16_rn(val);
+        for (int co = 0; co < 16; ++co) {
+          if (co < p.nc_cout) {
+            const float val = __uint_as_float(v[co]) + (p.bias ? __ldg(p.bias + co) : 0.f);
+            const int64_t idx = ((b * p.nc_cout + co) * p.nc_F + f) * p.nc_HW + pix;
+            if (p.nc_dtype == B2V_F32) reinterpret_cast<float*>(p.out_raw)[idx] = val;
+            else if (p.nc_dtype == B2V_F16) reinterpret_cast<__half*>(p.out_raw)[idx] = __float2half_rn(val);
+            else reinterpret_cast<__nv_bfloat16*>(p.out_raw)[idx] = __float2bfloat16_rn(val);
+          }
+        }
+      }
     }
+    tc_fence_before();
+    __syncwarp();
+    if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
+    if (++acc == 2) { acc = 0; acc_phase ^= 1; }
   }
 }
 
 // MODE 0: A through a 3-D tiled tensor map (channels, rows, slabs); MODE 1: A through a 4-D im2col map.
-template <int BN, int MODE, int EPI>
+template <int BN, int MODE, int EPI, bool RES>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
-            const __grid_constant__ CUtensorMap tmO, const GemmParams p) {
-  using Cfg = TileCfg<BN, EPI == EPI_GEGLU_T>;
+            const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR, const GemmParams p) {
+  using Cfg = TileCfg<BN, EPI == EPI_GEGLU_T, RES>;
   constexpr int STAGES = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -262,10 +322,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   uint8_t* sB = smem + STAGES * A_BYTES;
   uint8_t* sEpi = smem + STAGES * Cfg::STAGE_BYTES;
   uint64_t* bars = reinterpret_cast<uint64_t*>(sEpi + Cfg::EPI_BYTES);
-  // bars: [0,STAGES) full, [STAGES,2*STAGES) empty, then tmem_full[2], tmem_empty[2], then the TMEM base slot
+  // bars: [0,STAGES) full, [STAGES,2*STAGES) empty, tmem_full[2], tmem_empty[2], the TMEM base slot, residual[8 warps][2]
   const uint32_t full0 = smem_u32(bars), empty0 = smem_u32(bars + STAGES);
   const uint32_t tfull0 = smem_u32(bars + 2 * STAGES), tempty0 = smem_u32(bars + 2 * STAGES + 2);
   uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 2 * STAGES + 4);
+  const uint32_t rbar0 = smem_u32(bars + 2 * STAGES + 5);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kb_per_tap = p.Kc / BK;
@@ -276,6 +337,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     prefetch_tmap(&tmA);
     prefetch_tmap(&tmB);
     prefetch_tmap(&tmO);
+    if (RES) prefetch_tmap(&tmR);
     for (int i = 0; i < STAGES; ++i) {
       mbar_init(full0 + 8 * i, 1);
       mbar_init(empty0 + 8 * i, 1);
@@ -284,6 +346,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
       mbar_init(tfull0 + 8 * i, 1);
       mbar_init(tempty0 + 8 * i, 8);
     }
+    for (int i = 0; i < 2 * EPI_WARPS; ++i) mbar_init(rbar0 + 8 * i, 1);
     fence_barrier_init();
   }
   if (warp == 1) {
@@ -363,37 +426,12 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
   } else {
     // ===================== epilogue (warps 2..9 -> TMEM lane quarters 2,3,0,1,2,3,0,1; column halves 0,0,0,0,1,1,1,1) ====
-    const int quarter = warp & 3;
-    const int group = (warp - 2) >> 2;
-    int acc = 0;
-    uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      const int n_tile = tile % p.num_n_tiles, m_tile = tile / p.num_n_tiles;
-      int64_t grow;
-      bool valid;
-      int slab = 0, row0;  // TMA-store coordinates of this warp's first row: row inside the slab, slab
-      if (MODE == 0) {
-        slab = m_tile / p.m_tiles_per_batch;
-        row0 = (m_tile % p.m_tiles_per_batch) * BM + quarter * 32;
-        const int64_t r = (int64_t)row0 + lane;
-        valid = r < p.rows_per_batch;
-        grow = (int64_t)slab * p.rows_per_batch + r;
-      } else {
-        row0 = m_tile * BM + quarter * 32;
-        grow = (int64_t)row0 + lane;
-        valid = grow < p.M;
-      }
-      const uint32_t tacc = tmem_base + acc * Cfg::ACC_STRIDE + ((uint32_t)(quarter * 32) << 16);
-      if constexpr (EPI == EPI_NCFHW) epilogue_ncfhw(p, tacc, grow, valid, group, tfull0 + 8 * acc, acc_phase);
-      else
-        epilogue_tile<BN, EPI == EPI_GEGLU_T>(p, &tmO, sEpi + (warp - 2) * Cfg::PANEL_BYTES, lane, row0, slab, tacc, grow,
-                                              valid, n_tile, group, tfull0 + 8 * acc, acc_phase);
-      tc_fence_before();
-      __syncwarp();
-      if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
-      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
-    }
-    if (lane == 0) bulk_wait0();  // this warp's TMA stores have drained before its shared memory goes away
+    if constexpr (EPI == EPI_NCFHW)
+      epilogue_loop_ncfhw<Cfg::ACC_STRIDE>(p, tmem_base, tfull0, tempty0, warp, lane, num_tiles);
+    else
+      epilogue_loop<BN, MODE, EPI == EPI_GEGLU_T, RES>(p, &tmO, &tmR, sEpi + (warp - 2) * Cfg::NBUF * Cfg::PANEL_BYTES,
+                                                       rbar0 + 16 * (warp - 2), tmem_base, tfull0, tempty0, warp, lane,
+                                                       num_tiles);
   }
 
   tc_fence_before();
@@ -404,45 +442,53 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   }
 }
 
-template <int BN, int MODE, int EPI>
+template <int BN, int MODE, int EPI, bool RES>
 int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int64_t out_rows_per_slab,
                 int64_t out_slabs, cudaStream_t s) {
-  using Cfg = TileCfg<BN, EPI == EPI_GEGLU_T>;
-  CUtensorMap tmO = tmA;  // EPI_NCFHW stores with plain instructions
+  using Cfg = TileCfg<BN, EPI == EPI_GEGLU_T, RES>;
+  CUtensorMap tmO = tmA, tmR = tmA;  // EPI_NCFHW stores with plain instructions
   if (EPI != EPI_NCFHW) {
     const int n_out = EPI == EPI_GEGLU_T ? p.N / 2 : p.N;
     const uint64_t dims[3] = {(uint64_t)n_out, (uint64_t)out_rows_per_slab, (uint64_t)out_slabs};
     const uint64_t strides[2] = {(uint64_t)p.ldo * 2, (uint64_t)out_rows_per_slab * (uint64_t)p.ldo * 2};
     const uint32_t box[3] = {(uint32_t)Cfg::PANEL_COLS, 32, 1};
     B2V_TRY(tmap_tiled_bf16_sw(&tmO, p.out, 3, dims, strides, box, Cfg::PANEL_SWIZZLE));
+    if (RES) B2V_TRY(tmap_tiled_bf16_sw(&tmR, p.residual, 3, dims, strides, box, Cfg::PANEL_SWIZZLE));
   }
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(gemm_kernel<BN, MODE, EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    attr_err = cudaFuncSetAttribute(gemm_kernel<BN, MODE, EPI, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     Cfg::SMEM_BYTES);
   });
   if (attr_err != cudaSuccess) return fail(B2V_ERR_CUDA, "gemm smem attr: %s", cudaGetErrorString(attr_err));
   const int tiles = p.num_m_tiles * p.num_n_tiles;
   const int grid = tiles < sm_count() ? tiles : sm_count();
-  gemm_kernel<BN, MODE, EPI><<<grid, NUM_THREADS, Cfg::SMEM_BYTES, s>>>(tmA, tmB, tmO, p);
+  gemm_kernel<BN, MODE, EPI, RES><<<grid, NUM_THREADS, Cfg::SMEM_BYTES, s>>>(tmA, tmB, tmO, tmR, p);
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;
+}
+
+template <int BN, int MODE>
+int launch_plain(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int64_t orows, int64_t oslabs,
+                 cudaStream_t s) {
+  if (p.residual) return launch_gemm<BN, MODE, EPI_PLAIN, true>(tmA, tmB, p, orows, oslabs, s);
+  return launch_gemm<BN, MODE, EPI_PLAIN, false>(tmA, tmB, p, orows, oslabs, s);
 }
 
 template <int MODE>
 int dispatch_gemm(int bn, bool geglu, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
                   int64_t orows, int64_t oslabs, cudaStream_t s) {
   if (geglu) {
-    if (bn == 256) return launch_gemm<256, MODE, EPI_GEGLU_T>(tmA, tmB, p, orows, oslabs, s);
+    if (bn == 256) return launch_gemm<256, MODE, EPI_GEGLU_T, false>(tmA, tmB, p, orows, oslabs, s);
     return fail(B2V_ERR_ARG, "GEGLU epilogue needs N %% 256 == 0");
   }
   switch (bn) {
-    case 256: return launch_gemm<256, MODE, EPI_PLAIN>(tmA, tmB, p, orows, oslabs, s);
-    case 160: return launch_gemm<160, MODE, EPI_PLAIN>(tmA, tmB, p, orows, oslabs, s);
-    case 128: return launch_gemm<128, MODE, EPI_PLAIN>(tmA, tmB, p, orows, oslabs, s);
-    case 64: return launch_gemm<64, MODE, EPI_PLAIN>(tmA, tmB, p, orows, oslabs, s);
+    case 256: return launch_plain<256, MODE>(tmA, tmB, p, orows, oslabs, s);
+    case 160: return launch_plain<160, MODE>(tmA, tmB, p, orows, oslabs, s);
+    case 128: return launch_plain<128, MODE>(tmA, tmB, p, orows, oslabs, s);
+    case 64: return launch_plain<64, MODE>(tmA, tmB, p, orows, oslabs, s);
   }
   return fail(B2V_ERR_ARG, "no tile for N");
 }
@@ -474,6 +520,7 @@ int gemm_tiled(const GemmArgs& g, cudaStream_t s) {
   B2V_CHECK(bn != 0, "GEMM N=%d has no supported tile (needs a multiple of 64; GEGLU of 256)", g.N);
   B2V_CHECK(g.Kc % BK == 0 && g.Kc > 0, "GEMM Kc=%d must be a multiple of 64", g.Kc);
   B2V_CHECK(g.taps == 1 || g.taps == 3, "tiled GEMM supports 1 or 3 taps");
+  B2V_CHECK(!(geglu && (g.residual || g.rowbias)), "the GEGLU epilogue takes no residual / row bias");
   const int64_t rpb = g.rows_per_batch > 0 ? g.rows_per_batch : g.M;
   B2V_CHECK(g.M > 0 && g.M % rpb == 0, "M must be slabs x rows_per_batch");
   const int64_t lda = g.lda > 0 ? g.lda : g.Kc;
@@ -550,7 +597,7 @@ int conv3x3_im2col(const ConvArgs& c, cudaStream_t s) {
               "conv NCFHW epilogue: needs a 64-row padded weight, <= 16 real channels, stride 1");
     p.out_raw = c.ncfhw_out; p.nc_dtype = c.ncfhw_dtype; p.nc_cout = c.ncfhw_cout; p.nc_F = c.ncfhw_F;
     p.nc_HW = (int64_t)P * Q;
-    return launch_gemm<64, 1, EPI_NCFHW>(tmA, tmB, p, p.M, 1, s);
+    return launch_gemm<64, 1, EPI_NCFHW, false>(tmA, tmB, p, p.M, 1, s);
   }
   return dispatch_gemm<1>(bn, false, tmA, tmB, p, p.M, 1, s);
 }
