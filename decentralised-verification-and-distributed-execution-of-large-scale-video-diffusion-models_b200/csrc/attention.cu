@@ -28,6 +28,7 @@ __device__ __forceinline__ float ex2(float x) {
 // CTA's softmax and vice versa)
 //   warp 0: TMA producer   warp 1: MMA issuer   warps 2-5: softmax (thread = query row)
 // smem: Q 16K | K 2x16K | V 2x16K | P 32K      TMEM: S cols [0,128)   O cols [128,192) (accumulates over kv tiles)
+// S(j+1) is computed while softmax(j) runs: the softmax warps release the S columns right after loading them.
 // Softmax is single pass: the S row (128 fp32) is held in registers; the exponent uses a *stale* running maximum
 // that is only refreshed (and O rescaled in TMEM) when the true maximum has moved by more than 2^8 — the final
 // O / l is exact either way, and O never round-trips through registers in the steady state.
@@ -56,8 +57,8 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
   uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 7 * AT_TILE);
   const uint32_t q_full = smem_u32(bars + 0), k_full0 = smem_u32(bars + 1), v_full0 = smem_u32(bars + 3),
                  kv_empty0 = smem_u32(bars + 5), s_full = smem_u32(bars + 7), p_full = smem_u32(bars + 8),
-                 o_full = smem_u32(bars + 9);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 10);
+                 o_full = smem_u32(bars + 9), s_free = smem_u32(bars + 10);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q0 = blockIdx.x * 128, h = blockIdx.y, b = blockIdx.z;
@@ -74,6 +75,7 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     mbar_init(s_full, 1);
     mbar_init(p_full, 4);
     mbar_init(o_full, 1);
+    mbar_init(s_free, 4);
     fence_barrier_init();
   }
   if (warp == 1) { tmem_alloc(smem_u32(tmem_slot), AT_TMEM_COLS); tmem_relinquish(); }
@@ -116,7 +118,14 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     issue_qk(0);
     for (int j = 0; j < nkv; ++j) {
       const int st = j & 1;
-      mbar_wait(p_full, j & 1);   // P(j) is in smem, S(j) has been consumed, O has been rescaled if it had to be
+      // S(j+1) = Q K(j+1)^T is issued as soon as the softmax warps have pulled S(j) into registers, so it runs on the
+      // tensor core UNDER softmax(j) and the softmax warps never wait for a score tile in the steady state
+      if (j + 1 < nkv) {
+        mbar_wait(s_free, j & 1);
+        tc_fence_after();
+        issue_qk(j + 1);
+      }
+      mbar_wait(p_full, j & 1);   // P(j) is in smem, O has been rescaled if it had to be
       mbar_wait(v_full0 + 8 * st, (j >> 1) & 1);
       tc_fence_after();
       if (elect_one()) {
@@ -131,7 +140,6 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
         umma_commit(kv_empty0 + 8 * st);
       }
       __syncwarp();
-      if (j + 1 < nkv) issue_qk(j + 1);
     }
   } else {
     const int quarter = warp & 3;
@@ -151,6 +159,9 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       tmem_ld32(tS + lane_off + 64, sv + 64);
       tmem_ld32(tS + lane_off + 96, sv + 96);
       tmem_wait_ld();
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(s_free);  // the S tile is in registers: the tensor core may overwrite it
       const int kv_left = p.Skv - j * 128;  // valid kv columns in this block
       if (kv_left < 128) {
 #pragma unroll

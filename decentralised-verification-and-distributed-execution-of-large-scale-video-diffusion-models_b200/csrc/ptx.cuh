@@ -32,6 +32,8 @@ __device__ __forceinline__ void mbar_expect_tx(uint32_t bar, uint32_t bytes) {
 __device__ __forceinline__ void mbar_arrive(uint32_t bar) {
   asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
+// try_wait suspends the warp in hardware until the phase completes or an implementation-defined time limit expires (an
+// explicit suspend-time hint measured slightly slower: later wake-ups).
 __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
   uint32_t ok;
   asm volatile(
@@ -43,12 +45,18 @@ __device__ __forceinline__ bool mbar_try_wait(uint32_t bar, uint32_t parity) {
       : "memory");
   return ok != 0;
 }
-// Bounded wait: a protocol bug becomes a trap (reported as a CUDA error) instead of a hung GPU.
+// Bounded wait: a protocol bug becomes a trap (reported as a CUDA error) instead of a hung GPU. The clock is read once
+// per 256 failed tries only.
 __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   if (mbar_try_wait(bar, parity)) return;
-  const long long t0 = clock64();
-  while (!mbar_try_wait(bar, parity)) {
-    if (clock64() - t0 > 8000000000LL) {
+  long long t0 = 0;
+  for (;;) {
+#pragma unroll 1
+    for (int i = 0; i < 256; ++i)
+      if (mbar_try_wait(bar, parity)) return;
+    const long long now = clock64();
+    if (t0 == 0) t0 = now;
+    if (now - t0 > 8000000000LL) {
       printf("b2v: mbarrier wait timeout (block %d thread %d bar %u parity %u)\n", (int)blockIdx.x,
              (int)threadIdx.x, bar, parity);
       __trap();
