@@ -12,70 +12,67 @@ namespace b2v {
 namespace {
 
 // ---------------- GroupNorm ----------------
-// pass 1: per-(item, group) sum / sum of squares. grid = (row_splits, n_items); block = 64 x 4 threads:
-// threadIdx.x walks the 8-channel vectors of a row (coalesced 1 KiB per 64 threads), threadIdx.y the rows.
-// C/groups is always even, so a bf16 pair never straddles two groups. DETERMINISTIC on purpose (the commitment
-// re-executes steps bit-for-bit): per-thread pair partials go to shared memory, one thread per group folds them in a
-// fixed order, each CTA writes its partial to its own slot, and gn_finalize_kernel folds the slots sequentially in
-// fp64 — no atomics anywhere.
-constexpr int GN_TX = 64, GN_TY = 4, GN_THREADS = GN_TX * GN_TY;
+// Thread mapping of both passes: a CTA is vecs x rpp threads (vecs = C/8 16-byte vectors per row, rpp rows per pass), so
+// EVERY lane owns one fixed 8-channel vector and walks rows; GN_UNROLL rows are loaded before any is consumed (the
+// kernels are pure HBM streams: the loads in flight per SM set the bandwidth). grid = (row_splits, n_items).
+// pass 1: per-(item, group) sum / sum of squares. C/groups is always even, so a bf16 pair never straddles two groups.
+// DETERMINISTIC on purpose (the commitment re-executes steps bit-for-bit): per-thread pair partials go to shared
+// memory, one thread per group folds them in a fixed order, each CTA writes its partial to its own slot, and
+// gn_finalize_kernel folds the slots sequentially in fp64 — no atomics anywhere.
+constexpr int GN_MAX_THREADS = 384, GN_UNROLL = 4;
 
-template <int ITERS>
-__global__ void __launch_bounds__(GN_THREADS)
+__device__ __forceinline__ uint4 gn_load(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat16* __restrict__ x2,
+                                         int C2, int64_t grow, int c) {
+  if (c < C1) return __ldg(reinterpret_cast<const uint4*>(x1 + grow * C1 + c));
+  return __ldg(reinterpret_cast<const uint4*>(x2 + grow * C2 + (c - C1)));
+}
+
+__global__ void __launch_bounds__(GN_MAX_THREADS)
 gn_stats_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat16* __restrict__ x2, int C2,
-                int64_t rows_per_item, int groups, float* __restrict__ partial /*[item][split][group][2]*/) {
-  extern __shared__ float sh[];  // [2][GN_TY][C/2]
+                int64_t rows_per_item, int groups, int rpp, float* __restrict__ partial /*[item][split][group][2]*/) {
+  extern __shared__ float sh[];  // [2][rpp][C/2]
   const int C = C1 + C2;
-  const int pairs = C >> 1;
+  const int vecs = C >> 3, pairs = C >> 1;
   const int cpg = C / groups;
   const int item = blockIdx.y;
-  const int tx = threadIdx.x & (GN_TX - 1), ty = threadIdx.x / GN_TX;
+  const int ty = threadIdx.x / vecs, tx = threadIdx.x - ty * vecs;
+  const int c = tx << 3;
   const int64_t rows_per_cta = (rows_per_item + gridDim.x - 1) / gridDim.x;
   const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta;
   int64_t r1 = r0 + rows_per_cta;
   if (r1 > rows_per_item) r1 = rows_per_item;
-  float s[ITERS][4], ss[ITERS][4];
+  const int64_t base = (int64_t)item * rows_per_item;
+  float s[4] = {0.f, 0.f, 0.f, 0.f}, ss[4] = {0.f, 0.f, 0.f, 0.f};
+  for (int64_t r = r0 + ty; r < r1; r += (int64_t)rpp * GN_UNROLL) {
+    uint4 u[GN_UNROLL];
 #pragma unroll
-  for (int i = 0; i < ITERS; ++i)
+    for (int k = 0; k < GN_UNROLL; ++k) {
+      const int64_t rr = r + (int64_t)k * rpp;
+      u[k] = rr < r1 ? gn_load(x1, C1, x2, C2, base + rr, c) : make_uint4(0, 0, 0, 0);
+    }
 #pragma unroll
-    for (int j = 0; j < 4; ++j) { s[i][j] = 0.f; ss[i][j] = 0.f; }
-  for (int64_t r = r0 + ty; r < r1; r += GN_TY) {
-    const int64_t grow = (int64_t)item * rows_per_item + r;
+    for (int k = 0; k < GN_UNROLL; ++k) {
+      const uint32_t uu[4] = {u[k].x, u[k].y, u[k].z, u[k].w};
 #pragma unroll
-    for (int i = 0; i < ITERS; ++i) {
-      const int c = (tx + i * GN_TX) << 3;
-      if (c < C) {
-        uint4 u;
-        if (c < C1) u = __ldg(reinterpret_cast<const uint4*>(x1 + grow * C1 + c));
-        else u = __ldg(reinterpret_cast<const uint4*>(x2 + grow * C2 + (c - C1)));
-        const uint32_t uu[4] = {u.x, u.y, u.z, u.w};
-#pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const float2 f = unpack_bf16x2(uu[j]);
-          s[i][j] += f.x + f.y;
-          ss[i][j] += f.x * f.x + f.y * f.y;
-        }
+      for (int j = 0; j < 4; ++j) {
+        const float2 f = unpack_bf16x2(uu[j]);
+        s[j] += f.x + f.y;
+        ss[j] += f.x * f.x + f.y * f.y;
       }
     }
   }
   float* shs = sh;
-  float* shq = sh + GN_TY * pairs;
+  float* shq = sh + rpp * pairs;
 #pragma unroll
-  for (int i = 0; i < ITERS; ++i) {
-    const int c = (tx + i * GN_TX) << 3;
-    if (c < C) {
-#pragma unroll
-      for (int j = 0; j < 4; ++j) {
-        shs[ty * pairs + (c >> 1) + j] = s[i][j];
-        shq[ty * pairs + (c >> 1) + j] = ss[i][j];
-      }
-    }
+  for (int j = 0; j < 4; ++j) {
+    shs[ty * pairs + (c >> 1) + j] = s[j];
+    shq[ty * pairs + (c >> 1) + j] = ss[j];
   }
   __syncthreads();
   const int ppg = cpg >> 1;
-  for (int g = threadIdx.x; g < groups; g += GN_THREADS) {
+  for (int g = threadIdx.x; g < groups; g += blockDim.x) {
     float a = 0.f, q = 0.f;
-    for (int y = 0; y < GN_TY; ++y)
+    for (int y = 0; y < rpp; ++y)
       for (int k = 0; k < ppg; ++k) {
         a += shs[y * pairs + g * ppg + k];
         q += shq[y * pairs + g * ppg + k];
@@ -128,50 +125,48 @@ __device__ __forceinline__ float silu_fast(float x) {
 }
 
 // pass 2: y = x * scale + shift with scale = rstd*gamma, shift = beta - mean*rstd*gamma folded once per thread
-// (a thread owns fixed 8-channel vectors and walks rows), optional SiLU. Same grid shape as the stats pass.
-template <int ITERS>
-__global__ void __launch_bounds__(GN_THREADS)
+// (a thread owns one fixed 8-channel vector and walks rows), optional SiLU. Same mapping / grid as the stats pass.
+__global__ void __launch_bounds__(GN_MAX_THREADS)
 gn_apply_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat16* __restrict__ x2, int C2,
                 const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
-                int64_t rows_per_item, int groups, int silu, const float2* __restrict__ stats) {
+                int64_t rows_per_item, int groups, int rpp, int silu, const float2* __restrict__ stats) {
   const int C = C1 + C2;
+  const int vecs = C >> 3;
   const int cpg = C / groups;
   const int item = blockIdx.y;
-  const int tx = threadIdx.x & (GN_TX - 1), ty = threadIdx.x / GN_TX;
+  const int ty = threadIdx.x / vecs, tx = threadIdx.x - ty * vecs;
+  const int c = tx << 3;
   const int64_t rows_per_cta = (rows_per_item + gridDim.x - 1) / gridDim.x;
   const int64_t r0 = (int64_t)blockIdx.x * rows_per_cta;
   int64_t r1 = r0 + rows_per_cta;
   if (r1 > rows_per_item) r1 = rows_per_item;
-  float sc[ITERS][8], sh[ITERS][8];
+  const int64_t base = (int64_t)item * rows_per_item;
+  float sc[8], sh[8];
 #pragma unroll
-  for (int i = 0; i < ITERS; ++i) {
-    const int c = (tx + i * GN_TX) << 3;
-    if (c < C) {
-#pragma unroll
-      for (int j = 0; j < 8; ++j) {
-        const float2 st = __ldg(stats + (int64_t)item * groups + (c + j) / cpg);
-        const float gm = __ldg(gamma + c + j), bt = __ldg(beta + c + j);
-        sc[i][j] = st.y * gm;
-        sh[i][j] = fmaf(-st.x, st.y * gm, bt);
-      }
-    }
+  for (int j = 0; j < 8; ++j) {
+    const float2 st = __ldg(stats + (int64_t)item * groups + (c + j) / cpg);
+    const float gm = __ldg(gamma + c + j), bt = __ldg(beta + c + j);
+    sc[j] = st.y * gm;
+    sh[j] = fmaf(-st.x, st.y * gm, bt);
   }
-  for (int64_t r = r0 + ty; r < r1; r += GN_TY) {
-    const int64_t grow = (int64_t)item * rows_per_item + r;
+  for (int64_t r = r0 + ty; r < r1; r += (int64_t)rpp * GN_UNROLL) {
+    uint4 u[GN_UNROLL];
 #pragma unroll
-    for (int i = 0; i < ITERS; ++i) {
-      const int c = (tx + i * GN_TX) << 3;
-      if (c < C) {
-        uint4 u;
-        if (c < C1) u = __ldg(reinterpret_cast<const uint4*>(x1 + grow * C1 + c));
-        else u = __ldg(reinterpret_cast<const uint4*>(x2 + grow * C2 + (c - C1)));
-        const uint32_t uu[4] = {u.x, u.y, u.z, u.w};
+    for (int k = 0; k < GN_UNROLL; ++k) {
+      const int64_t rr = r + (int64_t)k * rpp;
+      if (rr < r1) u[k] = gn_load(x1, C1, x2, C2, base + rr, c);
+    }
+#pragma unroll
+    for (int k = 0; k < GN_UNROLL; ++k) {
+      const int64_t rr = r + (int64_t)k * rpp;
+      if (rr < r1) {
+        const uint32_t uu[4] = {u[k].x, u[k].y, u[k].z, u[k].w};
         float f[8];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
           const float2 t = unpack_bf16x2(uu[j]);
-          f[2 * j] = fmaf(t.x, sc[i][2 * j], sh[i][2 * j]);
-          f[2 * j + 1] = fmaf(t.y, sc[i][2 * j + 1], sh[i][2 * j + 1]);
+          f[2 * j] = fmaf(t.x, sc[2 * j], sh[2 * j]);
+          f[2 * j + 1] = fmaf(t.y, sc[2 * j + 1], sh[2 * j + 1]);
         }
         if (silu) {
 #pragma unroll
@@ -180,54 +175,59 @@ gn_apply_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat1
         uint4 o;
         o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
         o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
-        *reinterpret_cast<uint4*>(y + grow * C + c) = o;
+        *reinterpret_cast<uint4*>(y + (base + rr) * C + c) = o;
       }
     }
   }
 }
 
-// ---------------- LayerNorm: one warp per row, row cached in registers ----------------
-template <int MAXV>  // max 8-channel vectors per lane
+// ---------------- LayerNorm: LPR lanes per row, V 16-byte vectors per lane, row cached in registers ----------------
+// A warp handles 32/LPR rows at once; lane l of a row group loads vectors l, l+LPR, ... (each load instruction reads
+// LPR*16 contiguous bytes per row: full sectors, every lane busy, V independent loads in flight per lane).
+template <int LPR, int V>
 __global__ void __launch_bounds__(256)
 layer_norm_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
                   __nv_bfloat16* __restrict__ y, int64_t rows, int C, float eps) {
+  constexpr int RPW = 32 / LPR;  // rows per warp
   const int lane = threadIdx.x & 31;
+  const int sub = lane / LPR, l = lane % LPR;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
   const int64_t nwarps = ((int64_t)gridDim.x * blockDim.x) >> 5;
-  const int vecs = C >> 3;
-  for (int64_t r = warp; r < rows; r += nwarps) {
-    float f[MAXV][8];
+  const float inv_c = 1.0f / (float)C;
+  for (int64_t r0 = warp * RPW; r0 < rows; r0 += nwarps * RPW) {
+    const int64_t r = r0 + sub;
+    const bool live = r < rows;
+    uint4 u[V];
+#pragma unroll
+    for (int i = 0; i < V; ++i)
+      u[i] = live ? __ldg(reinterpret_cast<const uint4*>(x + r * C + ((l + LPR * i) << 3))) : make_uint4(0, 0, 0, 0);
+    float f[V][8];
     float s = 0.f;
 #pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
-      const int v = lane + 32 * i;
-      if (v < vecs) {
-        const uint4 u = __ldg(reinterpret_cast<const uint4*>(x + r * C + (v << 3)));
-        const uint32_t uu[4] = {u.x, u.y, u.z, u.w};
+    for (int i = 0; i < V; ++i) {
+      const uint32_t uu[4] = {u[i].x, u[i].y, u[i].z, u[i].w};
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const float2 t = unpack_bf16x2(uu[j]);
-          f[i][2 * j] = t.x; f[i][2 * j + 1] = t.y;
-          s += t.x + t.y;
-        }
+      for (int j = 0; j < 4; ++j) {
+        const float2 t = unpack_bf16x2(uu[j]);
+        f[i][2 * j] = t.x; f[i][2 * j + 1] = t.y;
+        s += t.x + t.y;
       }
     }
-    const float mean = warp_sum(s) / (float)C;
+#pragma unroll
+    for (int o = LPR / 2; o > 0; o >>= 1) s += __shfl_xor_sync(0xffffffffu, s, o);
+    const float mean = s * inv_c;
     float ss = 0.f;
 #pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
-      const int v = lane + 32 * i;
-      if (v < vecs) {
+    for (int i = 0; i < V; ++i)
 #pragma unroll
-        for (int j = 0; j < 8; ++j) { const float d = f[i][j] - mean; ss += d * d; }
-      }
-    }
-    const float rstd = rsqrtf(warp_sum(ss) / (float)C + eps);
+      for (int j = 0; j < 8; ++j) { const float d = f[i][j] - mean; ss += d * d; }
 #pragma unroll
-    for (int i = 0; i < MAXV; ++i) {
-      const int v = lane + 32 * i;
-      if (v < vecs) {
-        const int c = v << 3;
+    for (int o = LPR / 2; o > 0; o >>= 1) ss += __shfl_xor_sync(0xffffffffu, ss, o);
+    const float rstd = rsqrtf(ss * inv_c + eps);
+    if (live) {
+#pragma unroll
+      for (int i = 0; i < V; ++i) {
+        const int c = (l + LPR * i) << 3;
         const float4 g0 = __ldg(reinterpret_cast<const float4*>(gamma + c)), g1 = __ldg(reinterpret_cast<const float4*>(gamma + c + 4));
         const float4 b0 = __ldg(reinterpret_cast<const float4*>(beta + c)), b1 = __ldg(reinterpret_cast<const float4*>(beta + c + 4));
         const float gm[8] = {g0.x, g0.y, g0.z, g0.w, g1.x, g1.y, g1.z, g1.w};
@@ -235,10 +235,10 @@ layer_norm_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__
         float o[8];
 #pragma unroll
         for (int j = 0; j < 8; ++j) o[j] = (f[i][j] - mean) * rstd * gm[j] + bt[j];
-        uint4 u;
-        u.x = pack_bf16x2(o[0], o[1]); u.y = pack_bf16x2(o[2], o[3]);
-        u.z = pack_bf16x2(o[4], o[5]); u.w = pack_bf16x2(o[6], o[7]);
-        *reinterpret_cast<uint4*>(y + r * C + c) = u;
+        uint4 w;
+        w.x = pack_bf16x2(o[0], o[1]); w.y = pack_bf16x2(o[2], o[3]);
+        w.z = pack_bf16x2(o[4], o[5]); w.w = pack_bf16x2(o[6], o[7]);
+        *reinterpret_cast<uint4*>(y + r * C + c) = w;
       }
     }
   }
@@ -295,9 +295,16 @@ inline int grid_1d(int64_t work_items, int block, int per_sm) {
 
 }  // namespace
 
+// rows per pass: as many as fit GN_MAX_THREADS threads of one 16-byte vector each
+static int gn_rpp(int C) {
+  const int vecs = C >> 3;
+  int rpp = GN_MAX_THREADS / vecs;
+  return rpp < 1 ? 1 : rpp;
+}
+
 int gn_splits(int64_t n_items, int64_t rows_per_item) {
-  // enough CTAs per item to fill the machine ~4x, at least 32 rows each
-  int64_t splits = ((int64_t)sm_count() * 4 + n_items - 1) / n_items;
+  // enough CTAs per item to fill the machine ~6x (<= 384-thread CTAs, 5-6 resident per SM), at least 32 rows each
+  int64_t splits = ((int64_t)sm_count() * 6 + n_items - 1) / n_items;
   const int64_t max_splits = (rows_per_item + 31) / 32;
   if (splits > max_splits) splits = max_splits;
   if (splits < 1) splits = 1;
@@ -314,43 +321,26 @@ int group_norm(const void* x1, int C1, const void* x2, int C2, const float* gamm
                cudaStream_t s) {
   const int C = C1 + C2;
   B2V_CHECK(C % 8 == 0 && C1 % 8 == 0 && C % groups == 0 && (C / groups) % 2 == 0, "group_norm: C=%d (C1=%d) groups=%d unsupported", C, C1, groups);
+  B2V_CHECK(C <= GN_MAX_THREADS * 8, "group_norm: C=%d too wide (max %d)", C, GN_MAX_THREADS * 8);
   B2V_CHECK(n_items > 0 && n_items < 65536 && rows_per_item > 0, "group_norm: bad item count");
   const int splits = gn_splits(n_items, rows_per_item);
   float* partial = (float*)scratch;
   const size_t pbytes = sizeof(float) * 2 * (size_t)n_items * splits * groups;
   float2* stats = (float2*)((uint8_t*)scratch + ((pbytes + 255) & ~(size_t)255));
   dim3 grid((unsigned)splits, (unsigned)n_items);
-  const int iters = ((C >> 3) + GN_TX - 1) / GN_TX;
-  const size_t shb = sizeof(float) * 2 * GN_TY * (C >> 1);
-#define B2V_GN_STATS(I)                                                                                     \
-  gn_stats_kernel<I><<<grid, GN_THREADS, shb, s>>>((const __nv_bfloat16*)x1, C1, (const __nv_bfloat16*)x2, C2, \
-                                                   rows_per_item, groups, partial)
-#define B2V_GN_APPLY(I)                                                                                      \
-  gn_apply_kernel<I><<<grid, GN_THREADS, 0, s>>>((const __nv_bfloat16*)x1, C1, (const __nv_bfloat16*)x2, C2, gamma, \
-                                                 beta, (__nv_bfloat16*)y, rows_per_item, groups, silu, stats)
-  switch (iters) {
-    case 1: B2V_GN_STATS(1); break;
-    case 2: B2V_GN_STATS(2); break;
-    case 3: B2V_GN_STATS(3); break;
-    case 4: B2V_GN_STATS(4); break;
-    case 5: B2V_GN_STATS(5); break;
-    default: return fail(B2V_ERR_ARG, "group_norm: C=%d too wide (max 2560)", C);
-  }
+  const int rpp = gn_rpp(C);
+  const int threads = (C >> 3) * rpp;
+  const size_t shb = sizeof(float) * 2 * rpp * (C >> 1);
+  gn_stats_kernel<<<grid, threads, shb, s>>>((const __nv_bfloat16*)x1, C1, (const __nv_bfloat16*)x2, C2, rows_per_item,
+                                            groups, rpp, partial);
   count_launch();
   const int64_t ng = n_items * groups;
   gn_finalize_kernel<<<(unsigned)((ng * 32 + 127) / 128), 128, 0, s>>>(partial, splits, groups, n_items,
                                                                        (double)rows_per_item * (double)(C / groups), eps,
                                                                        stats);
   count_launch();
-  switch (iters) {
-    case 1: B2V_GN_APPLY(1); break;
-    case 2: B2V_GN_APPLY(2); break;
-    case 3: B2V_GN_APPLY(3); break;
-    case 4: B2V_GN_APPLY(4); break;
-    default: B2V_GN_APPLY(5); break;
-  }
-#undef B2V_GN_STATS
-#undef B2V_GN_APPLY
+  gn_apply_kernel<<<grid, threads, 0, s>>>((const __nv_bfloat16*)x1, C1, (const __nv_bfloat16*)x2, C2, gamma, beta,
+                                          (__nv_bfloat16*)y, rows_per_item, groups, rpp, silu, stats);
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;
@@ -358,15 +348,26 @@ int group_norm(const void* x1, int C1, const void* x2, int C2, const float* gamm
 
 int layer_norm(const void* x, const float* gamma, const float* beta, void* y, int64_t rows, int C, float eps,
                cudaStream_t s) {
-  B2V_CHECK(C % 8 == 0 && C <= 2048 && rows > 0, "layer_norm: C=%d unsupported", C);
+  B2V_CHECK(C % 64 == 0 && C <= 2048 && rows > 0, "layer_norm: C=%d unsupported (multiple of 64, <= 2048)", C);
   const int vecs = C >> 3;
-  const int grid = grid_1d(rows * 32, 256, 8);
-  if (vecs <= 64)
-    layer_norm_kernel<2><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, gamma, beta, (__nv_bfloat16*)y, rows, C, eps);
-  else if (vecs <= 160)
-    layer_norm_kernel<5><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, gamma, beta, (__nv_bfloat16*)y, rows, C, eps);
-  else
-    layer_norm_kernel<8><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, gamma, beta, (__nv_bfloat16*)y, rows, C, eps);
+  // lanes per row x vectors per lane = vecs, with <= 8 vectors per lane and every lane of the warp busy
+  int lpr = 8;
+  while (lpr < 32 && (vecs % lpr != 0 || vecs / lpr > 8 || (vecs % (lpr * 2) == 0 && vecs / lpr > 5))) lpr *= 2;
+  B2V_CHECK(vecs % lpr == 0 && vecs / lpr <= 8, "layer_norm: C=%d has no lane mapping", C);
+  const int v = vecs / lpr;
+  const int64_t warps = (rows + (32 / lpr) - 1) / (32 / lpr);
+  const int grid = grid_1d(warps * 32, 256, 8);
+#define B2V_LN(L, V)                                                                                                 \
+  if (lpr == L && v == V) {                                                                                          \
+    layer_norm_kernel<L, V><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, gamma, beta, (__nv_bfloat16*)y, rows, C, eps); \
+    launched = true;                                                                                                 \
+  }
+  bool launched = false;
+  B2V_LN(8, 1) B2V_LN(8, 2) B2V_LN(8, 3) B2V_LN(8, 4) B2V_LN(8, 5)
+  B2V_LN(16, 3) B2V_LN(16, 4) B2V_LN(16, 5) B2V_LN(16, 7)
+  B2V_LN(32, 3) B2V_LN(32, 4) B2V_LN(32, 5) B2V_LN(32, 6) B2V_LN(32, 7) B2V_LN(32, 8)
+#undef B2V_LN
+  if (!launched) return fail(B2V_ERR_ARG, "layer_norm: C=%d (lanes %d x vectors %d) not instantiated", C, lpr, v);
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;
