@@ -33,7 +33,9 @@ int temporal_attention(const void* qkv, int64_t ld, int q_off, int k_off, int v_
                        int F, int64_t HW, int heads, float scale, cudaStream_t s);
 
 // small.cu : SIMT kernels for the thin ends of the network
-int time_embedding(float timestep, int B, int dim0, const float* w1, const float* b1, const float* w2, const float* b2,
+int set_scalar(float* dst_dev, float v, cudaStream_t s);
+// timestep_dev: device float (set by set_scalar outside the replayed graph)
+int time_embedding(const float* timestep_dev, int B, int dim0, const float* w1, const float* b1, const float* w2, const float* b2,
                    int temb_dim, float* silu_emb_out /*[B,temb_dim] = SiLU(emb)*/, cudaStream_t s);
 // out[b, n] = bias[n] + sum_k W[n,k] * in[b,k]  (fp32, tiny M)
 int small_linear(const float* in, const float* w, const float* bias, float* out, int B, int N, int K, cudaStream_t s);

@@ -29,7 +29,8 @@ __global__ void small_linear_kernel(const float* __restrict__ in, const float* _
 }
 
 // Timesteps(dim, flip_sin_to_cos=True, downscale_freq_shift=0): [cos(t f_i), sin(t f_i)], f_i = exp(-ln(1e4) i/half)
-__global__ void timestep_sinusoid_kernel(float t, int dim, int B, float* __restrict__ out) {
+__global__ void timestep_sinusoid_kernel(const float* __restrict__ t_dev, int dim, int B, float* __restrict__ out) {
+  const float t = *t_dev;  // read from device memory: the kernel is replayed from a CUDA graph with a new timestep
   const int half = dim / 2;
   for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < B * dim; i += gridDim.x * blockDim.x) {
     const int j = i % dim;
@@ -72,7 +73,16 @@ __global__ void to_bf16_kernel(const T* __restrict__ x, __nv_bfloat16* __restric
     y[i] = __float2bfloat16_rn(DT<T>::ld(x + i));
 }
 
+__global__ void set_scalar_kernel(float* dst, float v) { *dst = v; }
+
 }  // namespace
+
+int set_scalar(float* dst_dev, float v, cudaStream_t s) {
+  set_scalar_kernel<<<1, 1, 0, s>>>(dst_dev, v);
+  count_launch();
+  B2V_CUDA_OK(launch_check());
+  return 0;
+}
 
 int small_linear(const float* in, const float* w, const float* bias, float* out, int B, int N, int K,
                  cudaStream_t s) {
@@ -85,11 +95,11 @@ int small_linear(const float* in, const float* w, const float* bias, float* out,
 
 // SiLU(time_embedding(Timesteps(t))) — every consumer (ResnetBlock2D.time_emb_proj) applies SiLU first.
 // scratch layout inside silu_emb_out's caller-provided buffer: [B,temb] result, then [B,dim0] + [B,temb] temporaries.
-int time_embedding(float timestep, int B, int dim0, const float* w1, const float* b1, const float* w2,
+int time_embedding(const float* timestep_dev, int B, int dim0, const float* w1, const float* b1, const float* w2,
                    const float* b2, int temb_dim, float* silu_emb_out, cudaStream_t s) {
   float* sinus = silu_emb_out + (int64_t)B * temb_dim;
   float* hid = sinus + (int64_t)B * dim0;
-  timestep_sinusoid_kernel<<<(B * dim0 + 255) / 256, 256, 0, s>>>(timestep, dim0, B, sinus);
+  timestep_sinusoid_kernel<<<(B * dim0 + 255) / 256, 256, 0, s>>>(timestep_dev, dim0, B, sinus);
   count_launch();
   {
     const int64_t threads = (int64_t)B * temb_dim * 32;

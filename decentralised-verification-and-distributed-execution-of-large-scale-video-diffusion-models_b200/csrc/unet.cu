@@ -10,6 +10,7 @@
 // reference vanish because temporal ops address frames by a row stride.
 #include <map>
 #include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -194,7 +195,22 @@ struct b2v_unet3d {
   int temb_dim = 0;
   static constexpr int kMaxB = 8;
   float* temb_scratch = nullptr;  // [kMaxB*temb] silu(emb) + sinusoid + hidden
+  float* t_dev = nullptr;         // the timestep, read by the (replayed) sinusoid kernel
   std::vector<ResnetW*> all_resnets;
+
+  // CUDA-graph replay of the ~1100-launch forward: one executable graph per (shape, io dtype, workspace). The graph
+  // reads / writes fixed staging buffers at the head of the workspace, so caller pointers may change between calls.
+  struct GraphEntry {
+    int B, F, H, W, dt;
+    void* ws;
+    size_t ws_bytes;
+    int seen;  // the first call of a key runs eagerly (one-off shapes never pay for a capture), the second captures
+    cudaGraphExec_t exec;
+    uint64_t launches;
+  };
+  std::vector<GraphEntry> graphs;
+  std::mutex graph_mu;
+  cudaStream_t cap_stream = nullptr;  // capture happens here (the caller's stream may be the legacy default stream)
 };
 
 namespace b2v {
@@ -364,6 +380,7 @@ struct Ctx {
   int status = 0;
   double flops = 0.0;  // algorithmic FLOPs (GEMM/conv/attention, MAC = 2)
   const bf16* text = nullptr;  // [B*text_len, cross_dim]
+  void *in_stage = nullptr, *ehs_stage = nullptr, *out_stage = nullptr;  // fixed-address io staging (graph replay)
 
   bool dry() const { return arena.dry(); }
   bf16* act(int64_t rows, int C) {
@@ -574,11 +591,24 @@ Act temporal(Ctx& c, const TemporalW& a, const Act& x) {
   return Act{out, M, C, x.H, x.W};
 }
 
-int forward_impl(b2v_unet3d* u, Ctx& c, const void* sample, float timestep, const void* ehs, void* out, int io_dtype,
-                 int H, int W) {
+// io staging at the head of the arena (first allocations: same addresses for every call on a workspace). Sized for
+// fp32 io so the plan does not depend on the io dtype.
+void plan_stage(b2v_unet3d* u, Ctx& c, int H, int W) {
+  const b2v_unet3d_config& cfg = u->cfg;
+  const size_t px = (size_t)c.B * c.F * H * W;
+  c.in_stage = c.bytes(px * cfg.in_channels * 4);
+  c.ehs_stage = c.bytes((size_t)c.B * cfg.text_len * cfg.cross_attention_dim * 4);
+  c.out_stage = c.bytes(px * cfg.out_channels * 4);
+}
+
+// runs the network from c.in_stage / c.ehs_stage to c.out_stage (plan_stage must have been called on c)
+int forward_impl(b2v_unet3d* u, Ctx& c, int io_dtype, int H, int W) {
   const b2v_unet3d_config& cfg = u->cfg;
   const int B = c.B, F = c.F, N = B * F;
   const int C0 = cfg.block_out_channels[0];
+  const void* sample = c.in_stage;
+  const void* ehs = c.ehs_stage;
+  void* out = c.out_stage;
 
   // text tokens -> bf16 rows; time embedding + the 22 per-resnet projections (fp32, M = B)
   const int64_t text_n = (int64_t)B * cfg.text_len * cfg.cross_attention_dim;
@@ -586,7 +616,7 @@ int forward_impl(b2v_unet3d* u, Ctx& c, const void* sample, float timestep, cons
   c.text = text;
   if (c.live()) {
     c.run(to_bf16(ehs, io_dtype, text, text_n, c.s));
-    c.run(time_embedding(timestep, B, C0, u->te_w1, u->te_b1, u->te_w2, u->te_b2, u->temb_dim, u->temb_scratch, c.s));
+    c.run(time_embedding(u->t_dev, B, C0, u->te_w1, u->te_b1, u->te_w2, u->te_b2, u->temb_dim, u->temb_scratch, c.s));
     for (ResnetW* r : u->all_resnets)
       c.run(small_linear(u->temb_scratch, r->temb_w, r->temb_b, r->rowbias, B, r->Cout, u->temb_dim, c.s));
   }
@@ -713,12 +743,19 @@ extern "C" int b2v_unet3d_create(const b2v_unet3d_config* cfg, b2v_unet3d** out)
   u->cfg = *cfg;
   cudaGetDevice(&u->device);
   u->temb_dim = cfg->block_out_channels[0] * 4;
+  if (cudaStreamCreateWithFlags(&u->cap_stream, cudaStreamNonBlocking) != cudaSuccess) {
+    delete u;
+    return fail(B2V_ERR_CUDA, "cudaStreamCreate failed");
+  }
   *out = u;
   return 0;
 }
 
 extern "C" void b2v_unet3d_destroy(b2v_unet3d* u) {
   if (!u) return;
+  for (auto& g : u->graphs)
+    if (g.exec) cudaGraphExecDestroy(g.exec);
+  if (u->cap_stream) cudaStreamDestroy(u->cap_stream);
   for (auto& kv : u->raw) cudaFree(kv.second.first);
   for (void* p : u->owned) cudaFree(p);
   delete u;
@@ -786,6 +823,7 @@ extern "C" int b2v_unet3d_finalize(b2v_unet3d* u) {
     u->te_w2 = mat("time_embedding.linear_2.weight", u->temb_dim, u->temb_dim);
     u->te_b2 = L.vec("time_embedding.linear_2.bias", u->temb_dim);
     u->temb_scratch = L.dalloc<float>((size_t)b2v_unet3d::kMaxB * (2 * u->temb_dim + ch[0]));
+    u->t_dev = L.dalloc<float>(1);
     u->transformer_in = L.temporal("transformer_in", ch[0], cfg.transformer_in_heads);
   }
   // down: CrossAttnDownBlock3D x3 + DownBlock3D
@@ -881,7 +919,8 @@ extern "C" size_t b2v_unet3d_workspace_bytes(const b2v_unet3d* u, int B, int F, 
   c.u = const_cast<b2v_unet3d*>(u);
   c.s = 0; c.B = B; c.F = F;
   c.arena.reset(nullptr, 0, true);
-  forward_impl(c.u, c, nullptr, 0.f, nullptr, nullptr, B2V_F32, H, W);
+  plan_stage(c.u, c, H, W);
+  forward_impl(c.u, c, B2V_F32, H, W);
   return c.arena.peak() + 4096;
 }
 
@@ -891,8 +930,15 @@ extern "C" double b2v_unet3d_flops(const b2v_unet3d* u, int B, int F, int H, int
   c.u = const_cast<b2v_unet3d*>(u);
   c.s = 0; c.B = B; c.F = F;
   c.arena.reset(nullptr, 0, true);
-  forward_impl(c.u, c, nullptr, 0.f, nullptr, nullptr, B2V_F32, H, W);
+  plan_stage(c.u, c, H, W);
+  forward_impl(c.u, c, B2V_F32, H, W);
   return c.flops;
+}
+
+static bool graphs_enabled() {
+  static int on = -1;
+  if (on < 0) on = getenv("B2V_NO_GRAPH") == nullptr;
+  return on == 1;
 }
 
 extern "C" int b2v_unet3d_forward(b2v_unet3d* u, const void* sample_dev, float timestep, const void* ehs_dev,
@@ -902,9 +948,67 @@ extern "C" int b2v_unet3d_forward(b2v_unet3d* u, const void* sample_dev, float t
   B2V_CHECK(sample_dev && ehs_dev && out_dev && workspace_dev, "null argument");
   B2V_CHECK(dtype_size(io_dtype) != 0, "bad io dtype");
   B2V_CHECK(((uintptr_t)workspace_dev & 1023) == 0, "workspace must be 1 KiB aligned");
+  cudaStream_t s = (cudaStream_t)stream;
+  const b2v_unet3d_config& cfg = u->cfg;
   Ctx c;
   c.u = u;
-  c.s = (cudaStream_t)stream; c.B = B; c.F = F;
+  c.s = s; c.B = B; c.F = F;
   c.arena.reset((uint8_t*)workspace_dev, workspace_bytes, false);
-  return forward_impl(u, c, sample_dev, timestep, ehs_dev, out_dev, io_dtype, H, W);
+  plan_stage(u, c, H, W);
+  if (c.status != 0) return c.status;
+  const size_t es = dtype_size(io_dtype), px = (size_t)B * F * H * W;
+  B2V_CUDA_OK(cudaMemcpyAsync(c.in_stage, sample_dev, px * cfg.in_channels * es, cudaMemcpyDeviceToDevice, s));
+  B2V_CUDA_OK(cudaMemcpyAsync(c.ehs_stage, ehs_dev, (size_t)B * cfg.text_len * cfg.cross_attention_dim * es,
+                              cudaMemcpyDeviceToDevice, s));
+  B2V_TRY(set_scalar(u->t_dev, timestep, s));
+
+  int status = 0;
+  cudaStreamCaptureStatus cap = cudaStreamCaptureStatusNone;
+  if (s != nullptr && s != cudaStreamLegacy && s != cudaStreamPerThread) cudaStreamIsCapturing(s, &cap);
+  cudaGetLastError();
+  if (!graphs_enabled() || cap != cudaStreamCaptureStatusNone) {
+    status = forward_impl(u, c, io_dtype, H, W);  // eager (or the caller is capturing us into a graph of its own)
+  } else {
+    std::lock_guard<std::mutex> lock(u->graph_mu);
+    b2v_unet3d::GraphEntry* e = nullptr;
+    for (auto& g : u->graphs)
+      if (g.B == B && g.F == F && g.H == H && g.W == W && g.dt == io_dtype && g.ws == workspace_dev &&
+          g.ws_bytes == workspace_bytes)
+        e = &g;
+    if (!e) {
+      if (u->graphs.size() >= 8) {  // oldest out
+        if (u->graphs.front().exec) cudaGraphExecDestroy(u->graphs.front().exec);
+        u->graphs.erase(u->graphs.begin());
+      }
+      u->graphs.push_back({B, F, H, W, io_dtype, workspace_dev, workspace_bytes, 0, nullptr, 0});
+      e = &u->graphs.back();
+    }
+    if (e->exec) {
+      count_launch((int)e->launches);
+      B2V_CUDA_OK(cudaGraphLaunch(e->exec, s));
+    } else if (e->seen++ == 0) {
+      status = forward_impl(u, c, io_dtype, H, W);  // also runs every one-time cudaFuncSetAttribute outside a capture
+    } else {
+      const uint64_t l0 = b2v_launch_count();
+      c.s = u->cap_stream;
+      B2V_CUDA_OK(cudaStreamBeginCapture(u->cap_stream, cudaStreamCaptureModeThreadLocal));
+      status = forward_impl(u, c, io_dtype, H, W);
+      cudaGraph_t graph = nullptr;
+      const cudaError_t ce = cudaStreamEndCapture(u->cap_stream, &graph);
+      if (status == 0 && ce != cudaSuccess) status = fail(B2V_ERR_CUDA, "graph capture: %s", cudaGetErrorString(ce));
+      if (status == 0) {
+        const cudaError_t ie = cudaGraphInstantiate(&e->exec, graph, 0);
+        if (ie != cudaSuccess) { e->exec = nullptr; status = fail(B2V_ERR_CUDA, "graph instantiate: %s", cudaGetErrorString(ie)); }
+      }
+      if (graph) cudaGraphDestroy(graph);
+      if (status == 0) {
+        e->launches = b2v_launch_count() - l0;
+        const cudaError_t le = cudaGraphLaunch(e->exec, s);
+        if (le != cudaSuccess) status = fail(B2V_ERR_CUDA, "graph launch: %s", cudaGetErrorString(le));
+      }
+    }
+  }
+  if (status != 0) return status;
+  B2V_CUDA_OK(cudaMemcpyAsync(out_dev, c.out_stage, px * cfg.out_channels * es, cudaMemcpyDeviceToDevice, s));
+  return 0;
 }
