@@ -39,9 +39,11 @@ constexpr int SMEM_LIMIT = 227 * 1024;
 // per epilogue warp] [barriers]. An epilogue warp owns 32 rows x GROUP_COLS columns of the tile and hands them to the
 // TMA store engine in panels of PANEL_COLS columns: 64 (128-byte rows, 128B swizzle, conflict-free writes) when the
 // group width allows it, else the whole group width unswizzled (BN = 160 -> 80 columns, BN = 64 -> 32).
-template <int BN, bool GEGLU, bool RES>
+// CG = CTAs per tile: 2 = CTA pair (tcgen05 cta_group::2): the pair computes a 256-row tile, each CTA stages its own 128
+// rows of A and HALF of the B tile (BN/2 rows) per k-block.
+template <int BN, bool GEGLU, bool RES, int CG>
 struct TileCfg {
-  static constexpr int B_BYTES = BN * BK * 2;
+  static constexpr int B_BYTES = (BN / CG) * BK * 2;
   static constexpr int STAGE_BYTES = A_BYTES + B_BYTES;
   static constexpr int ACC_STRIDE = (BN > 128) ? 256 : 128;  // TMEM columns between the two accumulators
   static constexpr int OUT_COLS = GEGLU ? BN / 2 : BN;
@@ -67,8 +69,8 @@ struct GemmParams {
   int taps;                // 1 | 3 | 9
   int64_t rows_per_batch;  // tiled mode: rows of one z-slab (tiles never straddle slabs)
   int64_t tap_row_stride;  // tiled mode, 3 taps: rows per frame
-  int m_tiles_per_batch;
-  int num_m_tiles;
+  int m_units_per_batch;  // units of CG x 128 rows per slab
+  int num_m_units;
   int num_n_tiles;
   // im2col geometry (output P x Q per image, conv stride)
   int P, Q, conv_stride;
@@ -111,13 +113,18 @@ __device__ __forceinline__ float gelu_fast(float x) {
 // GEMMs were bound by the LSU/L2 request rate of the latter). With RES the residual panel ARRIVES in the same buffer by
 // TMA load and is updated in place; when a tile is one panel wide (all but BN = 256) two buffers alternate so the
 // residual of the NEXT tile is already in flight while this one is processed.
-template <int BN, int MODE, bool GEGLU, bool RES>
+template <int BN, int MODE, bool GEGLU, bool RES, int CG>
 __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtensorMap* tmO, const CUtensorMap* tmR,
                                               uint8_t* stage0, uint32_t rbar0, uint32_t tmem_base, uint32_t tfull0,
                                               uint32_t tempty0, int warp, int lane, int num_tiles) {
-  using Cfg = TileCfg<BN, GEGLU, RES>;
+  using Cfg = TileCfg<BN, GEGLU, RES, CG>;
   constexpr int OUT_COLS = Cfg::OUT_COLS;
   constexpr int NCH = OUT_COLS / 32;  // 16-column chunks per group
+  // work units: tile `u` of this CTA (CG = 1) or of this CTA pair (CG = 2: rank r owns rows [128 r, +128) of the unit)
+  const int rank = CG == 2 ? (int)(blockIdx.x & 1) : 0;
+  const int unit0 = CG == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int ustride = CG == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
+  const uint32_t tempty_leader = CG == 2 ? mapa_shared(tempty0, 0) : tempty0;
   constexpr int CH_PER_PANEL = Cfg::PANEL_COLS / 16;
   constexpr int NBUF = Cfg::NBUF;
   const int quarter = warp & 3;
@@ -128,10 +135,10 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
   // TMA coordinates of this warp's part of a tile: (first column, first row inside the slab, slab)
   auto tile_col = [&](int tile) { return (tile % p.num_n_tiles) * OUT_COLS + c_base; };
   auto tile_row0 = [&](int tile) {
-    const int m_tile = tile / p.num_n_tiles;
-    return (MODE == 0 ? (m_tile % p.m_tiles_per_batch) : m_tile) * BM + quarter * 32;
+    const int m_unit = tile / p.num_n_tiles;
+    return ((MODE == 0 ? (m_unit % p.m_units_per_batch) : m_unit) * CG + rank) * BM + quarter * 32;
   };
-  auto tile_slab = [&](int tile) { return MODE == 0 ? (tile / p.num_n_tiles) / p.m_tiles_per_batch : 0; };
+  auto tile_slab = [&](int tile) { return MODE == 0 ? (tile / p.num_n_tiles) / p.m_units_per_batch : 0; };
   auto load_residual = [&](int tile, int panel, int buf) {  // one lane
     const uint32_t bar = rbar0 + 8 * buf;
     mbar_expect_tx(bar, Cfg::PANEL_BYTES);
@@ -140,10 +147,10 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
   };
 
   uint32_t q = 0;  // panels processed by this warp so far: buffer q % NBUF, residual barrier parity (q / NBUF) & 1
-  if (RES && NBUF == 2 && lane == 0 && (int)blockIdx.x < num_tiles) load_residual(blockIdx.x, 0, 0);
+  if (RES && NBUF == 2 && lane == 0 && unit0 < num_tiles) load_residual(unit0, 0, 0);
   int acc = 0;
   uint32_t acc_phase = 0;
-  for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
+  for (int tile = unit0; tile < num_tiles; tile += ustride) {
     const int n_tile = tile % p.num_n_tiles;
     const int row0 = tile_row0(tile), slab = tile_slab(tile);
     const int ocol0 = tile_col(tile);
@@ -170,7 +177,7 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
           bulk_wait_read0();
           if (RES) {
             if (NBUF == 2) {
-              if (tile + (int)gridDim.x < num_tiles) load_residual(tile + gridDim.x, 0, buf ^ 1);
+              if (tile + ustride < num_tiles) load_residual(tile + ustride, 0, buf ^ 1);
             } else {
               load_residual(tile, panel, 0);
             }
@@ -261,7 +268,10 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
     }
     tc_fence_before();
     __syncwarp();
-    if (lane == 0) mbar_arrive(tempty0 + 8 * acc);
+    if (lane == 0) {  // the accumulator is free again: tell the MMA warp (of the leader CTA for a pair)
+      if (CG == 2) mbar_arrive_cluster(tempty_leader + 8 * acc);
+      else mbar_arrive(tempty0 + 8 * acc);
+    }
     if (++acc == 2) { acc = 0; acc_phase ^= 1; }
   }
   if (lane == 0) bulk_wait0();  // this warp's TMA stores have drained before its shared memory goes away
@@ -308,11 +318,11 @@ __device__ __forceinline__ void epilogue_loop_ncfhw(const GemmParams& p, uint32_
 }
 
 // MODE 0: A through a 3-D tiled tensor map (channels, rows, slabs); MODE 1: A through a 4-D im2col map.
-template <int BN, int MODE, int EPI, bool RES>
+template <int BN, int MODE, int EPI, bool RES, int CG>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR, const GemmParams p) {
-  using Cfg = TileCfg<BN, EPI == EPI_GEGLU_T, RES>;
+  using Cfg = TileCfg<BN, EPI == EPI_GEGLU_T, RES, CG>;
   constexpr int STAGES = Cfg::STAGES;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = reinterpret_cast<uint8_t*>((reinterpret_cast<uintptr_t>(smem_raw) + 1023) & ~(uintptr_t)1023);
@@ -329,7 +339,11 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int kb_per_tap = p.Kc / BK;
   const int num_kb = p.taps * kb_per_tap;
-  const int num_tiles = p.num_m_tiles * p.num_n_tiles;
+  const int num_tiles = p.num_m_units * p.num_n_tiles;  // work units (a unit is CG x 128 rows x BN columns)
+  // CTA pair: rank 0 (leader) issues the MMAs; both CTAs load operands, both run the epilogue on their own 128 rows
+  const int rank = CG == 2 ? (int)(blockIdx.x & 1) : 0;
+  const int unit0 = CG == 2 ? (int)(blockIdx.x >> 1) : (int)blockIdx.x;
+  const int ustride = CG == 2 ? (int)(gridDim.x >> 1) : (int)gridDim.x;
 
   if (warp == 0 && lane == 0) {
     prefetch_tmap(&tmA);
@@ -342,14 +356,15 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     }
     for (int i = 0; i < 2; ++i) {
       mbar_init(tfull0 + 8 * i, 1);
-      mbar_init(tempty0 + 8 * i, 8);
+      mbar_init(tempty0 + 8 * i, EPI_WARPS * CG);
     }
     for (int i = 0; i < 2 * EPI_WARPS; ++i) mbar_init(rbar0 + 8 * i, 1);
     fence_barrier_init();
   }
+  if (CG == 2) cluster_sync_all();  // the peer's barriers exist before anything can signal them
   if (warp == 1) {
-    tmem_alloc(smem_u32(tmem_slot), TMEM_COLS);
-    tmem_relinquish();
+    if (CG == 2) { tmem2_alloc(smem_u32(tmem_slot), TMEM_COLS); tmem2_relinquish(); }
+    else { tmem_alloc(smem_u32(tmem_slot), TMEM_COLS); tmem_relinquish(); }
   }
   tc_fence_before();
   __syncthreads();
@@ -357,18 +372,18 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   const uint32_t tmem_base = *tmem_slot;
 
   if (warp == 0) {
-    // ===================== TMA producer =====================
+    // ===================== TMA producer (both CTAs of a pair) =====================
     if (elect_one()) {
       int stage = 0;
       uint32_t phase = 0;
-      for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-        const int n_tile = tile % p.num_n_tiles, m_tile = tile / p.num_n_tiles;
+      for (int tile = unit0; tile < num_tiles; tile += ustride) {
+        const int n_tile = tile % p.num_n_tiles, m_unit = tile / p.num_n_tiles;
         int c1 = 0, c2 = 0, c3 = 0;
         if (MODE == 0) {
-          c2 = m_tile / p.m_tiles_per_batch;                   // slab
-          c1 = (m_tile % p.m_tiles_per_batch) * BM;            // first row inside the slab
+          c2 = m_unit / p.m_units_per_batch;                                  // slab
+          c1 = ((m_unit % p.m_units_per_batch) * CG + rank) * BM;             // first row inside the slab
         } else {
-          const int64_t m0 = (int64_t)m_tile * BM;
+          const int64_t m0 = ((int64_t)m_unit * CG + rank) * BM;
           const int pq = p.P * p.Q;
           c3 = (int)(m0 / pq);
           const int rem = (int)(m0 % pq);
@@ -378,72 +393,89 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
         for (int kb = 0; kb < num_kb; ++kb) {
           mbar_wait(empty0 + 8 * stage, phase ^ 1);
           const uint32_t fb = full0 + 8 * stage;
-          mbar_expect_tx(fb, Cfg::STAGE_BYTES);
+          // a pair counts the bytes of BOTH CTAs on the leader's barrier; only the leader arrives on it
+          if (rank == 0) mbar_expect_tx(fb, CG * Cfg::STAGE_BYTES);
           const int tap = kb / kb_per_tap, kc = (kb % kb_per_tap) * BK;
           const uint32_t dstA = smem_u32(sA + stage * A_BYTES);
+          const uint32_t dstB = smem_u32(sB + stage * Cfg::B_BYTES);
+          const int brow = n_tile * BN + rank * (BN / CG);
           if (MODE == 0) {
             const int64_t r = (int64_t)c1 + (int64_t)(tap - (p.taps >> 1)) * p.tap_row_stride;
-            tma_load_3d(dstA, &tmA, fb, kc, (int)r, c2);
+            if (CG == 2) tma2_load_3d(dstA, &tmA, fb, kc, (int)r, c2);
+            else tma_load_3d(dstA, &tmA, fb, kc, (int)r, c2);
           } else {
-            tma_load_im2col_4d(dstA, &tmA, fb, kc, c1, c2, c3, (uint16_t)(tap % 3), (uint16_t)(tap / 3));
+            if (CG == 2) tma2_load_im2col_4d(dstA, &tmA, fb, kc, c1, c2, c3, (uint16_t)(tap % 3), (uint16_t)(tap / 3));
+            else tma_load_im2col_4d(dstA, &tmA, fb, kc, c1, c2, c3, (uint16_t)(tap % 3), (uint16_t)(tap / 3));
           }
-          tma_load_2d(smem_u32(sB + stage * Cfg::B_BYTES), &tmB, fb, kb * BK, n_tile * BN);
+          if (CG == 2) tma2_load_2d(dstB, &tmB, fb, kb * BK, brow);
+          else tma_load_2d(dstB, &tmB, fb, kb * BK, brow);
           if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
       }
     }
   } else if (warp == 1) {
-    // ===================== MMA issuer =====================
-    constexpr uint32_t idesc = umma_idesc_bf16(BM, BN);
-    int stage = 0;
-    uint32_t phase = 0;
-    int acc = 0;
-    uint32_t acc_phase = 0;
-    for (int tile = blockIdx.x; tile < num_tiles; tile += gridDim.x) {
-      mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
-      tc_fence_after();
-      const uint32_t d_tmem = tmem_base + acc * Cfg::ACC_STRIDE;
-      for (int kb = 0; kb < num_kb; ++kb) {
-        mbar_wait(full0 + 8 * stage, phase);
+    // ===================== MMA issuer (the leader CTA of a pair) =====================
+    if (rank == 0) {
+      constexpr uint32_t idesc = umma_idesc_bf16(BM * CG, BN);
+      int stage = 0;
+      uint32_t phase = 0;
+      int acc = 0;
+      uint32_t acc_phase = 0;
+      for (int tile = unit0; tile < num_tiles; tile += ustride) {
+        mbar_wait(tempty0 + 8 * acc, acc_phase ^ 1);
         tc_fence_after();
-        if (elect_one()) {
-          const uint64_t adesc = umma_desc_sw128(smem_u32(sA + stage * A_BYTES));
-          const uint64_t bdesc = umma_desc_sw128(smem_u32(sB + stage * Cfg::B_BYTES));
+        const uint32_t d_tmem = tmem_base + acc * Cfg::ACC_STRIDE;
+        for (int kb = 0; kb < num_kb; ++kb) {
+          mbar_wait(full0 + 8 * stage, phase);
+          tc_fence_after();
+          if (elect_one()) {
+            const uint64_t adesc = umma_desc_sw128(smem_u32(sA + stage * A_BYTES));
+            const uint64_t bdesc = umma_desc_sw128(smem_u32(sB + stage * Cfg::B_BYTES));
 #pragma unroll
-          for (int k = 0; k < BK / 16; ++k) {
-            // advance 16 bf16 = 32 bytes inside the swizzle atom: +2 in the 16-byte address field
-            umma_bf16_ss(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb | k) != 0);
+            for (int k = 0; k < BK / 16; ++k) {
+              // advance 16 bf16 = 32 bytes inside the swizzle atom: +2 in the 16-byte address field
+              if (CG == 2) umma2_bf16_ss(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb | k) != 0);
+              else umma_bf16_ss(d_tmem, adesc + (uint64_t)(2 * k), bdesc + (uint64_t)(2 * k), idesc, (kb | k) != 0);
+            }
+            if (CG == 2) {
+              umma2_commit(empty0 + 8 * stage);                       // frees the slot in BOTH CTAs
+              if (kb == num_kb - 1) umma2_commit(tfull0 + 8 * acc);   // both CTAs' epilogues may read their half
+            } else {
+              umma_commit(empty0 + 8 * stage);                    // slot reusable when these MMAs retire
+              if (kb == num_kb - 1) umma_commit(tfull0 + 8 * acc);  // accumulator complete
+            }
           }
-          umma_commit(empty0 + 8 * stage);                    // slot reusable when these MMAs retire
-          if (kb == num_kb - 1) umma_commit(tfull0 + 8 * acc);  // accumulator complete
+          __syncwarp();
+          if (++stage == STAGES) { stage = 0; phase ^= 1; }
         }
-        __syncwarp();
-        if (++stage == STAGES) { stage = 0; phase ^= 1; }
+        if (++acc == 2) { acc = 0; acc_phase ^= 1; }
       }
-      if (++acc == 2) { acc = 0; acc_phase ^= 1; }
     }
   } else {
     // ===================== epilogue (warps 2..9 -> TMEM lane quarters 2,3,0,1,2,3,0,1; column halves 0,0,0,0,1,1,1,1) ====
     if constexpr (EPI == EPI_NCFHW)
       epilogue_loop_ncfhw<Cfg::ACC_STRIDE>(p, tmem_base, tfull0, tempty0, warp, lane, num_tiles);
     else
-      epilogue_loop<BN, MODE, EPI == EPI_GEGLU_T, RES>(p, &tmO, &tmR, sEpi + (warp - 2) * Cfg::NBUF * Cfg::PANEL_BYTES,
-                                                       rbar0 + 16 * (warp - 2), tmem_base, tfull0, tempty0, warp, lane,
-                                                       num_tiles);
+      epilogue_loop<BN, MODE, EPI == EPI_GEGLU_T, RES, CG>(p, &tmO, &tmR,
+                                                           sEpi + (warp - 2) * Cfg::NBUF * Cfg::PANEL_BYTES,
+                                                           rbar0 + 16 * (warp - 2), tmem_base, tfull0, tempty0, warp,
+                                                           lane, num_tiles);
   }
 
   tc_fence_before();
   __syncthreads();
+  if (CG == 2) cluster_sync_all();  // the peer's shared memory / barriers stay valid until both CTAs are done
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, TMEM_COLS);
+    if (CG == 2) tmem2_dealloc(tmem_base, TMEM_COLS);
+    else tmem_dealloc(tmem_base, TMEM_COLS);
   }
 }
 
-template <int BN, int MODE, int EPI, bool RES>
+template <int BN, int MODE, int EPI, bool RES, int CG>
 int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int64_t out_rows_per_slab,
                 int64_t out_slabs, cudaStream_t s) {
-  using Cfg = TileCfg<BN, EPI == EPI_GEGLU_T, RES>;
+  using Cfg = TileCfg<BN, EPI == EPI_GEGLU_T, RES, CG>;
   CUtensorMap tmO = tmA, tmR = tmA;  // EPI_NCFHW stores with plain instructions
   if (EPI != EPI_NCFHW) {
     const int n_out = EPI == EPI_GEGLU_T ? p.N / 2 : p.N;
@@ -456,39 +488,69 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(gemm_kernel<BN, MODE, EPI, RES>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    attr_err = cudaFuncSetAttribute(gemm_kernel<BN, MODE, EPI, RES, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     Cfg::SMEM_BYTES);
   });
   if (attr_err != cudaSuccess) return fail(B2V_ERR_CUDA, "gemm smem attr: %s", cudaGetErrorString(attr_err));
-  const int tiles = p.num_m_tiles * p.num_n_tiles;
-  const int grid = tiles < sm_count() ? tiles : sm_count();
-  gemm_kernel<BN, MODE, EPI, RES><<<grid, NUM_THREADS, Cfg::SMEM_BYTES, s>>>(tmA, tmB, tmO, tmR, p);
+  const int units = p.num_m_units * p.num_n_tiles;
+  if (CG == 1) {
+    const int grid = units < sm_count() ? units : sm_count();
+    gemm_kernel<BN, MODE, EPI, RES, CG><<<grid, NUM_THREADS, Cfg::SMEM_BYTES, s>>>(tmA, tmB, tmO, tmR, p);
+  } else {
+    // one CTA pair (cluster of 2 = the two SMs of a TPC) per work unit, persistent over the units
+    const int pairs = units < sm_count() / 2 ? units : sm_count() / 2;
+    cudaLaunchConfig_t cfg = {};
+    cfg.gridDim = dim3((unsigned)(2 * pairs));
+    cfg.blockDim = dim3(NUM_THREADS);
+    cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
+    cfg.stream = s;
+    cudaLaunchAttribute attr[1];
+    attr[0].id = cudaLaunchAttributeClusterDimension;
+    attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    cfg.attrs = attr;
+    cfg.numAttrs = 1;
+    B2V_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_kernel<BN, MODE, EPI, RES, CG>, tmA, tmB, tmO, tmR, p));
+  }
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;
 }
 
-template <int BN, int MODE>
+template <int BN, int MODE, int CG>
 int launch_plain(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int64_t orows, int64_t oslabs,
                  cudaStream_t s) {
-  if (p.residual) return launch_gemm<BN, MODE, EPI_PLAIN, true>(tmA, tmB, p, orows, oslabs, s);
-  return launch_gemm<BN, MODE, EPI_PLAIN, false>(tmA, tmB, p, orows, oslabs, s);
+  if (p.residual) return launch_gemm<BN, MODE, EPI_PLAIN, true, CG>(tmA, tmB, p, orows, oslabs, s);
+  return launch_gemm<BN, MODE, EPI_PLAIN, false, CG>(tmA, tmB, p, orows, oslabs, s);
 }
 
-template <int MODE>
+template <int MODE, int CG>
 int dispatch_gemm(int bn, bool geglu, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
                   int64_t orows, int64_t oslabs, cudaStream_t s) {
   if (geglu) {
-    if (bn == 256) return launch_gemm<256, MODE, EPI_GEGLU_T, false>(tmA, tmB, p, orows, oslabs, s);
+    if (bn == 256) return launch_gemm<256, MODE, EPI_GEGLU_T, false, CG>(tmA, tmB, p, orows, oslabs, s);
     return fail(B2V_ERR_ARG, "GEGLU epilogue needs N %% 256 == 0");
   }
   switch (bn) {
-    case 256: return launch_plain<256, MODE>(tmA, tmB, p, orows, oslabs, s);
-    case 160: return launch_plain<160, MODE>(tmA, tmB, p, orows, oslabs, s);
-    case 128: return launch_plain<128, MODE>(tmA, tmB, p, orows, oslabs, s);
-    case 64: return launch_plain<64, MODE>(tmA, tmB, p, orows, oslabs, s);
+    case 256: return launch_plain<256, MODE, CG>(tmA, tmB, p, orows, oslabs, s);
+    case 160: return launch_plain<160, MODE, CG>(tmA, tmB, p, orows, oslabs, s);
+    case 128: return launch_plain<128, MODE, CG>(tmA, tmB, p, orows, oslabs, s);
+    case 64: return launch_plain<64, MODE, CG>(tmA, tmB, p, orows, oslabs, s);
   }
   return fail(B2V_ERR_ARG, "no tile for N");
+}
+
+// CTA pairs pay off when the tile is MMA / operand-fill bound: enough 128-row tiles to pair up inside a slab and to fill
+// the machine, and a reduction of >= 640 (measured: with K = 320 the GEMM is bound by its epilogue / HBM and the
+// lock-step of the pair costs 10-30 %; from K = 640 up pairs win 5-15 %). B2V_GEMM_CG=1|2 forces the choice (A/B).
+static int pick_cg(int64_t m_tiles_per_slab, int64_t total_tiles, int64_t k_total) {
+  static int forced = -1;
+  if (forced < 0) {
+    const char* e = getenv("B2V_GEMM_CG");
+    forced = e ? atoi(e) : 0;
+  }
+  if (m_tiles_per_slab < 2) return 1;
+  if (forced == 1 || forced == 2) return forced;
+  return (total_tiles >= 2 * (int64_t)sm_count() && k_total >= 640) ? 2 : 1;
 }
 
 }  // namespace
@@ -523,6 +585,8 @@ int gemm_tiled(const GemmArgs& g, cudaStream_t s) {
   B2V_CHECK(g.M > 0 && g.M % rpb == 0, "M must be slabs x rows_per_batch");
   const int64_t lda = g.lda > 0 ? g.lda : g.Kc;
   const int64_t slabs = g.M / rpb;
+  const int64_t m_tiles_per_slab = (rpb + BM - 1) / BM;
+  const int cg = pick_cg(m_tiles_per_slab, slabs * m_tiles_per_slab * (g.N / bn), (int64_t)g.taps * g.Kc);
   CUtensorMap tmA, tmB;
   {
     const uint64_t dims[3] = {(uint64_t)g.Kc, (uint64_t)rpb, (uint64_t)slabs};
@@ -534,22 +598,23 @@ int gemm_tiled(const GemmArgs& g, cudaStream_t s) {
     const uint64_t K = (uint64_t)g.taps * g.Kc;
     const uint64_t dims[2] = {K, (uint64_t)g.N};
     const uint64_t strides[1] = {K * 2};
-    const uint32_t box[2] = {BK, (uint32_t)bn};
+    const uint32_t box[2] = {BK, (uint32_t)(bn / cg)};  // a CTA pair loads half of the B tile each
     B2V_TRY(tmap_tiled_bf16(&tmB, g.w, 2, dims, strides, box));
   }
   GemmParams p{};
   p.M = g.M; p.N = g.N; p.Kc = g.Kc; p.taps = g.taps;
   p.rows_per_batch = rpb;
   p.tap_row_stride = g.tap_row_stride;
-  p.m_tiles_per_batch = (int)((rpb + BM - 1) / BM);
-  p.num_m_tiles = (int)(slabs * p.m_tiles_per_batch);
+  p.m_units_per_batch = (int)((rpb + BM * cg - 1) / (BM * cg));
+  p.num_m_units = (int)(slabs * p.m_units_per_batch);
   p.num_n_tiles = g.N / bn;
   p.bias = g.bias; p.rowbias = g.rowbias; p.rows_per_group = g.rows_per_group > 0 ? g.rows_per_group : 1;
   p.residual = (const __nv_bfloat16*)g.residual;
   p.out = (__nv_bfloat16*)g.out;
   p.ldo = g.ldo > 0 ? g.ldo : (geglu ? g.N / 2 : g.N);
   p.gelu = (g.flags & B2V_EPI_GELU) ? 1 : 0;
-  return dispatch_gemm<0>(bn, geglu, tmA, tmB, p, rpb, slabs, s);
+  if (cg == 2) return dispatch_gemm<0, 2>(bn, geglu, tmA, tmB, p, rpb, slabs, s);
+  return dispatch_gemm<0, 1>(bn, geglu, tmA, tmB, p, rpb, slabs, s);
 }
 
 // 3x3 / pad 1 / stride {1,2} convolution over NHWC through the TMA im2col path.
@@ -561,6 +626,8 @@ int conv3x3_im2col(const ConvArgs& c, cudaStream_t s) {
   B2V_CHECK(c.Cin % BK == 0, "conv Cin=%d must be a multiple of 64", c.Cin);
   B2V_CHECK(c.stride == 1 || c.stride == 2, "conv stride must be 1 or 2");
   const int P = (c.H - 1) / c.stride + 1, Q = (c.W - 1) / c.stride + 1;
+  const int64_t m_tiles = ((int64_t)c.N * P * Q + BM - 1) / BM;
+  const int cg = c.ncfhw_out ? 1 : pick_cg(m_tiles, m_tiles * (c.Cout / bn), 9ll * c.Cin);
   CUtensorMap tmA, tmB;
   {
     const uint64_t dims[4] = {(uint64_t)c.Cin, (uint64_t)c.W, (uint64_t)c.H, (uint64_t)c.N};
@@ -574,14 +641,14 @@ int conv3x3_im2col(const ConvArgs& c, cudaStream_t s) {
     const uint64_t K = 9ull * c.Cin;
     const uint64_t dims[2] = {K, (uint64_t)c.Cout};
     const uint64_t strides[1] = {K * 2};
-    const uint32_t box[2] = {BK, (uint32_t)bn};
+    const uint32_t box[2] = {BK, (uint32_t)(bn / cg)};
     B2V_TRY(tmap_tiled_bf16(&tmB, c.w, 2, dims, strides, box));
   }
   GemmParams p{};
   p.M = (int64_t)c.N * P * Q; p.N = c.Cout; p.Kc = c.Cin; p.taps = 9;
   p.rows_per_batch = p.M; p.tap_row_stride = 0;
-  p.num_m_tiles = (int)((p.M + BM - 1) / BM);
-  p.m_tiles_per_batch = p.num_m_tiles;
+  p.num_m_units = (int)((p.M + BM * cg - 1) / (BM * cg));
+  p.m_units_per_batch = p.num_m_units;
   p.num_n_tiles = c.Cout / bn;
   p.P = P; p.Q = Q; p.conv_stride = c.stride;
   p.bias = c.bias; p.rowbias = c.rowbias; p.rows_per_group = c.rows_per_group > 0 ? c.rows_per_group : 1;
@@ -595,9 +662,10 @@ int conv3x3_im2col(const ConvArgs& c, cudaStream_t s) {
               "conv NCFHW epilogue: needs a 64-row padded weight, <= 16 real channels, stride 1");
     p.out_raw = c.ncfhw_out; p.nc_dtype = c.ncfhw_dtype; p.nc_cout = c.ncfhw_cout; p.nc_F = c.ncfhw_F;
     p.nc_HW = (int64_t)P * Q;
-    return launch_gemm<64, 1, EPI_NCFHW, false>(tmA, tmB, p, p.M, 1, s);
+    return launch_gemm<64, 1, EPI_NCFHW, false, 1>(tmA, tmB, p, p.M, 1, s);
   }
-  return dispatch_gemm<1>(bn, false, tmA, tmB, p, p.M, 1, s);
+  if (cg == 2) return dispatch_gemm<1, 2>(bn, false, tmA, tmB, p, p.M, 1, s);
+  return dispatch_gemm<1, 1>(bn, false, tmA, tmB, p, p.M, 1, s);
 }
 
 }  // namespace b2v
