@@ -6,6 +6,8 @@
 //   * temporal_attention(): attention over the frame axis (seq = F <= 32, batch = B*h*w). FLOPs are
 //                           negligible (0.2 %), the kernel is HBM-bound: one warp per (pixel, head), K/V in
 //                           shared memory, one lane per query frame, no permute copies of the activations.
+#include <stdlib.h>
+
 #include <mutex>
 
 #include "common.cuh"
@@ -21,6 +23,36 @@ __device__ __forceinline__ float ex2(float x) {
   float y;
   asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(y) : "f"(x));
   return y;
+}
+
+// Packed fp32 pairs (Blackwell FFMA2 / FADD2: two lanes of fp32 per instruction on the FMA pipe).
+__device__ __forceinline__ uint64_t pack2(float a, float b) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "f"(a), "f"(b));
+  return r;
+}
+__device__ __forceinline__ uint64_t pack2u(uint32_t a, uint32_t b) {
+  uint64_t r;
+  asm("mov.b64 %0, {%1, %2};" : "=l"(r) : "r"(a), "r"(b));
+  return r;
+}
+__device__ __forceinline__ void unpack2(uint64_t r, float& a, float& b) {
+  asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(r));
+}
+__device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
+  uint64_t d;
+  asm("fma.rn.f32x2 %0, %1, %2, %3;" : "=l"(d) : "l"(a), "l"(b), "l"(c));
+  return d;
+}
+__device__ __forceinline__ uint64_t add2(uint64_t a, uint64_t b) {
+  uint64_t d;
+  asm("add.rn.f32x2 %0, %1, %2;" : "=l"(d) : "l"(a), "l"(b));
+  return d;
+}
+__device__ __forceinline__ float max3(float a, float b, float c) {
+  float d;
+  asm("max.f32 %0, %1, %2, %3;" : "=f"(d) : "f"(a), "f"(b), "f"(c));
+  return d;
 }
 
 // ------------------------------------------------------------------------------------------------
@@ -170,11 +202,11 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       }
       float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
-      for (int i = 0; i < 128; i += 4) {
-        mx0 = fmaxf(mx0, __uint_as_float(sv[i]));
-        mx1 = fmaxf(mx1, __uint_as_float(sv[i + 1]));
-        mx2 = fmaxf(mx2, __uint_as_float(sv[i + 2]));
-        mx3 = fmaxf(mx3, __uint_as_float(sv[i + 3]));
+      for (int i = 0; i < 128; i += 8) {  // FMNMX3: two new values per instruction
+        mx0 = max3(mx0, __uint_as_float(sv[i]), __uint_as_float(sv[i + 1]));
+        mx1 = max3(mx1, __uint_as_float(sv[i + 2]), __uint_as_float(sv[i + 3]));
+        mx2 = max3(mx2, __uint_as_float(sv[i + 4]), __uint_as_float(sv[i + 5]));
+        mx3 = max3(mx3, __uint_as_float(sv[i + 6]), __uint_as_float(sv[i + 7]));
       }
       const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
       // refresh the reference maximum only when it is stale by more than 2^AT_RESCALE_LOG2 (always on the first tile)
@@ -185,17 +217,26 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
         m_used = mx;
       }
       const float mb = m_used * sl2;
-      float sum0 = 0.f, sum1 = 0.f;
+      // exponent = s * scale*log2e - m*scale*log2e: two columns per FFMA2 / FADD2 (half the issue slots of scalar fp32).
+      // Moving a share of the exponentials to an FMA-pipe polynomial (Cody-Waite + degree 3, as FlashAttention-4 does) was
+      // measured and rejected: 25 / 37.5 / 50 % of the columns cost +4 / +6.5 / +8.5 % (profiles/r01b_attn_ab.log) — FFMA2
+      // does not double the fp32 rate on this part, so the polynomial is no cheaper than the MUFU it replaces.
+      const uint64_t sl2_2 = pack2(sl2, sl2), nmb2 = pack2(-mb, -mb);
+      uint64_t sumA = 0ull, sumB = 0ull;  // (0.f, 0.f)
       uint32_t pk[64];
 #pragma unroll
       for (int i = 0; i < 64; ++i) {
-        const float e0 = ex2(fmaf(__uint_as_float(sv[2 * i]), sl2, -mb));
-        const float e1 = ex2(fmaf(__uint_as_float(sv[2 * i + 1]), sl2, -mb));
-        sum0 += e0;
-        sum1 += e1;
+        const uint64_t x2 = fma2(pack2u(sv[2 * i], sv[2 * i + 1]), sl2_2, nmb2);
+        float x0, x1;
+        unpack2(x2, x0, x1);
+        const float e0 = ex2(x0), e1 = ex2(x1);
+        if (i & 1) sumB = add2(sumB, pack2(e0, e1));
+        else sumA = add2(sumA, pack2(e0, e1));
         pk[i] = pack_bf16x2(e0, e1);
       }
-      l = l * alpha + (sum0 + sum1);
+      float s0, s1;
+      unpack2(add2(sumA, sumB), s0, s1);
+      l = l * alpha + (s0 + s1);
       if (j > 0) {
         mbar_wait(o_full, (j - 1) & 1);  // PV(j-1) retired: sP may be overwritten, O may be touched
         tc_fence_after();
