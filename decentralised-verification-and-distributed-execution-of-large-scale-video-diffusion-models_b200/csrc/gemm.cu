@@ -131,6 +131,7 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
   const int group = (warp - 2) >> 2;
   const int c_base = group * NCH * 16;
   const int lane_off = lane * (Cfg::PANEL_COLS * 2);
+  const uint32_t stage_u32 = smem_u32(stage0);
 
   // TMA coordinates of this warp's part of a tile: (first column, first row inside the slab, slab)
   auto tile_col = [&](int tile) { return (tile % p.num_n_tiles) * OUT_COLS + c_base; };
@@ -170,7 +171,7 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
       const int c = ch * 16;
       const int k = ch % CH_PER_PANEL, panel = ch / CH_PER_PANEL;
       const int buf = q % NBUF;
-      uint8_t* srow = stage0 + buf * Cfg::PANEL_BYTES + lane_off;
+      const uint32_t srow = stage_u32 + buf * Cfg::PANEL_BYTES + lane_off;  // shared-space address: STS / LDS, not generic
       if (k == 0) {
         // ---- panel start: the buffer(s) about to be (over)written must have been read out by their TMA store ----
         if (lane == 0) {
@@ -241,9 +242,9 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
       for (int j = 0; j < 2; ++j) {
         const int piece = 2 * k + j;
         const int pos = Cfg::PANEL_SWIZZLE ? (piece ^ (lane & 7)) : piece;
-        uint4* dst = reinterpret_cast<uint4*>(srow + (pos << 4));
+        const uint32_t dst = srow + (pos << 4);
         if (RES) {
-          const uint4 r = *dst;
+          const uint4 r = lds128(dst);
           const float2 a = unpack_bf16x2(r.x), b = unpack_bf16x2(r.y), cc = unpack_bf16x2(r.z), d = unpack_bf16x2(r.w);
           f[8 * j] += a.x; f[8 * j + 1] += a.y; f[8 * j + 2] += b.x; f[8 * j + 3] += b.y;
           f[8 * j + 4] += cc.x; f[8 * j + 5] += cc.y; f[8 * j + 6] += d.x; f[8 * j + 7] += d.y;
@@ -253,7 +254,7 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
         o.y = pack_bf16x2(f[8 * j + 2], f[8 * j + 3]);
         o.z = pack_bf16x2(f[8 * j + 4], f[8 * j + 5]);
         o.w = pack_bf16x2(f[8 * j + 6], f[8 * j + 7]);
-        *dst = o;
+        sts128(dst, o);
       }
       if (k == CH_PER_PANEL - 1) {
         // ---- panel complete: ONE TMA store of 32 rows x PANEL_COLS (rows outside the tensor / slab are clipped) ----

@@ -293,6 +293,25 @@ inline int grid_1d(int64_t work_items, int block, int per_sm) {
   return g < 1 ? 1 : (int)g;
 }
 
+// CTAs of `kernel` the device holds at once at this block size (registers / threads / shared memory, asked of the
+// runtime). The HBM-stream kernels size their grids to whole waves of it: a grid of 2.02 waves costs 3 (ncu r01b: the
+// GroupNorm passes ran 896 CTAs on 444 slots).
+template <class K>
+int resident_slots(K kernel, int threads, size_t smem) {
+  int n = 0;
+  if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&n, kernel, threads, smem) != cudaSuccess || n < 1) n = 1;
+  return n * sm_count();
+}
+
+// grid of a grid-stride kernel: everything resident at once, never more CTAs than there is work
+template <class K>
+int grid_resident(K kernel, int64_t work_items, int block, size_t smem = 0) {
+  const int64_t need = (work_items + block - 1) / block;
+  const int64_t slots = resident_slots(kernel, block, smem);
+  const int64_t g = need < slots ? need : slots;
+  return g < 1 ? 1 : (int)g;
+}
+
 }  // namespace
 
 // rows per pass: as many as fit GN_MAX_THREADS threads of one 16-byte vector each
@@ -302,17 +321,34 @@ static int gn_rpp(int C) {
   return rpp < 1 ? 1 : rpp;
 }
 
-int gn_splits(int64_t n_items, int64_t rows_per_item) {
-  // enough CTAs per item to fill the machine ~6x (<= 384-thread CTAs, 5-6 resident per SM), at least 32 rows each
-  int64_t splits = ((int64_t)sm_count() * 6 + n_items - 1) / n_items;
+// CTAs per item. The grid (splits x n_items) is sized to 1-3 WHOLE waves of the resident slots, whichever wastes least
+// (each CTA walks a contiguous row range, so a partial last wave costs a full one), at least 32 rows per CTA.
+static int gn_splits(int64_t n_items, int64_t rows_per_item, int64_t slots) {
   const int64_t max_splits = (rows_per_item + 31) / 32;
-  if (splits > max_splits) splits = max_splits;
-  if (splits < 1) splits = 1;
-  return (int)splits;
+  int64_t best = 1;
+  double best_util = -1.0;
+  for (int w = 1; w <= 3; ++w) {
+    int64_t sp = (w * slots) / n_items;
+    if (sp > max_splits) sp = max_splits;
+    if (sp < 1) sp = 1;
+    const int64_t ctas = sp * n_items;
+    const int64_t waves = (ctas + slots - 1) / slots;
+    const double util = (double)ctas / (double)(waves * slots);
+    if (util > best_util + 0.02) { best_util = util; best = sp; }
+  }
+  return (int)best;
+}
+
+// upper bound of gn_splits over every block size the kernels use (<= 10 CTAs of >= 193 threads per SM, 3 waves)
+static int64_t gn_splits_bound(int64_t n_items, int64_t rows_per_item) {
+  int64_t sp = ((int64_t)sm_count() * 30 + n_items - 1) / n_items;
+  const int64_t max_splits = (rows_per_item + 31) / 32;
+  if (sp > max_splits) sp = max_splits;
+  return sp < 1 ? 1 : sp;
 }
 
 size_t group_norm_scratch_bytes(int64_t n_items, int64_t rows_per_item, int groups) {
-  const size_t partial = sizeof(float) * 2 * (size_t)n_items * gn_splits(n_items, rows_per_item) * groups;
+  const size_t partial = sizeof(float) * 2 * (size_t)n_items * gn_splits_bound(n_items, rows_per_item) * groups;
   return ((partial + 255) & ~(size_t)255) + sizeof(float2) * (size_t)n_items * groups;
 }
 
@@ -323,14 +359,17 @@ int group_norm(const void* x1, int C1, const void* x2, int C2, const float* gamm
   B2V_CHECK(C % 8 == 0 && C1 % 8 == 0 && C % groups == 0 && (C / groups) % 2 == 0, "group_norm: C=%d (C1=%d) groups=%d unsupported", C, C1, groups);
   B2V_CHECK(C <= GN_MAX_THREADS * 8, "group_norm: C=%d too wide (max %d)", C, GN_MAX_THREADS * 8);
   B2V_CHECK(n_items > 0 && n_items < 65536 && rows_per_item > 0, "group_norm: bad item count");
-  const int splits = gn_splits(n_items, rows_per_item);
-  float* partial = (float*)scratch;
-  const size_t pbytes = sizeof(float) * 2 * (size_t)n_items * splits * groups;
-  float2* stats = (float2*)((uint8_t*)scratch + ((pbytes + 255) & ~(size_t)255));
-  dim3 grid((unsigned)splits, (unsigned)n_items);
   const int rpp = gn_rpp(C);
   const int threads = (C >> 3) * rpp;
   const size_t shb = sizeof(float) * 2 * rpp * (C >> 1);
+  const int s1 = resident_slots(gn_stats_kernel, threads, shb), s2 = resident_slots(gn_apply_kernel, threads, 0);
+  const int splits = gn_splits(n_items, rows_per_item, s1 < s2 ? s1 : s2);
+  float* partial = (float*)scratch;
+  const size_t pbytes = sizeof(float) * 2 * (size_t)n_items * splits * groups;
+  B2V_CHECK(pbytes + 256 + sizeof(float2) * (size_t)n_items * groups <= group_norm_scratch_bytes(n_items, rows_per_item, groups) + 256,
+            "group_norm: scratch too small for %d splits", splits);
+  float2* stats = (float2*)((uint8_t*)scratch + ((pbytes + 255) & ~(size_t)255));
+  dim3 grid((unsigned)splits, (unsigned)n_items);
   gn_stats_kernel<<<grid, threads, shb, s>>>((const __nv_bfloat16*)x1, C1, (const __nv_bfloat16*)x2, C2, rows_per_item,
                                             groups, rpp, partial);
   count_launch();
@@ -356,9 +395,9 @@ int layer_norm(const void* x, const float* gamma, const float* beta, void* y, in
   B2V_CHECK(vecs % lpr == 0 && vecs / lpr <= 8, "layer_norm: C=%d has no lane mapping", C);
   const int v = vecs / lpr;
   const int64_t warps = (rows + (32 / lpr) - 1) / (32 / lpr);
-  const int grid = grid_1d(warps * 32, 256, 8);
 #define B2V_LN(L, V)                                                                                                 \
   if (lpr == L && v == V) {                                                                                          \
+    const int grid = grid_resident(layer_norm_kernel<L, V>, warps * 32, 256);                                        \
     layer_norm_kernel<L, V><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, gamma, beta, (__nv_bfloat16*)y, rows, C, eps); \
     launched = true;                                                                                                 \
   }

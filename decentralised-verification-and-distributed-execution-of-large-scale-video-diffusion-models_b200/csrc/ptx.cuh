@@ -64,6 +64,16 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
   }
 }
 
+// explicit shared-space 16-byte accesses (a generic pointer into shared memory compiles to ST.E / LD.E plus a MEMBAR in
+// front of the proxy fence)
+__device__ __forceinline__ void sts128(uint32_t addr, const uint4& v) {
+  asm volatile("st.shared.v4.b32 [%0], {%1, %2, %3, %4};" ::"r"(addr), "r"(v.x), "r"(v.y), "r"(v.z), "r"(v.w) : "memory");
+}
+__device__ __forceinline__ uint4 lds128(uint32_t addr) {
+  uint4 v;
+  asm volatile("ld.shared.v4.b32 {%0, %1, %2, %3}, [%4];" : "=r"(v.x), "=r"(v.y), "=r"(v.z), "=r"(v.w) : "r"(addr) : "memory");
+  return v;
+}
 __device__ __forceinline__ void fence_proxy_async_smem() {
   asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
 }
@@ -167,8 +177,12 @@ __device__ __forceinline__ uint32_t mapa_shared(uint32_t addr, uint32_t rank) {
   asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(r) : "r"(addr), "r"(rank));
   return r;
 }
+// Remote arrive on a peer CTA's mbarrier. No `.release.cluster` qualifier on purpose: ptxas turns that into MEMBAR.ALL.GPU
+// + ERRBAR + CCTL.IVALL (an L1 invalidate) in front of every arrive — 28 % of the stall samples of the CTA-pair GEMM
+// (ncu r01d). The arrive only hands a TMEM accumulator back (ordered by tcgen05.fence::before_thread_sync); no
+// generic-proxy data travels with it.
 __device__ __forceinline__ void mbar_arrive_cluster(uint32_t cluster_addr) {
-  asm volatile("mbarrier.arrive.release.cluster.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
+  asm volatile("mbarrier.arrive.shared::cluster.b64 _, [%0];" ::"r"(cluster_addr) : "memory");
 }
 constexpr uint32_t kPeerBitMask = 0xFEFFFFFFu;  // clears the CTA-pair rank bit of a shared-memory address: -> leader CTA
 // TMA loads of a CTA pair: the data lands in THIS CTA's shared memory, the transaction bytes are counted on the

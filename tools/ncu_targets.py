@@ -25,17 +25,20 @@ def t(fn, name):
     print("%-40s %.3f ms" % (name, e0.elapsed_time(e1)), flush=True)
 
 
-if what in ("gemm", "all"):
-    for (m, n, k, flags, r) in [(M, 960, 320, 0, 0), (M, 320, 320, 0, 1), (M, 2560, 320, 1, 0), (18432, 3840, 1280, 0, 0)]:
+if what in ("gemm", "gemm2", "all"):
+    shapes = [(M, 960, 320, 0, 0), (M, 320, 320, 0, 1), (M, 2560, 320, 1, 0), (18432, 3840, 1280, 0, 0)]
+    if what == "gemm2":
+        shapes = [(73728, 640, 640, 0, 1), (73728, 1920, 640, 0, 0), (18432, 1280, 1280, 0, 1), (73728, 5120, 640, 1, 0)]
+    for (m, n, k, flags, r) in shapes:
         a = torch.randn(m, k, device=dev).bfloat16()
         w = (torch.randn(n, k, device=dev) / math.sqrt(k)).bfloat16()
         bias = torch.zeros(n, device=dev)
         out = torch.randn(m, n // 2 if flags & 1 else n, device=dev).bfloat16()
         t(lambda: ops.gemm(a, w, bias=bias, residual=out if r else None, flags=flags, out=out), "gemm %d %d %d f%d r%d" % (m, n, k, flags, r))
 if what in ("attn", "all"):
-    nb, heads, S = 8, 5, 9216
+    nb, heads, S = 32, 5, 9216  # the shape bench.py's roofline times (2 x 16 frames)
     q, k, v = (torch.randn(nb, S, heads * 64, device=dev).bfloat16() for _ in range(3))
-    t(lambda: ops.attention(q, k, v, heads), "attention nb=8 h=5 S=9216")
+    t(lambda: ops.attention(q, k, v, heads), "attention nb=32 h=5 S=9216")
 if what in ("norm", "all"):
     x = torch.randn(M, 320, device=dev).bfloat16()
     g, b = torch.ones(320, device=dev), torch.zeros(320, device=dev)
