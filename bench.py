@@ -378,7 +378,7 @@ def gpu_main(args):
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "roofline_step": roofline_step,
         "merkle": merkle, "cpu_baseline": cpu,
     }
-    print(json.dumps(line), flush=True)
+    emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
@@ -444,7 +444,25 @@ def merkle_bench(torch, ops, proof, dev, peaks, h, w):
     return out
 
 
+_REAL_STDOUT = None
+
+
+def emit(line):
+    """The ONE JSON line goes to the process's original stdout; everything else written to fd 1 while the bench runs
+    (NCCL prints its version banner there) is diverted to stderr by main()."""
+    data = (json.dumps(line) + "\n").encode()
+    if _REAL_STDOUT is None:
+        sys.stdout.write(data.decode())
+        sys.stdout.flush()
+    else:
+        os.write(_REAL_STDOUT, data)
+
+
 def main():
+    global _REAL_STDOUT
+    sys.stdout.flush()
+    _REAL_STDOUT = os.dup(1)
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
@@ -463,14 +481,14 @@ def main():
         h, w = HEIGHT // 8, WIDTH // 8
         # the CPU arm has one host: it executes every rank's windows, i.e. the whole-video step
         value, per, cpu = cpu_line(args, plan.ranges, h, w, as_reference=True)
-        print(json.dumps({
+        emit({
             "impl": "reference", "metric": METRIC, "value": value, "unit": "steps/s", "n_gpus": args.gpus,
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": 1e3 / value, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "config": {"workload": "ZeroscopeXL 1024x576x24f fsdp_chunked_coherent hybrid_ctx, CFG 7.5 (CPU oracle port)",
                        "plan": {"note": note, "windows": plan.ranges}},
             "cpu_baseline": cpu, "e2e": {"value": value, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
-            "gpu_launches": 0}), flush=True)
+            "gpu_launches": 0})
         return
     gpu_main(args)
 

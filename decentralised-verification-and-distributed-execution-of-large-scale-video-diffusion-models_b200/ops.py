@@ -77,30 +77,41 @@ def context_mean(base):
     return ctx
 
 
+def blend_overlap_ptrs(ptrs, ranges, weights, T, Cc, h, w, dtype, device, return_full=False):
+    """b2v_blend_overlap on raw device pointers: ptrs[i] -> [1,C,len_i,h,w] of `dtype` in THIS device's address space —
+    local memory or a peer GPU's memory mapped over NVLink (exchange.PeerWindows): the kernel then pulls the windows out
+    of the owners' HBM while it blends. Returns fp32 [1,C,T,h,w] (and the `dtype` accumulator when return_full)."""
+    import numpy as np
+    lib = _lib.load()
+    n = len(ptrs)
+    if n == 0:
+        raise ValueError("no chunks")
+    cp = (C.c_void_p * n)(*[int(p) for p in ptrs])
+    starts = (C.c_int * n)(*[int(s) for s, _ in ranges])
+    ends = (C.c_int * n)(*[int(e) for _, e in ranges])
+    wflat = np.concatenate([np.asarray(wi, dtype=np.float32).reshape(-1) for wi in weights]).astype(np.float32)
+    if wflat.size != sum(e - s for s, e in ranges):
+        raise ValueError("one weight per frame of every chunk is required")
+    out = torch.empty((1, Cc, T, h, w), dtype=torch.float32, device=device)
+    full = torch.empty((1, Cc, T, h, w), dtype=dtype, device=device) if return_full else None
+    check(lib.b2v_blend_overlap(cp, starts, ends, n, wflat.ctypes.data_as(C.c_void_p), Cc, T, h * w, _DT[dtype],
+                                ptr(out), ptr(full), stream()))
+    return (out, full) if return_full else out
+
+
 def blend_overlap(chunks, ranges, weights, T, return_full=False):
     """chunks[i]: CUDA [1,C,len_i,h,w]; ranges[i] = (s,e); weights[i]: python/torch fp32 per-frame weights.
     Returns fp32 [1,C,T,h,w] (and the accumulator in the chunks' dtype when return_full)."""
-    import numpy as np
-    lib = _lib.load()
-    n = len(chunks)
-    if n == 0:
+    if len(chunks) == 0:
         raise ValueError("no chunks")
     for c in chunks:
         _cuda(c, "chunk")
     _, Cc, _, h, w = chunks[0].shape
     dev, dt = chunks[0].device, chunks[0].dtype
-    ptrs = (C.c_void_p * n)(*[c.data_ptr() for c in chunks])
-    starts = (C.c_int * n)(*[int(s) for s, _ in ranges])
-    ends = (C.c_int * n)(*[int(e) for _, e in ranges])
-    wflat = np.concatenate([np.asarray(wi, dtype=np.float32).reshape(-1) for wi in weights]).astype(np.float32)
     for (s, e), c in zip(ranges, chunks):
         if c.shape[2] != e - s or c.dtype != dt:
             raise ValueError("chunk shape/dtype does not match its range")
-    out = torch.empty((1, Cc, T, h, w), dtype=torch.float32, device=dev)
-    full = torch.empty((1, Cc, T, h, w), dtype=dt, device=dev) if return_full else None
-    check(lib.b2v_blend_overlap(ptrs, starts, ends, n, wflat.ctypes.data_as(C.c_void_p), Cc, T, h * w, _DT[dt],
-                                ptr(out), ptr(full), stream()))
-    return (out, full) if return_full else out
+    return blend_overlap_ptrs([c.data_ptr() for c in chunks], ranges, weights, T, Cc, h, w, dt, dev, return_full)
 
 
 # ---- proof -----------------------------------------------------------------------------------------------------

@@ -18,7 +18,7 @@ import time
 import torch
 import torch.distributed as dist
 
-from .. import ops, planner
+from .. import exchange, ops, planner
 
 LOG = logging.getLogger("b2v.strategy")
 
@@ -47,6 +47,9 @@ def add_common_args(p, num_frames=32, out_csv="benchmarks.csv", chunking=True):
     # additions that do not exist in the reference (defaults keep its behaviour)
     p.add_argument("--seed", type=int, default=1234, help="seed of the random-init weights (no checkpoint download)")
     p.add_argument("--dtype", default="bf16", choices=["bf16", "fp16", "fp32"], help="I/O dtype of the latents")
+    p.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
+                   help="end-of-denoise window exchange: p2p = blend kernel reads the peers' windows over NVLink "
+                        "(fused exchange + blend), nccl = all_gather then blend")
     return p
 
 
@@ -106,36 +109,8 @@ class CudaDenoiser:
 
 
 def exchange_windows(my_windows, plan, rank, world, device):
-    """All ranks end up with every window, in gather order (rank 0's list, rank 1's, ...): one all_gather of a
-    device buffer padded to the longest per-rank payload. Returns (list of (s, e, tensor), seconds)."""
-    if world == 1:
-        return [(s, e, t) for (s, e, t) in my_windows], 0.0
-    shape = my_windows[0][2].shape  # [1,C,len,h,w]
-    C, h, w = shape[1], shape[3], shape[4]
-    dtype = my_windows[0][2].dtype
-    per_rank = [plan.of_rank(r) for r in range(world)]
-    frames = [sum(e - s for s, e in lst) for lst in per_rank]
-    cap = max(frames)
-    send = torch.zeros((C, cap, h, w), dtype=dtype, device=device)
-    off = 0
-    for s, e, t in my_windows:
-        send[:, off:off + (e - s)] = t[0]
-        off += e - s
-    recv = torch.empty((world, C, cap, h, w), dtype=dtype, device=device)
-    if device.type == "cuda":
-        torch.cuda.synchronize(device)
-    t0 = time.time()
-    dist.all_gather_into_tensor(recv.view(-1), send.view(-1))
-    if device.type == "cuda":
-        torch.cuda.synchronize(device)
-    dt = time.time() - t0
-    out = []
-    for r in range(world):
-        off = 0
-        for s, e in per_rank[r]:
-            out.append((s, e, recv[r, :, off:off + (e - s)].unsqueeze(0).contiguous()))
-            off += e - s
-    return out, dt
+    """NCCL / gloo transport: every rank receives every window (exchange.nccl_all_gather)."""
+    return exchange.nccl_all_gather(my_windows, plan, rank, world, device)
 
 
 def cuda_blend(windows, T, ov):
@@ -277,8 +252,18 @@ class WindowedDiffuser:
             dist.barrier()
         payload = planner.payload_bytes([(s, e) for s, e, _ in mine], self.unet.config.in_channels)
         emulate_network(payload, cfg)
-        windows, gather_s = exchange_windows(mine, plan, self.rank, self.world, self.device)
-        lat = self._blend(windows, T, plan.overlap)
+        if cuda and self.world > 1 and self._blend_fn is None and getattr(cfg, "exchange", "p2p") == "p2p":
+            # fused exchange + blend: ONE kernel pulls every window out of its owner's HBM over NVLink and blends
+            if getattr(self, "_peer_windows", None) is None:
+                t = mine[0][2]
+                self._peer_windows = exchange.PeerWindows(plan, self.world, self.rank, t.shape[1], t.shape[3],
+                                                          t.shape[4], t.dtype, self.device)
+            lat, gather_s = self._peer_windows.gather_blend(mine, T, plan.overlap)
+            self.timings["exchange"] = "p2p"
+        else:
+            windows, gather_s = exchange_windows(mine, plan, self.rank, self.world, self.device)
+            lat = self._blend(windows, T, plan.overlap)
+            self.timings["exchange"] = "nccl" if self.world > 1 else "local"
         self.latents = lat
         frames = self.decode(lat)
         if self.rank == 0 and frames:

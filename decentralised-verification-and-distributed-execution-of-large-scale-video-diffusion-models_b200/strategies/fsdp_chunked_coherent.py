@@ -7,7 +7,14 @@ all-gather."""
 import argparse
 import logging
 
-from .common import WindowedDiffuser, add_common_args, run_cli
+if __package__ in (None, ""):  # run by path like the reference: torchrun --nproc_per_node=W <pkg>/strategies/fsdp_chunked_coherent.py ...
+    import os
+    import sys
+    sys.path.insert(0, os.path.join(os.path.dirname(os.path.abspath(__file__)), "..", ".."))
+    import b2v  # noqa: F401
+    from b2v.strategies.common import WindowedDiffuser, add_common_args, run_cli
+else:
+    from .common import WindowedDiffuser, add_common_args, run_cli
 
 
 class DistributedVideoDiffuser(WindowedDiffuser):
