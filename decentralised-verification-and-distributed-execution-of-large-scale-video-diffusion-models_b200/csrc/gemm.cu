@@ -540,10 +540,10 @@ int dispatch_gemm(int bn, bool geglu, const CUtensorMap& tmA, const CUtensorMap&
   return fail(B2V_ERR_ARG, "no tile for N");
 }
 
-// CTA pairs pay off when the tile is MMA / operand-fill bound: enough 128-row tiles to pair up inside a slab and to fill
-// the machine, and a reduction of >= 640 (measured: with K = 320 the GEMM is bound by its epilogue / HBM and the
-// lock-step of the pair costs 10-30 %; from K = 640 up pairs win 5-15 %). B2V_GEMM_CG=1|2 forces the choice (A/B).
-static int pick_cg(int64_t m_tiles_per_slab, int64_t total_tiles, int64_t k_total) {
+// CTA pairs (256-row units, each CTA stages its own A rows and half of B) win or tie on every shape of the census since
+// the remote accumulator hand-back became a plain arrive (profiles/r01g_gemm_tile_ab.md: K = 320 GEGLU -8 %, N = 960 -6 %,
+// small-M convs -18 %); the only requirement is two 128-row tiles inside a slab. B2V_GEMM_CG=1|2 forces the choice (A/B).
+static int pick_cg(int64_t m_tiles_per_slab) {
   static int forced = -1;
   if (forced < 0) {
     const char* e = getenv("B2V_GEMM_CG");
@@ -551,18 +551,41 @@ static int pick_cg(int64_t m_tiles_per_slab, int64_t total_tiles, int64_t k_tota
   }
   if (m_tiles_per_slab < 2) return 1;
   if (forced == 1 || forced == 2) return forced;
-  return (total_tiles >= 2 * (int64_t)sm_count() && k_total >= 640) ? 2 : 1;
+  return 2;
 }
 
 }  // namespace
 
-int pick_bn(int N, bool geglu) {
+// Tile width. Candidates are the instantiated widths that divide N; the cost of a candidate is
+// waves x (BN + 64): waves = ceil(tiles / resident tile slots) is the wave quantisation (it decides the small-M levels:
+// M = 4608, N = 1280 runs 2 waves at BN = 160 against 2 much longer ones at 256), and BN + 64 is the per-tile time — the
+// B columns plus a fixed share for the A tile / epilogue hand-over, which is what makes 160 beat 128 at N = 640 / 1920
+// (4 instead of 5 A re-reads; measured -8 % to -23 %, profiles/r01g_gemm_tile_ab.md). m_units = row units (128 x CG rows)
+// of the whole problem; 0 = unknown (widest tile that divides N). GEGLU tiles are 256 wide by construction of the weight
+// interleave.
+int pick_bn(int N, bool geglu, int64_t m_units, int cg) {
   if (geglu) return (N % 256 == 0) ? 256 : 0;
-  if (N % 256 == 0) return 256;
-  if (N % 160 == 0 && N % 128 != 0) return 160;
-  if (N % 128 == 0) return 128;
-  if (N % 64 == 0) return 64;
-  return 0;
+  static int forced = -1;  // B2V_GEMM_BN=64|128|160|256 forces the tile width where it divides N (A/B knob of tools/)
+  if (forced < 0) {
+    const char* e = getenv("B2V_GEMM_BN");
+    forced = e ? atoi(e) : 0;
+  }
+  if ((forced == 64 || forced == 128 || forced == 160 || forced == 256) && N % forced == 0) return forced;
+  const int cand[3] = {256, 160, 128};
+  const int64_t slots = sm_count() / (cg < 1 ? 1 : cg);
+  int best = 0;
+  int64_t best_cost = 0;
+  for (int i = 0; i < 3; ++i) {
+    const int bn = cand[i];
+    if (N % bn != 0) continue;
+    if (m_units <= 0) return bn;
+    const int64_t tiles = m_units * (N / bn);
+    const int64_t waves = (tiles + slots - 1) / slots;
+    const int64_t cost = waves * (bn + 64);
+    if (best == 0 || cost < best_cost) { best = bn; best_cost = cost; }
+  }
+  if (best) return best;
+  return (N % 64 == 0) ? 64 : 0;
 }
 
 static bool trace_on() {
@@ -577,8 +600,6 @@ int gemm_tiled(const GemmArgs& g, cudaStream_t s) {
     fprintf(stderr, "B2VTRACE gemm M=%lld N=%d K=%d taps=%d flags=%d res=%d rpb=%lld trs=%lld\n", (long long)g.M, g.N,
             g.Kc, g.taps, g.flags, g.residual != nullptr, (long long)g.rows_per_batch, (long long)g.tap_row_stride);
   const bool geglu = (g.flags & B2V_EPI_GEGLU) != 0;
-  const int bn = pick_bn(g.N, geglu);
-  B2V_CHECK(bn != 0, "GEMM N=%d has no supported tile (needs a multiple of 64; GEGLU of 256)", g.N);
   B2V_CHECK(g.Kc % BK == 0 && g.Kc > 0, "GEMM Kc=%d must be a multiple of 64", g.Kc);
   B2V_CHECK(g.taps == 1 || g.taps == 3, "tiled GEMM supports 1 or 3 taps");
   B2V_CHECK(!(geglu && (g.residual || g.rowbias)), "the GEGLU epilogue takes no residual / row bias");
@@ -587,7 +608,9 @@ int gemm_tiled(const GemmArgs& g, cudaStream_t s) {
   const int64_t lda = g.lda > 0 ? g.lda : g.Kc;
   const int64_t slabs = g.M / rpb;
   const int64_t m_tiles_per_slab = (rpb + BM - 1) / BM;
-  const int cg = pick_cg(m_tiles_per_slab, slabs * m_tiles_per_slab * (g.N / bn), (int64_t)g.taps * g.Kc);
+  const int cg = pick_cg(m_tiles_per_slab);
+  const int bn = pick_bn(g.N, geglu, slabs * ((m_tiles_per_slab + cg - 1) / cg), cg);
+  B2V_CHECK(bn != 0, "GEMM N=%d has no supported tile (needs a multiple of 64; GEGLU of 256)", g.N);
   CUtensorMap tmA, tmB;
   {
     const uint64_t dims[3] = {(uint64_t)g.Kc, (uint64_t)rpb, (uint64_t)slabs};
@@ -622,13 +645,13 @@ int gemm_tiled(const GemmArgs& g, cudaStream_t s) {
 int conv3x3_im2col(const ConvArgs& c, cudaStream_t s) {
   if (trace_on())
     fprintf(stderr, "B2VTRACE conv N=%d H=%d W=%d Cin=%d Cout=%d stride=%d\n", c.N, c.H, c.W, c.Cin, c.Cout, c.stride);
-  const int bn = pick_bn(c.Cout, false);
-  B2V_CHECK(bn != 0, "conv Cout=%d must be a multiple of 64", c.Cout);
   B2V_CHECK(c.Cin % BK == 0, "conv Cin=%d must be a multiple of 64", c.Cin);
   B2V_CHECK(c.stride == 1 || c.stride == 2, "conv stride must be 1 or 2");
   const int P = (c.H - 1) / c.stride + 1, Q = (c.W - 1) / c.stride + 1;
   const int64_t m_tiles = ((int64_t)c.N * P * Q + BM - 1) / BM;
-  const int cg = c.ncfhw_out ? 1 : pick_cg(m_tiles, m_tiles * (c.Cout / bn), 9ll * c.Cin);
+  const int cg = c.ncfhw_out ? 1 : pick_cg(m_tiles);
+  const int bn = pick_bn(c.Cout, false, (m_tiles + cg - 1) / cg, cg);
+  B2V_CHECK(bn != 0, "conv Cout=%d must be a multiple of 64", c.Cout);
   CUtensorMap tmA, tmB;
   {
     const uint64_t dims[4] = {(uint64_t)c.Cin, (uint64_t)c.W, (uint64_t)c.H, (uint64_t)c.N};

@@ -50,7 +50,7 @@ struct ConvArgs {
   int ncfhw_dtype = 0, ncfhw_cout = 0, ncfhw_F = 1;
 };
 
-int pick_bn(int N, bool geglu);
+int pick_bn(int N, bool geglu, int64_t m_units = 0, int cg = 1);
 int gemm_tiled(const GemmArgs& g, cudaStream_t s);
 int conv3x3_im2col(const ConvArgs& c, cudaStream_t s);
 
