@@ -165,6 +165,36 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
     const uint32_t tacc = tmem_base + acc * Cfg::ACC_STRIDE + ((uint32_t)(quarter * 32) << 16);
     uint32_t v[2][16];
     uint32_t g[GEGLU ? 2 : 1][16];
+    // bias (+ time-embedding row bias) of a chunk is fetched ONE CHUNK AHEAD, together with the chunk's TMEM load: the
+    // adds used to sit right behind their own loads (ncu r01b: 22 % of the GEGLU kernel's stall samples were FADDs
+    // waiting on the scoreboard of those LDGs)
+    float bv[2][16];
+    float bg[GEGLU ? 2 : 1][16];
+    // (GEGLU tiles only: on the plain epilogues, which are bound by their stores, the extra live registers cost 4-7 %)
+    const bool has_b = GEGLU && p.bias != nullptr;
+    auto fetch_bias = [&](int ch, int slot) {
+      const int c = ch * 16;
+      if (p.bias) {
+        const float4* b4 = reinterpret_cast<const float4*>(p.bias + wcol0 + c);
+#pragma unroll
+        for (int j = 0; j < 4; ++j) {
+          const float4 b = __ldg(b4 + j);
+          bv[slot][4 * j] = b.x; bv[slot][4 * j + 1] = b.y; bv[slot][4 * j + 2] = b.z; bv[slot][4 * j + 3] = b.w;
+        }
+        if constexpr (GEGLU) {
+          const float4* g4 = reinterpret_cast<const float4*>(p.bias + wcol0 + BN / 2 + c);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float4 b = __ldg(g4 + j);
+            bg[slot][4 * j] = b.x; bg[slot][4 * j + 1] = b.y; bg[slot][4 * j + 2] = b.z; bg[slot][4 * j + 3] = b.w;
+          }
+        }
+      } else {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) { bv[slot][j] = 0.f; if constexpr (GEGLU) bg[slot][j] = 0.f; }
+      }
+    };
+    if (has_b) fetch_bias(0, 0);
 #pragma unroll
     for (int ch = 0; ch < NCH; ++ch) {
       const int cur = ch & 1, nxt = cur ^ 1;
@@ -197,33 +227,24 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
       if (ch + 1 < NCH) {
         tmem_ld16(tacc + c_base + c + 16, v[nxt]);
         if constexpr (GEGLU) tmem_ld16(tacc + BN / 2 + c_base + c + 16, g[nxt]);
+        if (has_b) fetch_bias(ch + 1, nxt);
       }
       float f[16];
 #pragma unroll
       for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[cur][j]);
-      if (p.bias) {
-        const float4* b4 = reinterpret_cast<const float4*>(p.bias + wcol0 + c);
+      if (has_b) {
 #pragma unroll
-        for (int j = 0; j < 4; ++j) {
-          const float4 b = __ldg(b4 + j);
-          f[4 * j] += b.x; f[4 * j + 1] += b.y; f[4 * j + 2] += b.z; f[4 * j + 3] += b.w;
-        }
+        for (int j = 0; j < 16; ++j) f[j] += bv[cur][j];
       }
-      if constexpr (GEGLU) {
-        float gt[16];
-#pragma unroll
-        for (int j = 0; j < 16; ++j) gt[j] = __uint_as_float(g[cur][j]);
+      if constexpr (!GEGLU) {
         if (p.bias) {
-          const float4* b4 = reinterpret_cast<const float4*>(p.bias + wcol0 + BN / 2 + c);
+          const float4* b4 = reinterpret_cast<const float4*>(p.bias + wcol0 + c);
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
             const float4 b = __ldg(b4 + j);
-            gt[4 * j] += b.x; gt[4 * j + 1] += b.y; gt[4 * j + 2] += b.z; gt[4 * j + 3] += b.w;
+            f[4 * j] += b.x; f[4 * j + 1] += b.y; f[4 * j + 2] += b.z; f[4 * j + 3] += b.w;
           }
         }
-#pragma unroll
-        for (int j = 0; j < 16; ++j) f[j] *= gelu_fast(gt[j]);
-      } else {
         if (rb) {
           const float4* r4 = reinterpret_cast<const float4*>(rb + c);
 #pragma unroll
@@ -232,6 +253,18 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
             f[4 * j] += b.x; f[4 * j + 1] += b.y; f[4 * j + 2] += b.z; f[4 * j + 3] += b.w;
           }
         }
+      }
+      if constexpr (GEGLU) {
+        float gt[16];
+#pragma unroll
+        for (int j = 0; j < 16; ++j) gt[j] = __uint_as_float(g[cur][j]);
+        if (has_b) {
+#pragma unroll
+          for (int j = 0; j < 16; ++j) gt[j] += bg[cur][j];
+        }
+#pragma unroll
+        for (int j = 0; j < 16; ++j) f[j] *= gelu_fast(gt[j]);
+      } else {
         if (p.gelu) {
 #pragma unroll
           for (int j = 0; j < 16; ++j) f[j] = gelu_fast(f[j]);

@@ -18,7 +18,7 @@ namespace {
 // pass 1: per-(item, group) sum / sum of squares. C/groups is always even, so a bf16 pair never straddles two groups.
 // DETERMINISTIC on purpose (the commitment re-executes steps bit-for-bit): per-thread pair partials go to shared
 // memory, one thread per group folds them in a fixed order, each CTA writes its partial to its own slot, and
-// gn_finalize_kernel folds the slots sequentially in fp64 — no atomics anywhere.
+// the apply pass folds the slots in a fixed order in fp64 (gn_fold) — no atomics anywhere.
 constexpr int GN_MAX_THREADS = 384, GN_UNROLL = 4;
 
 __device__ __forceinline__ uint4 gn_load(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat16* __restrict__ x2,
@@ -83,16 +83,12 @@ gn_stats_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat1
   }
 }
 
-// fold the per-CTA partials in a fixed order: one warp per (item, group); lane k sums splits k, k+32, ... in order,
-// then a fixed butterfly combines the lanes (same tree every run -> bit-reproducible). stats[item][group] = {mean, rstd}
-__global__ void __launch_bounds__(128)
-gn_finalize_kernel(const float* __restrict__ partial, int splits, int groups, int64_t n_items, double cnt, float eps,
-                   float2* __restrict__ stats) {
-  const int lane = threadIdx.x & 31;
-  const int64_t i = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
-  if (i >= n_items * groups) return;
-  const int64_t item = i / groups;
-  const int g = (int)(i % groups);
+// fold the per-CTA partials of one (item, group) in a fixed order: lane k sums splits k, k+32, ... in order in fp64, then a
+// fixed butterfly combines the lanes (same tree every run and in every CTA -> bit-reproducible). Returns {mean, rstd}.
+// Called by every CTA of the apply pass for its own item (a few hundred floats out of L2): the separate finalize launch
+// it replaces cost 5 us x 166 norms per forward.
+__device__ __forceinline__ float2 gn_fold(const float* __restrict__ partial, int64_t item, int splits, int groups, int g,
+                                          double cnt, float eps, int lane) {
   double a = 0.0, q = 0.0;
   for (int sp = lane; sp < splits; sp += 32) {
     const float2 p = __ldg(reinterpret_cast<const float2*>(partial + (((item * splits + sp) * groups + g) << 1)));
@@ -104,12 +100,10 @@ gn_finalize_kernel(const float* __restrict__ partial, int splits, int groups, in
     a += __shfl_xor_sync(0xffffffffu, a, o);
     q += __shfl_xor_sync(0xffffffffu, q, o);
   }
-  if (lane == 0) {
-    const double m = a / cnt;
-    double var = q / cnt - m * m;
-    if (var < 0.0) var = 0.0;
-    stats[i] = make_float2((float)m, (float)(1.0 / sqrt(var + (double)eps)));
-  }
+  const double m = a / cnt;
+  double var = q / cnt - m * m;
+  if (var < 0.0) var = 0.0;
+  return make_float2((float)m, (float)(1.0 / sqrt(var + (double)eps)));
 }
 
 __device__ __forceinline__ float tanh_approx(float x) {
@@ -129,7 +123,21 @@ __device__ __forceinline__ float silu_fast(float x) {
 __global__ void __launch_bounds__(GN_MAX_THREADS)
 gn_apply_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat16* __restrict__ x2, int C2,
                 const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
-                int64_t rows_per_item, int groups, int rpp, int silu, const float2* __restrict__ stats) {
+                int64_t rows_per_item, int groups, int rpp, int silu, const float* __restrict__ partial, double cnt,
+                float eps) {
+  __shared__ float2 stats[64];  // {mean, rstd} of this CTA's item, per group
+  {
+    // only the FULL warps fold (the block is vecs x rpp threads, > 192, rarely a multiple of 32: the trailing partial
+    // warp must stay out of the full-mask shuffles)
+    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nfull = blockDim.x >> 5;
+    if (warp < nfull) {
+      for (int g = warp; g < groups; g += nfull) {
+        const float2 st = gn_fold(partial, blockIdx.y, gridDim.x, groups, g, cnt, eps, lane);
+        if (lane == 0) stats[g] = st;
+      }
+    }
+  }
+  __syncthreads();
   const int C = C1 + C2;
   const int vecs = C >> 3;
   const int cpg = C / groups;
@@ -144,7 +152,7 @@ gn_apply_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat1
   float sc[8], sh[8];
 #pragma unroll
   for (int j = 0; j < 8; ++j) {
-    const float2 st = __ldg(stats + (int64_t)item * groups + (c + j) / cpg);
+    const float2 st = stats[(c + j) / cpg];
     const float gm = __ldg(gamma + c + j), bt = __ldg(beta + c + j);
     sc[j] = st.y * gm;
     sh[j] = fmaf(-st.x, st.y * gm, bt);
@@ -358,6 +366,7 @@ int group_norm(const void* x1, int C1, const void* x2, int C2, const float* gamm
   const int C = C1 + C2;
   B2V_CHECK(C % 8 == 0 && C1 % 8 == 0 && C % groups == 0 && (C / groups) % 2 == 0, "group_norm: C=%d (C1=%d) groups=%d unsupported", C, C1, groups);
   B2V_CHECK(C <= GN_MAX_THREADS * 8, "group_norm: C=%d too wide (max %d)", C, GN_MAX_THREADS * 8);
+  B2V_CHECK(groups <= 64, "group_norm: at most 64 groups");
   B2V_CHECK(n_items > 0 && n_items < 65536 && rows_per_item > 0, "group_norm: bad item count");
   const int rpp = gn_rpp(C);
   const int threads = (C >> 3) * rpp;
@@ -368,18 +377,13 @@ int group_norm(const void* x1, int C1, const void* x2, int C2, const float* gamm
   const size_t pbytes = sizeof(float) * 2 * (size_t)n_items * splits * groups;
   B2V_CHECK(pbytes + 256 + sizeof(float2) * (size_t)n_items * groups <= group_norm_scratch_bytes(n_items, rows_per_item, groups) + 256,
             "group_norm: scratch too small for %d splits", splits);
-  float2* stats = (float2*)((uint8_t*)scratch + ((pbytes + 255) & ~(size_t)255));
   dim3 grid((unsigned)splits, (unsigned)n_items);
   gn_stats_kernel<<<grid, threads, shb, s>>>((const __nv_bfloat16*)x1, C1, (const __nv_bfloat16*)x2, C2, rows_per_item,
                                             groups, rpp, partial);
   count_launch();
-  const int64_t ng = n_items * groups;
-  gn_finalize_kernel<<<(unsigned)((ng * 32 + 127) / 128), 128, 0, s>>>(partial, splits, groups, n_items,
-                                                                       (double)rows_per_item * (double)(C / groups), eps,
-                                                                       stats);
-  count_launch();
   gn_apply_kernel<<<grid, threads, 0, s>>>((const __nv_bfloat16*)x1, C1, (const __nv_bfloat16*)x2, C2, gamma, beta,
-                                          (__nv_bfloat16*)y, rows_per_item, groups, rpp, silu, stats);
+                                          (__nv_bfloat16*)y, rows_per_item, groups, rpp, silu, partial,
+                                          (double)rows_per_item * (double)(C / groups), eps);
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;
