@@ -15,7 +15,7 @@ sys.modules.setdefault("b2v", _pkg)
 # make ``import b2v.ops`` / ``from b2v.strategies import chunk_only`` resolve to the SAME module objects
 for _sub in ("ops", "scheduler", "unet", "pipeline", "planner", "proof", "strategies", "strategies.common",
              "strategies.chunk_only", "strategies.fsdp_chunked_coherent", "strategies.fsdp_chunked",
-             "strategies.fsdp", "build", "exchange"):
+             "strategies.fsdp", "build", "exchange", "miner"):
     try:
         _m = importlib.import_module(PKG_NAME + "." + _sub)
     except ModuleNotFoundError as _e:  # a submodule that does not exist (yet) is not an error of the alias

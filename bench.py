@@ -359,6 +359,10 @@ def gpu_main(args):
                              "(b2v_unet3d_flops, MAC=2) / CUDA-event time; peak = sustained cuBLAS bf16, " + peaks["source"]}
     roofline = dominant_kernel_roofline(torch, ops, dev, peaks, mine)
     merkle = merkle_bench(torch, ops, proof, dev, peaks, h, w)
+    try:
+        merkle["in_loop"] = in_loop_commit(torch, pipe, emb[:1], dev, h, w)
+    except Exception as ex:  # a report, never a reason to lose the line
+        merkle["in_loop"] = {"error": repr(ex)}
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         try:
@@ -411,6 +415,25 @@ def dominant_kernel_roofline(torch, ops, dev, peaks, mine):
             "frac": ach / peaks["bf16_burst"], "traffic": None, "kernel": "attn_kernel (spatial self-attention L0)",
             "shape": {"batch": nb, "heads": heads, "seq": S, "head_dim": 64}, "ms_per_launch": ms,
             "flops_per_launch": flops, "peak_source": "burst cuBLAS bf16, " + peaks["source"]}
+
+
+def in_loop_commit(torch, pipe, ehs, dev, h, w, steps=3):
+    """Cost of committing INSIDE the miner's recording loop (b2v.miner.record_trajectory: batch 1, no CFG, 24 frames;
+    leaf i hashed on a side stream under the UNet of step i+1): the same loop timed with and without the commitment."""
+    from b2v import miner
+    z0 = torch.randn(1, 4, FRAMES, h, w, device=dev, generator=torch.Generator(device=dev).manual_seed(3)).half()
+    ehs = ehs.to(torch.float16)
+    out = {}
+    for commit in (False, True):
+        miner.record_trajectory(pipe, z0, ehs, steps, commit=commit)  # warm-up (graph capture for this shape)
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        miner.record_trajectory(pipe, z0, ehs, steps, commit=commit)
+        torch.cuda.synchronize()
+        out["ms_per_step_commit" if commit else "ms_per_step_plain"] = (time.perf_counter() - t0) * 1e3 / steps
+    out["overhead_frac"] = out["ms_per_step_commit"] / out["ms_per_step_plain"] - 1.0
+    out["note"] = "miner path B=1 x %d frames, %d steps; one 3.5 MB leaf per step hashed concurrently" % (FRAMES, steps)
+    return out
 
 
 def merkle_bench(torch, ops, proof, dev, peaks, h, w):

@@ -1,0 +1,82 @@
+"""The miner's recording loop and commitment (InferNet/neurons/miner.py:571-589 + 180-264), on libb2v.
+
+Reference loop, batch 1, NO classifier-free guidance, fp16 latents::
+
+    for t in scheduler.timesteps:
+        latents.append(z); timesteps.append(t.item())
+        eps = pipe.unet(z, t, encoder_hidden_states=ehs).sample
+        noise_preds.append(eps)
+        z = scheduler.step(eps, t, z).prev_sample
+    root, leaf_data = self._build_merkle_tree(latents, noise_preds, timesteps)   # after the loop, on the CPU
+
+Here every step is one UNet forward (CUDA-graph replay) plus ONE fused kernel (``b2v_cfg_ddim_step`` with guidance off)
+that performs the DDIM update and writes the step's two leaf images (z_t and eps_t as little-endian fp16, the exact bytes
+the reference hashes) into a preallocated trajectory buffer. The SHA-256 leaf of step i is hashed ON THE DEVICE on a
+side stream while the UNet of step i+1 runs on the main stream (a leaf is one serial 3.5 MB Merkle-Damgard chain,
+~50 ms at ZeroscopeXL: far below a UNet step, so the commitment costs nothing on the critical path); the tree is
+built from the 32-byte digests at the end. Nothing is copied to the host unless the caller asks for the reference's
+``leaf_data`` byte images.
+"""
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+from . import ops, proof
+
+
+class Trajectory:
+    """What the recording loop leaves behind: device-resident fp16 leaf images and the per-leaf digests."""
+
+    def __init__(self, latents, noise_preds, timesteps, alphas, final, digests):
+        self.latents: List[torch.Tensor] = latents          # z_t before the step, fp16 [1,C,F,h,w]
+        self.noise_preds: List[torch.Tensor] = noise_preds  # eps_t, fp16
+        self.timesteps: List[int] = timesteps
+        self.alphas: List[float] = alphas                   # alphas_cumprod[t] as Python floats (miner.py:536-543)
+        self.final: torch.Tensor = final                    # z after the last step (goes to the VAE)
+        self.digests: Optional[torch.Tensor] = digests      # uint8 [n,32] on the device, or None (commit=False)
+
+    def merkle(self, with_bytes=True) -> Tuple[bytes, Dict[int, Tuple[bytes, bytes, List[bytes]]]]:
+        """(root, {t: (z_bytes, eps_bytes, [sibling, ...])}) exactly like ``Miner._build_merkle_tree``."""
+        if self.digests is None:
+            return proof.build_merkle_tree(self.latents, self.noise_preds, self.timesteps, with_bytes=with_bytes)
+        n = len(self.timesteps)
+        fetch = proof.leaf_bytes_to_host(self.latents + self.noise_preds) if with_bytes else None
+        root, paths = ops.merkle_build(self.digests)
+        plist = proof._paths_as_lists(paths, n)
+        blobs = fetch() if fetch is not None else [b""] * (2 * n)
+        leaf_data = {int(t): (blobs[i], blobs[n + i], plist[i]) for i, t in enumerate(self.timesteps)}
+        return root.cpu().numpy().tobytes(), leaf_data
+
+
+def record_trajectory(pipe, z0, encoder_hidden_states, num_steps, commit=True) -> Trajectory:
+    """miner.py:571-589. ``z0`` [1,C,F,h,w] (the reference draws fp16 noise on the device; parity tests pass it in),
+    ``encoder_hidden_states`` [1,77,D]. Returns a :class:`Trajectory`."""
+    if z0.dim() != 5 or z0.shape[0] != 1:
+        raise ValueError("the miner path is batch 1: z0 must be [1,C,F,h,w]")
+    sched, unet = pipe.scheduler, pipe.unet
+    sched.set_timesteps(num_steps)
+    ts = [int(t) for t in sched.host_timesteps()]
+    alphas = [float(sched.alphas_cumprod[t]) for t in ts]
+    dev = z0.device
+    n = len(ts)
+    # trajectory buffers: the leaf images of all steps, allocated once (XL, 50 steps: 2 x 88 MB)
+    zbuf = torch.empty((n,) + tuple(z0.shape), dtype=torch.float16, device=dev)
+    ebuf = torch.empty((n,) + tuple(z0.shape), dtype=torch.float16, device=dev)
+    digests = torch.empty((n, 32), dtype=torch.uint8, device=dev) if commit else None
+    main = torch.cuda.current_stream(dev)
+    side = torch.cuda.Stream(device=dev) if commit else None
+    lat = z0.contiguous()
+    x = ops.make_unet_input(lat, 1)
+    eps = torch.empty_like(x)
+    emb = encoder_hidden_states.contiguous()
+    for i, t in enumerate(ts):
+        unet.forward_into(x, t, emb, eps)
+        lat, x = sched.fused_cfg_step(lat, eps, t, None, n_dup=1, leaf_z=zbuf[i], leaf_eps=ebuf[i], xnext=x)
+        if commit:
+            # leaf i is complete once the step kernel has run: hash it under the next UNet forward
+            side.wait_stream(main)
+            with torch.cuda.stream(side):
+                digests[i:i + 1].copy_(ops.sha256_leaves([zbuf[i]], [ebuf[i]], prefixes=[t]))
+    if commit:
+        main.wait_stream(side)
+    return Trajectory([zbuf[i] for i in range(n)], [ebuf[i] for i in range(n)], ts, alphas, lat, digests)

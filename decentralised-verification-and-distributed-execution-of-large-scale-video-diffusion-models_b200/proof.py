@@ -148,20 +148,78 @@ def commit_trajectory_device(latents, noise_preds, timesteps, mode=0):
     return root, digests, paths
 
 
+_PINNED = {}
+
+
+def _pinned(nbytes):
+    """Page-locked staging buffer, grown on demand and reused (pinning 177 MB costs more than copying it)."""
+    buf = _PINNED.get("buf")
+    if buf is None or buf.numel() < nbytes:
+        buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, pin_memory=True)
+        _PINNED["buf"] = buf
+    return buf
+
+
+def leaf_bytes_to_host(tensors, stream=None):
+    """Byte images of CUDA tensors as Python ``bytes`` (what ``z.cpu().numpy().tobytes()`` returns in miner.py:209-214)
+    through ONE pinned staging buffer: adjacent tensors (views of one trajectory buffer) travel as a single DMA, all
+    copies are asynchronous on `stream`, and the host slices them apart afterwards. Returns a closure that waits for
+    the copies and yields the list — so the caller can hash on the device while the bytes are in flight."""
+    if not tensors:
+        return lambda: []
+    dev = tensors[0].device
+    flat = [t.contiguous().view(-1).view(torch.uint8) for t in tensors]
+    sizes = [f.numel() for f in flat]
+    host = _pinned(sum(sizes))
+    stream = stream or torch.cuda.Stream(device=dev)
+    stream.wait_stream(torch.cuda.current_stream(dev))
+    with torch.cuda.stream(stream):
+        i, off = 0, 0
+        while i < len(flat):  # coalesce runs that are contiguous in device memory
+            j, run = i + 1, sizes[i]
+            while j < len(flat) and flat[j].data_ptr() == flat[i].data_ptr() + run:
+                run += sizes[j]
+                j += 1
+            if j == i + 1:
+                src = flat[i]
+            else:
+                src = torch.empty(0, dtype=torch.uint8, device=dev).set_(flat[i].untyped_storage(),
+                                                                        flat[i].storage_offset(), (run,), (1,))
+            host[off:off + run].copy_(src, non_blocking=True)
+            off += run
+            i = j
+    done = torch.cuda.Event()
+    done.record(stream)
+
+    keep = [flat, tensors]  # the sources stay referenced until the DMA has finished
+
+    def finish():
+        done.synchronize()
+        keep.clear()
+        mv = memoryview(host.numpy())
+        out, off = [], 0
+        for n in sizes:
+            out.append(bytes(mv[off:off + n]))
+            off += n
+        return out
+    return finish
+
+
 def build_merkle_tree(latents, noise_preds, timesteps, with_bytes=True):
     """Drop-in for ``Miner._build_merkle_tree``: returns (root bytes, {t: (z_bytes, eps_bytes, [sibling, ...])}).
     The hashing happens on the device in place; the byte images are copied to the host only because the reference's
-    return value contains them (with_bytes=False leaves them empty)."""
+    return value contains them (with_bytes=False leaves them empty) — as one pinned DMA on a side stream UNDER the
+    hashing."""
+    fetch = None
+    if with_bytes:
+        fetch = leaf_bytes_to_host([z.contiguous() for z in latents] + [e.contiguous() for e in noise_preds])
     root, _, paths = commit_trajectory_device(latents, noise_preds, timesteps)
     plist = _paths_as_lists(paths, len(timesteps))
+    n = len(timesteps)
+    blobs = fetch() if fetch is not None else [b""] * (2 * n)
     leaf_data = {}
     for i, t in enumerate(timesteps):
-        if with_bytes:
-            zb = latents[i].cpu().numpy().tobytes()
-            eb = noise_preds[i].cpu().numpy().tobytes()
-        else:
-            zb = eb = b""
-        leaf_data[int(t)] = (zb, eb, plist[i])
+        leaf_data[int(t)] = (blobs[i], blobs[n + i], plist[i])
     return root.cpu().numpy().tobytes(), leaf_data
 
 

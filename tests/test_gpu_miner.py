@@ -1,0 +1,70 @@
+"""-m gpu: the miner's recording loop + in-loop commitment (InferNet/neurons/miner.py:571-589, 180-264) on libb2v against
+the oracle's restatement (oracle/strategy_ref.denoise_miner, oracle/merkle_ref): per-step latents within the stated
+bf16-compute tolerance, Merkle root / sibling paths bit-exact for the device's own leaf bytes."""
+import hashlib
+
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+STEP_REL_L2 = 5e-2  # per-step latent rel-l2 (bf16 tensor-core compute vs the fp32 CPU oracle), as in test_gpu_strategy
+
+
+def _setup(cuda, frames=4, hw=16, steps=3, io_dtype=torch.float16):
+    from b2v.pipeline import VideoPipeline
+    from oracle import unet3d_ref as R
+    from oracle.ddim_ref import pipeline_scheduler
+    ref = R.random_init_(R.UNet3DConditionModel(R.TINY), seed=1234, round_bf16=True).eval()
+    pipe = VideoPipeline.from_state_dict(ref.state_dict(), config=R.TINY.to_dict(), device=cuda, dtype=io_dtype)
+    g = torch.Generator().manual_seed(7)
+    ehs = torch.randn(1, 77, R.TINY.cross_attention_dim, generator=g)
+    z0 = torch.randn(1, 4, frames, hw, hw, generator=g).to(io_dtype)
+    sr = pipeline_scheduler()
+    sr.set_timesteps(steps)
+    return ref, pipe, sr, ehs, z0
+
+
+def test_record_trajectory_matches_oracle_and_commits(cuda):
+    from b2v import miner, proof
+    from oracle import merkle_ref as M
+    from oracle import strategy_ref as S
+    steps = 3
+    ref, pipe, sr, ehs, z0 = _setup(cuda, steps=steps)
+    z_ref, lat_ref, eps_ref, ts_ref = S.denoise_miner(ref, sr, z0.float(), ehs)
+    traj = miner.record_trajectory(pipe, z0.to(cuda), ehs.to(cuda, z0.dtype), steps)
+    torch.cuda.synchronize()
+    assert traj.timesteps == ts_ref
+    assert len(traj.alphas) == steps and all(0.0 < a < 1.0 for a in traj.alphas)
+    assert torch.equal(traj.latents[0].cpu(), z0)  # leaf 0 holds the initial noise bytes untouched
+    for i in range(steps):
+        for got, want in ((traj.latents[i], lat_ref[i]), (traj.noise_preds[i], eps_ref[i])):
+            assert got.dtype == torch.float16
+            rel = float((got.float().cpu() - want).norm() / want.norm())
+            assert rel < STEP_REL_L2, "step %d: rel-l2 %g" % (i, rel)
+    rel = float((traj.final.float().cpu() - z_ref).norm() / z_ref.norm())
+    assert rel < STEP_REL_L2
+    # commitment: bit-exact against hashlib / the oracle tree over the DEVICE's own leaf bytes
+    root, leaf = traj.merkle()
+    zb = [t.cpu().numpy().tobytes() for t in traj.latents]
+    eb = [t.cpu().numpy().tobytes() for t in traj.noise_preds]
+    want_hashes = [hashlib.sha256(int(t).to_bytes(2, "big") + z + e).digest() for t, z, e in zip(traj.timesteps, zb, eb)]
+    assert [bytes(r) for r in traj.digests.cpu().numpy()] == want_hashes  # hashed in the loop, on the side stream
+    o_root, o_leaf = M.commit_trajectory([t.cpu() for t in traj.latents], [t.cpu() for t in traj.noise_preds], traj.timesteps)
+    assert root == o_root
+    for t in traj.timesteps:
+        assert leaf[t][0] == o_leaf[t][0] and leaf[t][1] == o_leaf[t][1] and leaf[t][2] == o_leaf[t][2]
+    assert all(proof.verify_merkle_leaf(h, leaf[t][2], root) for h, t in zip(want_hashes, traj.timesteps))
+    # the drop-in call over the same tensors gives the same commitment
+    root2, _ = proof.build_merkle_tree(traj.latents, traj.noise_preds, traj.timesteps, with_bytes=False)
+    assert root2 == root
+
+
+def test_record_trajectory_without_commit(cuda):
+    from b2v import miner
+    ref, pipe, sr, ehs, z0 = _setup(cuda, steps=2, io_dtype=torch.bfloat16)
+    a = miner.record_trajectory(pipe, z0.to(cuda), ehs.to(cuda, z0.dtype), 2, commit=False)
+    b = miner.record_trajectory(pipe, z0.to(cuda), ehs.to(cuda, z0.dtype), 2, commit=True)
+    torch.cuda.synchronize()
+    assert a.digests is None and torch.equal(a.final, b.final)  # the side-stream commitment never perturbs the trajectory
+    assert a.merkle(with_bytes=False)[0] == b.merkle(with_bytes=False)[0]
