@@ -411,8 +411,13 @@ def dominant_kernel_roofline(torch, ops, dev, peaks, mine):
     ms = _time_cuda(torch, lambda: ops.attention(q, k, v, heads))
     flops = 4.0 * nb * heads * S * S * 64
     ach = flops / (ms / 1e3) / 1e12
+    # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this shape from the committed `ncu --set full` capture
+    # (profiles/r01j_ncu_full_summary.md: 566.4 MB read + 172.1 MB written; algorithmic q+k+v+out = 755 MB)
+    traffic = 738.4e6 if (nb, heads, S) == (32, 5, 9216) else None
     return {"bound": "tensor", "achieved": ach, "peak": peaks["bf16_burst"], "unit": "TFLOP/s",
-            "frac": ach / peaks["bf16_burst"], "traffic": None, "kernel": "attn_kernel (spatial self-attention L0)",
+            "frac": ach / peaks["bf16_burst"], "traffic": traffic,
+            "traffic_source": "ncu --set full, profiles/r01j_ncu_full_summary.md (bytes per launch)",
+            "kernel": "attn_kernel (spatial self-attention L0)",
             "shape": {"batch": nb, "heads": heads, "seq": S, "head_dim": 64}, "ms_per_launch": ms,
             "flops_per_launch": flops, "peak_source": "burst cuBLAS bf16, " + peaks["source"]}
 
