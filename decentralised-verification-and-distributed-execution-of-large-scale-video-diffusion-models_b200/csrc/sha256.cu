@@ -218,6 +218,65 @@ __global__ void __launch_bounds__(64) sha256_chain_kernel(const LeafDesc* __rest
 }
 
 // ---------------------------------------------------------------------------------------------
+// warp kernel: ONE warp per leaf, NO shared memory — the in-loop commitment (b2v.miner.record_trajectory) hashes one
+// leaf on a side stream while the UNet runs. The UNet's GEMM kernels are persistent, one CTA per SM, and take the whole
+// shared memory of the SM: a hashing CTA that owns even 17 KB of it (the chain kernel) evicts one GEMM CTA from its SM
+// for the whole ~50 ms of the chain and stretches every GEMM of that window (measured +27 % per denoise step). This
+// kernel needs 32 threads x ~110 registers and nothing else, so it sits BESIDE the resident GEMM / attention CTAs.
+// Lane l expands the message schedule (W+K, 64 registers) of block 32*batch + l; the 64 dependent rounds of each block
+// then run on all lanes redundantly with the schedule words broadcast by SHFL from the owning lane. The raw words of the
+// next batch are loaded before the round loop so the global-memory latency hides under ~50 k cycles of rounds.
+// ---------------------------------------------------------------------------------------------
+__global__ void __launch_bounds__(32) sha256_warp_kernel(const LeafDesc* __restrict__ descs,
+                                                         uint8_t* __restrict__ digests) {
+  const Msg m = make_msg(descs[blockIdx.x]);
+  const int lane = threadIdx.x;
+  const uint64_t nbatches = (m.nblocks + 31) >> 5;
+  uint32_t st[8];
+  sha_init(st);
+  uint32_t wn[16];
+  {
+    const uint64_t blk = (uint64_t)lane;
+#pragma unroll
+    for (int j = 0; j < 16; ++j) wn[j] = blk < m.nblocks ? msg_word(m, blk * 16 + j) : 0u;
+  }
+  for (uint64_t bt = 0; bt < nbatches; ++bt) {
+    uint32_t kw[64];
+#pragma unroll
+    for (int t = 0; t < 64; ++t) {
+      if (t >= 16) {
+        const int i = t & 15;
+        wn[i] = wn[i] + s0(wn[(i + 1) & 15]) + wn[(i + 9) & 15] + s1(wn[(i + 14) & 15]);
+      }
+      kw[t] = wn[t & 15] + K256[t];
+    }
+    if (bt + 1 < nbatches) {
+      const uint64_t blk = (bt + 1) * 32 + lane;
+#pragma unroll
+      for (int j = 0; j < 16; ++j) wn[j] = blk < m.nblocks ? msg_word(m, blk * 16 + j) : 0u;
+    }
+    const uint64_t left = m.nblocks - bt * 32;
+    const int cnt = left < 32 ? (int)left : 32;
+    for (int src = 0; src < cnt; ++src) {
+      uint32_t a = st[0], b = st[1], c = st[2], d = st[3], e = st[4], f = st[5], g = st[6], h = st[7];
+#pragma unroll
+      for (int t = 0; t < 64; t += 8) {
+        SHA_ROUND(a, b, c, d, e, f, g, h, __shfl_sync(0xffffffffu, kw[t + 0], src));
+        SHA_ROUND(h, a, b, c, d, e, f, g, __shfl_sync(0xffffffffu, kw[t + 1], src));
+        SHA_ROUND(g, h, a, b, c, d, e, f, __shfl_sync(0xffffffffu, kw[t + 2], src));
+        SHA_ROUND(f, g, h, a, b, c, d, e, __shfl_sync(0xffffffffu, kw[t + 3], src));
+        SHA_ROUND(e, f, g, h, a, b, c, d, __shfl_sync(0xffffffffu, kw[t + 4], src));
+        SHA_ROUND(d, e, f, g, h, a, b, c, __shfl_sync(0xffffffffu, kw[t + 5], src));
+        SHA_ROUND(c, d, e, f, g, h, a, b, __shfl_sync(0xffffffffu, kw[t + 6], src));
+        SHA_ROUND(b, c, d, e, f, g, h, a, __shfl_sync(0xffffffffu, kw[t + 7], src));
+      }
+      st[0] += a; st[1] += b; st[2] += c; st[3] += d; st[4] += e; st[5] += f; st[6] += g; st[7] += h;
+    }
+  }
+  if (lane == 0) store_digest(digests + (size_t)blockIdx.x * 32, st);
+}
+
+// ---------------------------------------------------------------------------------------------
 // lane kernel: one lane per leaf
 // ---------------------------------------------------------------------------------------------
 __global__ void __launch_bounds__(128) sha256_lane_kernel(const LeafDesc* __restrict__ descs, int n,
@@ -363,6 +422,8 @@ extern "C" int b2v_sha256_leaves(const uint16_t* prefix_be16_host, const void* c
   if (mode == 0) mode = (n > 4 * sm_count() * 4) ? 2 : 1;
   if (mode == 1) {
     sha256_chain_kernel<<<n, 64, 0, s>>>(d_dev, digests_dev);
+  } else if (mode == 3) {
+    sha256_warp_kernel<<<n, 32, 0, s>>>(d_dev, digests_dev);
   } else {
     sha256_lane_kernel<<<(n + 127) / 128, 128, 0, s>>>(d_dev, n, digests_dev);
   }

@@ -13,7 +13,8 @@ Here every step is one UNet forward (CUDA-graph replay) plus ONE fused kernel (`
 that performs the DDIM update and writes the step's two leaf images (z_t and eps_t as little-endian fp16, the exact bytes
 the reference hashes) into a preallocated trajectory buffer. The SHA-256 leaf of step i is hashed ON THE DEVICE on a
 side stream while the UNet of step i+1 runs on the main stream (a leaf is one serial 3.5 MB Merkle-Damgard chain,
-~50 ms at ZeroscopeXL: far below a UNet step, so the commitment costs nothing on the critical path); the tree is
+~50 ms at ZeroscopeXL, below a UNet step; it runs as ONE warp without shared memory — ``b2v_sha256_leaves`` mode 3 — so
+it sits beside the UNet's resident one-CTA-per-SM kernels instead of taking an SM away from them); the tree is
 built from the 32-byte digests at the end. Nothing is copied to the host unless the caller asks for the reference's
 ``leaf_data`` byte images.
 """
@@ -76,7 +77,7 @@ def record_trajectory(pipe, z0, encoder_hidden_states, num_steps, commit=True) -
             # leaf i is complete once the step kernel has run: hash it under the next UNet forward
             side.wait_stream(main)
             with torch.cuda.stream(side):
-                digests[i:i + 1].copy_(ops.sha256_leaves([zbuf[i]], [ebuf[i]], prefixes=[t]))
+                digests[i:i + 1].copy_(ops.sha256_leaves([zbuf[i]], [ebuf[i]], prefixes=[t], mode=3))
     if commit:
         main.wait_stream(side)
     return Trajectory([zbuf[i] for i in range(n)], [ebuf[i] for i in range(n)], ts, alphas, lat, digests)

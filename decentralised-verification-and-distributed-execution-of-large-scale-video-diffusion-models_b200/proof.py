@@ -177,7 +177,9 @@ def leaf_bytes_to_host(tensors, stream=None):
         i, off = 0, 0
         while i < len(flat):  # coalesce runs that are contiguous in device memory
             j, run = i + 1, sizes[i]
-            while j < len(flat) and flat[j].data_ptr() == flat[i].data_ptr() + run:
+            base = flat[i].untyped_storage()
+            while (j < len(flat) and flat[j].data_ptr() == flat[i].data_ptr() + run
+                   and flat[j].untyped_storage().data_ptr() == base.data_ptr()):  # same allocation only
                 run += sizes[j]
                 j += 1
             if j == i + 1:

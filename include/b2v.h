@@ -58,7 +58,8 @@ uint64_t b2v_launch_count(void);
  * timestep (miner.py:207 `t.to_bytes(2,'big') + z_bytes + eps_bytes`) when prefix_be16_host != NULL, or
  * empty (proof.py:256 `hashlib.sha256(leaf)` on a raw leaf). A_i / B_i are device buffers (B may be
  * NULL / 0 bytes). One independent Merkle–Damgård chain per leaf; mode 0 = auto, 1 = one CTA per chain
- * (few long leaves), 2 = one lane per chain (thousands of leaves).
+ * (few long leaves), 2 = one lane per chain (thousands of leaves), 3 = one warp per chain without shared memory
+ * (a leaf hashed on a side stream BESIDE the UNet's resident one-CTA-per-SM kernels: the in-loop commitment).
  * a_ptrs_host/b_ptrs_host: host arrays of n device pointers; lens in bytes; digests_dev: [n][32]. */
 int b2v_sha256_leaves(const uint16_t* prefix_be16_host, const void* const* a_ptrs_host,
                       const uint64_t* a_lens_host, const void* const* b_ptrs_host,

@@ -28,7 +28,7 @@ def _tree(leaf_hashes):
     return tree[-1][0], paths
 
 
-@pytest.mark.parametrize("mode", [1, 2])
+@pytest.mark.parametrize("mode", [1, 2, 3])
 @pytest.mark.parametrize("lens", [[0], [1], [55], [56], [63], [64], [65], [119], [120], [128], [1000, 3, 64, 0, 4096],
                                   [2048] * 7, [100003]])
 def test_sha256_raw(cuda, mode, lens):
@@ -41,7 +41,7 @@ def test_sha256_raw(cuda, mode, lens):
         assert dig[i].tobytes() == hashlib.sha256(b.numpy().tobytes()).digest(), (mode, lens[i])
 
 
-@pytest.mark.parametrize("mode", [0, 1, 2])
+@pytest.mark.parametrize("mode", [0, 1, 2, 3])
 @pytest.mark.parametrize("shape", [(1, 4, 2, 8, 8), (1, 4, 5, 32, 32), (1, 4, 3, 5, 7)])
 def test_sha256_leaf_prefix_z_eps(cuda, mode, shape):
     """leaf = t.to_bytes(2,'big') + z_bytes + eps_bytes (miner.py:207), z/eps hashed in place on the device."""
