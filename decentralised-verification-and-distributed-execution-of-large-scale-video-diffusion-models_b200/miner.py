@@ -11,12 +11,17 @@ Reference loop, batch 1, NO classifier-free guidance, fp16 latents::
 
 Here every step is one UNet forward (CUDA-graph replay) plus ONE fused kernel (``b2v_cfg_ddim_step`` with guidance off)
 that performs the DDIM update and writes the step's two leaf images (z_t and eps_t as little-endian fp16, the exact bytes
-the reference hashes) into a preallocated trajectory buffer. The SHA-256 leaf of step i is hashed ON THE DEVICE on a
-side stream while the UNet of step i+1 runs on the main stream (a leaf is one serial 3.5 MB Merkle-Damgard chain,
-~50 ms at ZeroscopeXL, below a UNet step; it runs as ONE warp without shared memory — ``b2v_sha256_leaves`` mode 3 — so
-it sits beside the UNet's resident one-CTA-per-SM kernels instead of taking an SM away from them); the tree is
-built from the 32-byte digests at the end. Nothing is copied to the host unless the caller asks for the reference's
-``leaf_data`` byte images.
+the reference hashes) into a preallocated trajectory buffer. Nothing is copied to the host unless the caller asks for
+the reference's ``leaf_data`` byte images.
+
+When to hash (``commit=``): a leaf is ONE serial 3.5 MB Merkle-Damgard chain (~55 ms at ZeroscopeXL) and chains only
+parallelise ACROSS leaves, so
+* ``"end"`` (default): all n leaves are hashed together after the loop, one CTA per leaf on n SMs — ~55 ms for the whole
+  50-step trajectory, ~1 % of the denoise time;
+* ``"loop"``: leaf i is hashed on a side stream under the UNet of step i+1 by one shared-memory-free warp
+  (``b2v_sha256_leaves`` mode 3, so it fits beside the UNet's resident one-CTA-per-SM kernels). The digest is ready one
+  step after its leaf, but the warp shares an SM with one CTA of every persistent GEMM and that CTA paces the kernel:
+  measured +15 % per step (bench.py ``merkle.in_loop``). Use it only when the commitment must stream out during the run.
 """
 from typing import Dict, List, Optional, Tuple
 
@@ -49,11 +54,15 @@ class Trajectory:
         return root.cpu().numpy().tobytes(), leaf_data
 
 
-def record_trajectory(pipe, z0, encoder_hidden_states, num_steps, commit=True) -> Trajectory:
+def record_trajectory(pipe, z0, encoder_hidden_states, num_steps, commit="end") -> Trajectory:
     """miner.py:571-589. ``z0`` [1,C,F,h,w] (the reference draws fp16 noise on the device; parity tests pass it in),
-    ``encoder_hidden_states`` [1,77,D]. Returns a :class:`Trajectory`."""
+    ``encoder_hidden_states`` [1,77,D]; ``commit``: "end" | "loop" | False (True = "end"). Returns a :class:`Trajectory`."""
     if z0.dim() != 5 or z0.shape[0] != 1:
         raise ValueError("the miner path is batch 1: z0 must be [1,C,F,h,w]")
+    if commit is True:
+        commit = "end"
+    if commit not in ("end", "loop", False, None):
+        raise ValueError("commit must be 'end', 'loop' or False")
     sched, unet = pipe.scheduler, pipe.unet
     sched.set_timesteps(num_steps)
     ts = [int(t) for t in sched.host_timesteps()]
@@ -63,9 +72,10 @@ def record_trajectory(pipe, z0, encoder_hidden_states, num_steps, commit=True) -
     # trajectory buffers: the leaf images of all steps, allocated once (XL, 50 steps: 2 x 88 MB)
     zbuf = torch.empty((n,) + tuple(z0.shape), dtype=torch.float16, device=dev)
     ebuf = torch.empty((n,) + tuple(z0.shape), dtype=torch.float16, device=dev)
-    digests = torch.empty((n, 32), dtype=torch.uint8, device=dev) if commit else None
+    in_loop = commit == "loop"
+    digests = torch.empty((n, 32), dtype=torch.uint8, device=dev) if in_loop else None
     main = torch.cuda.current_stream(dev)
-    side = torch.cuda.Stream(device=dev) if commit else None
+    side = torch.cuda.Stream(device=dev) if in_loop else None
     lat = z0.contiguous()
     x = ops.make_unet_input(lat, 1)
     eps = torch.empty_like(x)
@@ -73,11 +83,14 @@ def record_trajectory(pipe, z0, encoder_hidden_states, num_steps, commit=True) -
     for i, t in enumerate(ts):
         unet.forward_into(x, t, emb, eps)
         lat, x = sched.fused_cfg_step(lat, eps, t, None, n_dup=1, leaf_z=zbuf[i], leaf_eps=ebuf[i], xnext=x)
-        if commit:
+        if in_loop:
             # leaf i is complete once the step kernel has run: hash it under the next UNet forward
             side.wait_stream(main)
             with torch.cuda.stream(side):
                 digests[i:i + 1].copy_(ops.sha256_leaves([zbuf[i]], [ebuf[i]], prefixes=[t], mode=3))
-    if commit:
+    zs, es = [zbuf[i] for i in range(n)], [ebuf[i] for i in range(n)]
+    if in_loop:
         main.wait_stream(side)
-    return Trajectory([zbuf[i] for i in range(n)], [ebuf[i] for i in range(n)], ts, alphas, lat, digests)
+    elif commit == "end":
+        digests = ops.sha256_leaves(zs, es, prefixes=ts)  # n chains side by side, one CTA each
+    return Trajectory(zs, es, ts, alphas, lat, digests)

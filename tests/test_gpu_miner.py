@@ -25,14 +25,15 @@ def _setup(cuda, frames=4, hw=16, steps=3, io_dtype=torch.float16):
     return ref, pipe, sr, ehs, z0
 
 
-def test_record_trajectory_matches_oracle_and_commits(cuda):
+@pytest.mark.parametrize("commit", ["end", "loop"])
+def test_record_trajectory_matches_oracle_and_commits(cuda, commit):
     from b2v import miner, proof
     from oracle import merkle_ref as M
     from oracle import strategy_ref as S
     steps = 3
     ref, pipe, sr, ehs, z0 = _setup(cuda, steps=steps)
     z_ref, lat_ref, eps_ref, ts_ref = S.denoise_miner(ref, sr, z0.float(), ehs)
-    traj = miner.record_trajectory(pipe, z0.to(cuda), ehs.to(cuda, z0.dtype), steps)
+    traj = miner.record_trajectory(pipe, z0.to(cuda), ehs.to(cuda, z0.dtype), steps, commit=commit)
     torch.cuda.synchronize()
     assert traj.timesteps == ts_ref
     assert len(traj.alphas) == steps and all(0.0 < a < 1.0 for a in traj.alphas)
@@ -49,7 +50,7 @@ def test_record_trajectory_matches_oracle_and_commits(cuda):
     zb = [t.cpu().numpy().tobytes() for t in traj.latents]
     eb = [t.cpu().numpy().tobytes() for t in traj.noise_preds]
     want_hashes = [hashlib.sha256(int(t).to_bytes(2, "big") + z + e).digest() for t, z, e in zip(traj.timesteps, zb, eb)]
-    assert [bytes(r) for r in traj.digests.cpu().numpy()] == want_hashes  # hashed in the loop, on the side stream
+    assert [bytes(r) for r in traj.digests.cpu().numpy()] == want_hashes  # hashed on the device (in the loop on a side stream, or all leaves together at the end)
     o_root, o_leaf = M.commit_trajectory([t.cpu() for t in traj.latents], [t.cpu() for t in traj.noise_preds], traj.timesteps)
     assert root == o_root
     for t in traj.timesteps:
@@ -64,7 +65,7 @@ def test_record_trajectory_without_commit(cuda):
     from b2v import miner
     ref, pipe, sr, ehs, z0 = _setup(cuda, steps=2, io_dtype=torch.bfloat16)
     a = miner.record_trajectory(pipe, z0.to(cuda), ehs.to(cuda, z0.dtype), 2, commit=False)
-    b = miner.record_trajectory(pipe, z0.to(cuda), ehs.to(cuda, z0.dtype), 2, commit=True)
+    b = miner.record_trajectory(pipe, z0.to(cuda), ehs.to(cuda, z0.dtype), 2, commit="loop")
     torch.cuda.synchronize()
     assert a.digests is None and torch.equal(a.final, b.final)  # the side-stream commitment never perturbs the trajectory
     assert a.merkle(with_bytes=False)[0] == b.merkle(with_bytes=False)[0]
