@@ -42,6 +42,10 @@ def plan_for(world):
     """(chunk_size, overlap, note) handed to the coherent planner."""
     if world >= 8:
         return 4, 1, "explicit --chunk_size 4 --overlap 1 (reference defaults loop forever at W=8)"
+    if world == 4:
+        return 8, 2, ("explicit --chunk_size 8 --overlap 2 = one 8-frame window per rank (what chunk_only.py plans at "
+                      "W=4); the coherent script's own default at W=4 is 12 windows of 6 frames, 3 per rank, 3x redundant: "
+                      "timed too and reported under reference_default_plan")
     return 0, 4, "reference defaults (--chunk_size 0 --overlap 4)"
 
 
@@ -309,6 +313,32 @@ def gpu_main(args):
     clocks = sampler.stop() if rank == 0 else None
     value = args.steps / (total_ms / 1e3)
 
+    # ---- W = 4 only: the coherent script's own default plan (3 windows of 6 frames per rank), same timing rules ----
+    ref_default = None
+    if world == 4:
+        dplan = planner.plan(FRAMES, world, 0, 4, variant="coherent")
+        main_state = state[:]
+        del state[:]
+        for s, e in dplan.of_rank(rank):
+            lat = base[:, :, s:e].clone()
+            x = ops.make_unet_input(lat, 2, ctx=ctx, ctx_w=CTX_W)
+            state.append([lat, x, torch.empty_like(x)])
+        for i in range(args.warmup):
+            video_step(i)
+        sync_all()
+        d0, d1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        d0.record()
+        for i in range(args.steps):
+            video_step(args.warmup + i)
+        d1.record()
+        sync_all()
+        dms = torch.tensor([d0.elapsed_time(d1)], device=dev, dtype=torch.float64)
+        dist.all_reduce(dms, op=dist.ReduceOp.MAX)
+        ref_default = {"value": args.steps / (float(dms.item()) / 1e3), "unit": "steps/s", "chunk_size": dplan.chunk_size,
+                       "overlap": dplan.overlap, "windows": dplan.ranges, "windows_per_rank": len(dplan.of_rank(rank))}
+        del state[:]
+        state.extend(main_state)
+
     # ---- e2e: the same step through the public per-step API with HOST buffers (pinned), copies inside the timing ----
     host_lat = [st[0].to("cpu").pin_memory() for st in state]
     host_emb = den.emb.to("cpu").pin_memory()
@@ -376,6 +406,7 @@ def gpu_main(args):
         "config": {"workload": "ZeroscopeXL 1024x576x24f fsdp_chunked_coherent hybrid_ctx, CFG 7.5, DDIM 50-step schedule",
                    "plan": {"note": plan_note, "chunk_size": plan.chunk_size, "overlap": plan.overlap,
                             "windows": plan.ranges, "windows_per_rank": len(mine)},
+                   "reference_default_plan": ref_default,
                    "latent": [1, 4, FRAMES, h, w], "unet_flops_per_step_bottleneck_rank": step_flops,
                    "l2": "no flush: each step streams 2.8 GB of weights + >2 GB of activations (>> 126 MB L2)"},
         "e2e": {"value": e2e_value, "unit": "steps/s", "h2d_bytes_per_step": bi, "d2h_bytes_per_step": bo},
