@@ -107,6 +107,27 @@ __device__ __forceinline__ float gelu_fast(float x) {
   return 0.5f * x * phi2;
 }
 
+// The same function for a PAIR of gates on packed fp32 (FFMA2 / FMUL2: half the issue slots — the GEGLU epilogue issues
+// about as many warp-instructions per tile as the K = 320 mainloop has tensor cycles), written without the sign select:
+//   gelu(x) = relu(x) - 0.5 |x| erfc(|x| / sqrt 2)      (x > 0: x (1 - erfc/2) = x (1 + erf)/2;  x < 0: x erfc/2)
+// Coefficients are those of gelu_fast, negated so the exponent needs no extra sign flip.
+__device__ __forceinline__ uint64_t gelu_fast2(uint64_t x2) {
+  float x0, x1;
+  unpack2(x2, x0, x1);
+  const uint64_t ax2 = pack2(fabsf(x0), fabsf(x1));
+  uint64_t q = fma2(pack2(-5.204590389e-04f, -5.204590389e-04f), ax2, pack2(7.397513200e-03f, 7.397513200e-03f));
+  q = fma2(q, ax2, pack2(-5.256124131e-02f, -5.256124131e-02f));
+  q = fma2(q, ax2, pack2(-4.592546802e-01f, -4.592546802e-01f));
+  q = fma2(q, ax2, pack2(-1.151091355e+00f, -1.151091355e+00f));
+  float e0, e1;
+  unpack2(mul2(q, ax2), e0, e1);
+  float p0, p1;
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(p0) : "f"(e0));  // erfc(|x| / sqrt 2)
+  asm("ex2.approx.ftz.f32 %0, %1;" : "=f"(p1) : "f"(e1));
+  const uint64_t nh2 = mul2(ax2, pack2(-0.5f, -0.5f));
+  return fma2(nh2, pack2(p0, p1), pack2(fmaxf(x0, 0.f), fmaxf(x1, 0.f)));
+}
+
 // Epilogue warp role. One warp handles 32 rows (its TMEM lane quarter) x half of the tile's output columns (group 0 / 1)
 // in 16-column chunks: tcgen05.ld of chunk c+1 is in flight while chunk c is computed. Results are staged in the warp's
 // own shared-memory panel and leave as TMA stores (full 128-byte lines instead of 16-byte scattered stores: the L0
@@ -171,7 +192,8 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
     float bv[2][16];
     float bg[GEGLU ? 2 : 1][16];
     // (GEGLU tiles only: on the plain epilogues, which are bound by their stores, the extra live registers cost 4-7 %)
-    const bool has_b = GEGLU && p.bias != nullptr;
+    // (a GEGLU projection without bias adds zeros: a runtime predicate here costs ~10 register moves per column pair)
+    constexpr bool has_b = GEGLU;
     auto fetch_bias = [&](int ch, int slot) {
       const int c = ch * 16;
       if (p.bias) {
@@ -230,11 +252,9 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
         if (has_b) fetch_bias(ch + 1, nxt);
       }
       float f[16];
+      if constexpr (!GEGLU) {
 #pragma unroll
-      for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[cur][j]);
-      if (has_b) {
-#pragma unroll
-        for (int j = 0; j < 16; ++j) f[j] += bv[cur][j];
+        for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[cur][j]);
       }
       if constexpr (!GEGLU) {
         if (p.bias) {
@@ -255,15 +275,15 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
         }
       }
       if constexpr (GEGLU) {
-        float gt[16];
+        // value * gelu(gate) on column pairs, packed fp32 throughout
 #pragma unroll
-        for (int j = 0; j < 16; ++j) gt[j] = __uint_as_float(g[cur][j]);
-        if (has_b) {
-#pragma unroll
-          for (int j = 0; j < 16; ++j) gt[j] += bg[cur][j];
+        for (int j = 0; j < 8; ++j) {
+          uint64_t val2 = pack2u(v[cur][2 * j], v[cur][2 * j + 1]);
+          uint64_t gate2 = pack2u(g[cur][2 * j], g[cur][2 * j + 1]);
+          val2 = add2(val2, pack2(bv[cur][2 * j], bv[cur][2 * j + 1]));
+          gate2 = add2(gate2, pack2(bg[cur][2 * j], bg[cur][2 * j + 1]));
+          unpack2(mul2(val2, gelu_fast2(gate2)), f[2 * j], f[2 * j + 1]);
         }
-#pragma unroll
-        for (int j = 0; j < 16; ++j) f[j] *= gelu_fast(gt[j]);
       } else {
         if (p.gelu) {
 #pragma unroll
