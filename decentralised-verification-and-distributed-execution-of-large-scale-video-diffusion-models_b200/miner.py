@@ -53,6 +53,47 @@ class Trajectory:
         leaf_data = {int(t): (blobs[i], blobs[n + i], plist[i]) for i, t in enumerate(self.timesteps)}
         return root.cpu().numpy().tobytes(), leaf_data
 
+    def wire(self) -> Dict:
+        """The base64 fields the miner puts on the synapse (miner.py:643-666): ``merkle_root``, ``timesteps``, ``latents``,
+        ``noise_preds``, ``alphas`` and ``leaf_data`` = {t: (z_b64, eps_b64, [sibling_b64, ...])}. The reference encodes
+        every leaf image twice (leaf_data and latents / noise_preds); here each is encoded once, on the device, and the
+        two views share the string."""
+        import base64
+        root, leaf = self.merkle(with_bytes=False)
+        zs, es = leaves_b64(self.latents), leaves_b64(self.noise_preds)
+        leaf_b64 = {int(t): (zs[i], es[i], [base64.b64encode(p).decode("ascii") for p in leaf[int(t)][2]])
+                    for i, t in enumerate(self.timesteps)}
+        return {"merkle_root": base64.b64encode(root).decode("ascii"), "timesteps": list(self.timesteps),
+                "latents": zs, "noise_preds": es, "alphas": list(self.alphas), "leaf_data": leaf_b64}
+
+
+def leaves_b64(tensors) -> List[str]:
+    """``[base64.b64encode(t.cpu().numpy().tobytes()).decode('ascii') for t in tensors]`` (miner.py:655-656) with the
+    encoding done on the device: equally sized tensors that sit back to back in one buffer (the trajectory buffers of
+    ``record_trajectory``) are encoded by ONE kernel launch and leave the device as ASCII through one pinned DMA."""
+    out: List[str] = []
+    i = 0
+    while i < len(tensors):
+        t0 = tensors[i].contiguous()
+        nbytes = t0.numel() * t0.element_size()
+        j = i + 1
+        while (j < len(tensors) and tensors[j].is_contiguous() and tensors[j].dtype == t0.dtype
+               and tensors[j].numel() == t0.numel()
+               and tensors[j].untyped_storage().data_ptr() == t0.untyped_storage().data_ptr()
+               and tensors[j].data_ptr() == t0.data_ptr() + (j - i) * nbytes):
+            j += 1
+        rows = j - i
+        if rows > 1:
+            flat = torch.empty(0, dtype=t0.dtype, device=t0.device).set_(t0.untyped_storage(), t0.storage_offset(),
+                                                                         (rows, t0.numel()), (t0.numel(), 1))
+        else:
+            flat = t0.view(1, -1)
+        enc = ops.base64_rows(flat)
+        blobs = proof.leaf_bytes_to_host([enc[k] for k in range(rows)])()
+        out.extend(b.decode("ascii") for b in blobs)
+        i = j
+    return out
+
 
 def record_trajectory(pipe, z0, encoder_hidden_states, num_steps, commit="end") -> Trajectory:
     """miner.py:571-589. ``z0`` [1,C,F,h,w] (the reference draws fp16 noise on the device; parity tests pass it in),

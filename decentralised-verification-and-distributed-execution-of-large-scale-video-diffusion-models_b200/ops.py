@@ -114,6 +114,21 @@ def blend_overlap(chunks, ranges, weights, T, return_full=False):
     return blend_overlap_ptrs([c.data_ptr() for c in chunks], ranges, weights, T, Cc, h, w, dt, dev, return_full)
 
 
+def base64_rows(buf, n_rows=None):
+    """RFC 4648 base64 of the rows of a contiguous CUDA tensor [n_rows, ...] (any dtype; a row is its raw bytes), encoded
+    on the device. Returns a CUDA uint8 tensor [n_rows, 4*ceil(row_bytes/3)] of ASCII (miner.py:643-657)."""
+    lib = _lib.load()
+    _cuda(buf, "buffer")
+    if not buf.is_contiguous():
+        raise ValueError("base64_rows needs a contiguous tensor")
+    n = buf.shape[0] if n_rows is None else int(n_rows)
+    row_bytes = (buf.numel() // max(buf.shape[0], 1)) * buf.element_size()
+    out_row = int(lib.b2v_base64_len(row_bytes))
+    out = torch.empty((n, out_row), dtype=torch.uint8, device=buf.device)
+    check(lib.b2v_base64_rows(ptr(buf), n, row_bytes, row_bytes, ptr(out), stream()))
+    return out
+
+
 # ---- proof -----------------------------------------------------------------------------------------------------
 def sha256_leaves(a_list, b_list=None, prefixes=None, mode=0):
     """digest[i] = SHA256(prefix_i(2B BE, optional) ‖ bytes(a_i) ‖ bytes(b_i)); tensors are hashed in place on the

@@ -130,6 +130,14 @@ int b2v_blend_overlap(const void* const* chunk_ptrs_host, const int* starts_host
                       int n_chunks, const float* w_host, int C, int T, int64_t hw, int dtype,
                       float* lat_out_f32_dev, void* full_out_dev, void* stream);
 
+/* Wire format of the commitment (InferNet/neurons/miner.py:643-657 and the spot-check reveal 417-423:
+ * `base64.b64encode(z_bytes).decode('ascii')` for every leaf image). Encodes n_rows rows of row_bytes bytes
+ * (row i at src_dev + i*row_stride) into dst_dev, row i at dst_dev + i*b2v_base64_len(row_bytes): RFC 4648
+ * standard alphabet with '=' padding, bit-identical to Python's base64.b64encode. */
+uint64_t b2v_base64_len(uint64_t nbytes);
+int b2v_base64_rows(const void* src_dev, int64_t n_rows, uint64_t row_bytes, uint64_t row_stride,
+                    void* dst_dev, void* stream);
+
 /* ------------------------------------------------------------------------------------------------
  * UNet3DConditionModel forward  ([UPSTREAM diffusers] pipe.unet(x, t, encoder_hidden_states=emb).sample,
  * chunk_only.py:71, fsdp_chunked_coherent.py:140, miner.py:581)

@@ -69,3 +69,23 @@ def test_record_trajectory_without_commit(cuda):
     torch.cuda.synchronize()
     assert a.digests is None and torch.equal(a.final, b.final)  # the side-stream commitment never perturbs the trajectory
     assert a.merkle(with_bytes=False)[0] == b.merkle(with_bytes=False)[0]
+
+
+def test_wire_format_matches_reference_encoding(cuda):
+    """Trajectory.wire() == the base64 fields the reference builds on the host (miner.py:643-666)."""
+    import base64
+    from b2v import miner
+    ref, pipe, sr, ehs, z0 = _setup(cuda, steps=3)
+    traj = miner.record_trajectory(pipe, z0.to(cuda), ehs.to(cuda, z0.dtype), 3)
+    w = traj.wire()
+    root, leaf = traj.merkle()
+    assert w["merkle_root"] == base64.b64encode(root).decode("ascii")
+    assert w["timesteps"] == traj.timesteps and w["alphas"] == traj.alphas
+    assert w["latents"] == [base64.b64encode(z.cpu().numpy().tobytes()).decode("ascii") for z in traj.latents]
+    assert w["noise_preds"] == [base64.b64encode(e.cpu().numpy().tobytes()).decode("ascii") for e in traj.noise_preds]
+    for t, (zb, eb, path) in leaf.items():
+        assert w["leaf_data"][t] == (base64.b64encode(zb).decode("ascii"), base64.b64encode(eb).decode("ascii"),
+                                     [base64.b64encode(p).decode("ascii") for p in path])
+    # separately allocated tensors (not views of one buffer) take the per-tensor path
+    loose = [z.clone() for z in traj.latents]
+    assert miner.leaves_b64(loose) == w["latents"]

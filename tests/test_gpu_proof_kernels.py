@@ -102,3 +102,25 @@ def test_merkle_duplicate_leaves_and_ties(cuda):
     lh = torch.tensor(list(b"".join(leaves)), dtype=torch.uint8).reshape(6, 32).to(cuda)
     root, _ = ops.merkle_build(lh)
     assert root.cpu().numpy().tobytes() == _tree(leaves)[0]
+
+
+@pytest.mark.parametrize("row_bytes", [1, 2, 3, 4, 5, 11, 12, 13, 23, 24, 36, 47, 48, 1000, 4096, 1769472])
+def test_base64_rows_match_stdlib(cuda, row_bytes):
+    """b2v_base64_rows == base64.b64encode (miner.py:643-657) for every padding case, unaligned and vector paths."""
+    import base64
+    from b2v import ops
+    n = 3 if row_bytes > 100000 else 5
+    g = torch.Generator().manual_seed(row_bytes)
+    host = torch.randint(0, 256, (n, row_bytes), dtype=torch.uint8, generator=g)
+    enc = ops.base64_rows(host.to(cuda)).cpu().numpy()
+    for i in range(n):
+        assert enc[i].tobytes() == base64.b64encode(host[i].numpy().tobytes()), (row_bytes, i)
+
+
+def test_base64_rows_fp16_latent(cuda):
+    import base64
+    from b2v import ops
+    z = torch.randn(4, 1, 4, 3, 8, 8, generator=torch.Generator().manual_seed(1)).half()
+    enc = ops.base64_rows(z.to(cuda)).cpu().numpy()
+    for i in range(4):
+        assert enc[i].tobytes() == base64.b64encode(z[i].numpy().tobytes())
