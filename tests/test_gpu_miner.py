@@ -89,3 +89,39 @@ def test_wire_format_matches_reference_encoding(cuda):
     # separately allocated tensors (not views of one buffer) take the per-tensor path
     loose = [z.clone() for z in traj.latents]
     assert miner.leaves_b64(loose) == w["latents"]
+
+
+def test_reexecution_spot_check(cuda):
+    """Validator-side re-execution of revealed leaves: an honest trajectory passes (bit-exact re-execution), a forged
+    eps that was committed honestly passes membership but fails re-execution, a flipped byte fails membership."""
+    from b2v import miner, proof
+    steps = 4
+    ref, pipe, sr, ehs, z0 = _setup(cuda, steps=steps)
+    e_dev = ehs.to(cuda, z0.dtype)
+    traj = miner.record_trajectory(pipe, z0.to(cuda), e_dev, steps)
+    root, leaf = traj.merkle()
+    idx = proof.commit_then_reveal_merkle_spotcheck(root, steps, 2, 7)
+    revealed = {traj.timesteps[i]: leaf[traj.timesteps[i]] for i in idx}
+    shape = tuple(z0.shape)
+    rep = miner.reexecute_spot_check(pipe, e_dev, revealed, root, traj.timesteps, shape, steps)
+    assert rep["ok"], rep
+    assert all(v["eps_exact"] and v["member"] for v in rep["leaves"].values()), rep
+    assert any(v["chain"] is True for v in rep["leaves"].values()), rep  # consecutive pairs were revealed
+    # sharded over two ranks: every leaf is checked exactly once
+    a = miner.reexecute_spot_check(pipe, e_dev, revealed, root, traj.timesteps, shape, steps, rank=0, world=2)
+    b = miner.reexecute_spot_check(pipe, e_dev, revealed, root, traj.timesteps, shape, steps, rank=1, world=2)
+    assert sorted(list(a["leaves"]) + list(b["leaves"])) == sorted(revealed) and a["ok"] and b["ok"]
+    # forged noise prediction, committed honestly: the tree is consistent, the UNet is not fooled
+    forged = [e.clone() for e in traj.noise_preds]
+    forged[idx[0]] = torch.randn_like(forged[idx[0]])
+    root_f, leaf_f = proof.build_merkle_tree(traj.latents, forged, traj.timesteps)
+    rev_f = {traj.timesteps[i]: leaf_f[traj.timesteps[i]] for i in idx}
+    rep_f = miner.reexecute_spot_check(pipe, e_dev, rev_f, root_f, traj.timesteps, shape, steps)
+    bad_t = traj.timesteps[idx[0]]
+    assert not rep_f["ok"] and rep_f["leaves"][bad_t]["member"] and not rep_f["leaves"][bad_t]["reexec"], rep_f
+    # a flipped byte in a revealed leaf breaks membership
+    t0 = traj.timesteps[idx[0]]
+    zb = bytearray(revealed[t0][0]); zb[5] ^= 0x40
+    rev_b = dict(revealed); rev_b[t0] = (bytes(zb), revealed[t0][1], revealed[t0][2])
+    rep_b = miner.reexecute_spot_check(pipe, e_dev, rev_b, root, traj.timesteps, shape, steps)
+    assert not rep_b["ok"] and not rep_b["leaves"][t0]["member"]
