@@ -86,6 +86,7 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
   const uint32_t tS = tmem_base, tO = tmem_base + 128;
+  pdl_wait();
 
   if (warp == 0) {
     if (elect_one()) {
@@ -287,6 +288,7 @@ __global__ void __launch_bounds__(TA_WARPS * 32)
 temporal_attn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int q_off, int k_off, int v_off,
                      __nv_bfloat16* __restrict__ out, int64_t ldo, int B, int F, int64_t HW, int heads,
                      float scale_log2) {
+  pdl_wait();
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int g = lane >> 2, tg = lane & 3;
   const int64_t total = (int64_t)B * HW * heads;
@@ -451,7 +453,7 @@ int attention(const AttnArgs& a, cudaStream_t s) {
   p.nkv = (a.Skv + 127) / 128;
   p.scale_log2 = a.scale * 1.4426950408889634f;
   dim3 grid((unsigned)((a.Sq + 127) / 128), (unsigned)a.heads, (unsigned)a.nb);
-  attn_kernel<<<grid, AT_THREADS, AT_SMEM, s>>>(tmQ, tmK, tmV, p);
+  B2V_CUDA_OK(launch_pdl(attn_kernel, grid, dim3(AT_THREADS), AT_SMEM, s, tmQ, tmK, tmV, p));
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;
@@ -469,13 +471,13 @@ int temporal_attention(const void* qkv, int64_t ld, int q_off, int k_off, int v_
   if (grid > cap) grid = cap;
   B2V_CHECK(ld % 8 == 0 && ((uintptr_t)qkv & 15) == 0 && ((uintptr_t)out & 15) == 0, "temporal_attention: 16-byte alignment");
   if (F <= 16)
-    temporal_attn_kernel<1><<<(unsigned)grid, TA_WARPS * 32, 0, s>>>((const __nv_bfloat16*)qkv, ld, q_off, k_off, v_off,
-                                                                    (__nv_bfloat16*)out, ldo, B, F, HW, heads,
-                                                                    scale * 1.4426950408889634f);
+    B2V_CUDA_OK(launch_pdl(temporal_attn_kernel<1>, dim3((unsigned)grid), dim3(TA_WARPS * 32), 0, s,
+                           (const __nv_bfloat16*)qkv, ld, q_off, k_off, v_off, (__nv_bfloat16*)out, ldo, B, F, HW, heads,
+                           scale * 1.4426950408889634f));
   else
-    temporal_attn_kernel<2><<<(unsigned)grid, TA_WARPS * 32, 0, s>>>((const __nv_bfloat16*)qkv, ld, q_off, k_off, v_off,
-                                                                    (__nv_bfloat16*)out, ldo, B, F, HW, heads,
-                                                                    scale * 1.4426950408889634f);
+    B2V_CUDA_OK(launch_pdl(temporal_attn_kernel<2>, dim3((unsigned)grid), dim3(TA_WARPS * 32), 0, s,
+                           (const __nv_bfloat16*)qkv, ld, q_off, k_off, v_off, (__nv_bfloat16*)out, ldo, B, F, HW, heads,
+                           scale * 1.4426950408889634f));
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;

@@ -41,6 +41,34 @@ static inline cudaError_t launch_check() { return cudaPeekAtLastError(); }
 // count of kernels this library launched (bench.py reports it as gpu_launches)
 void count_launch(int n = 1);
 
+// ---- programmatic dependent launch (PDL) ----
+// The forward is ~1000 back-to-back kernels replayed from a CUDA graph; between two of them the GPU drains, flushes and
+// launches (~5 us: 5 % of a forward). Kernels launched through launch_pdl() may start as soon as the CTAs of the
+// previous kernel have exited and run their prologue (barrier init, TMEM allocation, tensor-map prefetch) there; every
+// such kernel executes pdl_wait() before it touches global memory, which blocks until the previous kernel has fully
+// completed and its writes are visible — so the order of memory effects is exactly that of plain stream order.
+// (griddepcontrol.wait is a no-op for a kernel launched without the attribute.) B2V_PDL=0 disables the attribute.
+bool pdl_enabled();
+#ifdef __CUDACC__
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_pdl(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t s,
+                              Args&&... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = s;
+  cudaLaunchAttribute attr[1];
+  attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+  attr[0].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
+  cfg.attrs = attr;
+  cfg.numAttrs = 1;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+#endif
+
 static inline size_t dtype_size(int dt) {
   switch (dt) {
     case B2V_F32: return 4;

@@ -424,6 +424,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+  pdl_wait();  // everything above overlapped the previous kernel's tail; from here on its results are read / overwritten
 
   if (warp == 0) {
     // ===================== TMA producer (both CTAs of a pair) =====================
@@ -549,7 +550,8 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
   const int units = p.num_m_units * p.num_n_tiles;
   if (CG == 1) {
     const int grid = units < sm_count() ? units : sm_count();
-    gemm_kernel<BN, MODE, EPI, RES, CG><<<grid, NUM_THREADS, Cfg::SMEM_BYTES, s>>>(tmA, tmB, tmO, tmR, p);
+    B2V_CUDA_OK(launch_pdl(gemm_kernel<BN, MODE, EPI, RES, CG>, dim3((unsigned)grid), dim3(NUM_THREADS), Cfg::SMEM_BYTES, s,
+                           tmA, tmB, tmO, tmR, p));
   } else {
     // one CTA pair (cluster of 2 = the two SMs of a TPC) per work unit, persistent over the units
     const int pairs = units < sm_count() / 2 ? units : sm_count() / 2;
@@ -558,11 +560,13 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
     cfg.blockDim = dim3(NUM_THREADS);
     cfg.dynamicSmemBytes = Cfg::SMEM_BYTES;
     cfg.stream = s;
-    cudaLaunchAttribute attr[1];
+    cudaLaunchAttribute attr[2];
     attr[0].id = cudaLaunchAttributeClusterDimension;
     attr[0].val.clusterDim.x = 2; attr[0].val.clusterDim.y = 1; attr[0].val.clusterDim.z = 1;
+    attr[1].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
     cfg.attrs = attr;
-    cfg.numAttrs = 1;
+    cfg.numAttrs = 2;
     B2V_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_kernel<BN, MODE, EPI, RES, CG>, tmA, tmB, tmO, tmR, p));
   }
   count_launch();

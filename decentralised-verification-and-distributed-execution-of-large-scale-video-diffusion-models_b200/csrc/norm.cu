@@ -31,6 +31,7 @@ __global__ void __launch_bounds__(GN_MAX_THREADS)
 gn_stats_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat16* __restrict__ x2, int C2,
                 int64_t rows_per_item, int groups, int rpp, float* __restrict__ partial /*[item][split][group][2]*/) {
   extern __shared__ float sh[];  // [2][rpp][C/2]
+  pdl_wait();
   const int C = C1 + C2;
   const int vecs = C >> 3, pairs = C >> 1;
   const int cpg = C / groups;
@@ -126,6 +127,7 @@ gn_apply_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat1
                 int64_t rows_per_item, int groups, int rpp, int silu, const float* __restrict__ partial, double cnt,
                 float eps) {
   __shared__ float2 stats[64];  // {mean, rstd} of this CTA's item, per group
+  pdl_wait();
   {
     // only the FULL warps fold (the block is vecs x rpp threads, > 192, rarely a multiple of 32: the trailing partial
     // warp must stay out of the full-mask shuffles)
@@ -197,6 +199,7 @@ __global__ void __launch_bounds__(256)
 layer_norm_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
                   __nv_bfloat16* __restrict__ y, int64_t rows, int C, float eps) {
   constexpr int RPW = 32 / LPR;  // rows per warp
+  pdl_wait();
   const int lane = threadIdx.x & 31;
   const int sub = lane / LPR, l = lane % LPR;
   const int64_t warp = ((int64_t)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
@@ -378,12 +381,12 @@ int group_norm(const void* x1, int C1, const void* x2, int C2, const float* gamm
   B2V_CHECK(pbytes + 256 + sizeof(float2) * (size_t)n_items * groups <= group_norm_scratch_bytes(n_items, rows_per_item, groups) + 256,
             "group_norm: scratch too small for %d splits", splits);
   dim3 grid((unsigned)splits, (unsigned)n_items);
-  gn_stats_kernel<<<grid, threads, shb, s>>>((const __nv_bfloat16*)x1, C1, (const __nv_bfloat16*)x2, C2, rows_per_item,
-                                            groups, rpp, partial);
+  B2V_CUDA_OK(launch_pdl(gn_stats_kernel, grid, dim3(threads), shb, s, (const __nv_bfloat16*)x1, C1,
+                         (const __nv_bfloat16*)x2, C2, rows_per_item, groups, rpp, partial));
   count_launch();
-  gn_apply_kernel<<<grid, threads, 0, s>>>((const __nv_bfloat16*)x1, C1, (const __nv_bfloat16*)x2, C2, gamma, beta,
-                                          (__nv_bfloat16*)y, rows_per_item, groups, rpp, silu, partial,
-                                          (double)rows_per_item * (double)(C / groups), eps);
+  B2V_CUDA_OK(launch_pdl(gn_apply_kernel, grid, dim3(threads), 0, s, (const __nv_bfloat16*)x1, C1,
+                         (const __nv_bfloat16*)x2, C2, gamma, beta, (__nv_bfloat16*)y, rows_per_item, groups, rpp, silu,
+                         (const float*)partial, (double)rows_per_item * (double)(C / groups), eps));
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;
@@ -402,7 +405,8 @@ int layer_norm(const void* x, const float* gamma, const float* beta, void* y, in
 #define B2V_LN(L, V)                                                                                                 \
   if (lpr == L && v == V) {                                                                                          \
     const int grid = grid_resident(layer_norm_kernel<L, V>, warps * 32, 256);                                        \
-    layer_norm_kernel<L, V><<<grid, 256, 0, s>>>((const __nv_bfloat16*)x, gamma, beta, (__nv_bfloat16*)y, rows, C, eps); \
+    B2V_CUDA_OK(launch_pdl(layer_norm_kernel<L, V>, dim3(grid), dim3(256), 0, s, (const __nv_bfloat16*)x, gamma, beta,    \
+                           (__nv_bfloat16*)y, rows, C, eps));                                                         \
     launched = true;                                                                                                 \
   }
   bool launched = false;

@@ -1,4 +1,5 @@
 // Library runtime: error state, device check, launch counter, TMA descriptor encoding.
+#include <stdlib.h>
 #include <atomic>
 #include <cstdarg>
 #include <mutex>
@@ -25,6 +26,15 @@ int fail(int code, const char* fmt, ...) {
 }
 
 void count_launch(int n) { g_launches.fetch_add((uint64_t)n, std::memory_order_relaxed); }
+
+bool pdl_enabled() {
+  static int on = -1;
+  if (on < 0) {
+    const char* e = getenv("B2V_PDL");
+    on = (e && e[0] == '0') ? 0 : 1;
+  }
+  return on == 1;
+}
 
 int sm_count() {
   static int cached[64] = {0};
