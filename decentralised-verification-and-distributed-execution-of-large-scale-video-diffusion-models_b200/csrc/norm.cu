@@ -84,27 +84,42 @@ gn_stats_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat1
   }
 }
 
-// fold the per-CTA partials of one (item, group) in a fixed order: lane k sums splits k, k+32, ... in order in fp64, then a
-// fixed butterfly combines the lanes (same tree every run and in every CTA -> bit-reproducible). Returns {mean, rstd}.
-// Called by every CTA of the apply pass for its own item (a few hundred floats out of L2): the separate finalize launch
-// it replaces cost 5 us x 166 norms per forward.
-__device__ __forceinline__ float2 gn_fold(const float* __restrict__ partial, int64_t item, int splits, int groups, int g,
-                                          double cnt, float eps, int lane) {
-  double a = 0.0, q = 0.0;
-  for (int sp = lane; sp < splits; sp += 32) {
-    const float2 p = __ldg(reinterpret_cast<const float2*>(partial + (((item * splits + sp) * groups + g) << 1)));
-    a += (double)p.x;
-    q += (double)p.y;
+// Fold the per-CTA partials [split][group]{sum, sumsq} of one item into {mean, rstd} per group, inside every CTA of the
+// apply pass (a few KB out of L2; the separate finalize launch it replaces cost 5 us x 166 norms per forward).
+// lane = group, warp = a stride over the splits: each warp reads whole 256-byte rows of the partial table (coalesced),
+// adds its splits in increasing order in fp64 and parks the result in shared memory; warp 0 then adds the per-warp
+// results in warp order. The order is fixed by (splits, warps) alone, so every CTA and every run gets the same bits.
+__device__ __forceinline__ void gn_fold_item(const float* __restrict__ partial, int64_t item, int splits, int groups,
+                                             double cnt, float eps, double2* __restrict__ scratch /*[nfull][64]*/,
+                                             float2* __restrict__ stats /*[64]*/) {
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nfull = blockDim.x >> 5;
+  if (warp < nfull) {
+    for (int g = lane; g < groups; g += 32) {
+      double a = 0.0, q = 0.0;
+      for (int sp = warp; sp < splits; sp += nfull) {
+        const float2 p = __ldg(reinterpret_cast<const float2*>(partial + (((item * splits + sp) * groups + g) << 1)));
+        a += (double)p.x;
+        q += (double)p.y;
+      }
+      scratch[warp * 64 + g] = make_double2(a, q);
+    }
   }
-#pragma unroll
-  for (int o = 16; o > 0; o >>= 1) {
-    a += __shfl_xor_sync(0xffffffffu, a, o);
-    q += __shfl_xor_sync(0xffffffffu, q, o);
+  __syncthreads();
+  if (warp == 0) {
+    for (int g = lane; g < groups; g += 32) {
+      double a = 0.0, q = 0.0;
+      for (int w = 0; w < nfull; ++w) {
+        const double2 v = scratch[w * 64 + g];
+        a += v.x;
+        q += v.y;
+      }
+      const double m = a / cnt;
+      double var = q / cnt - m * m;
+      if (var < 0.0) var = 0.0;
+      stats[g] = make_float2((float)m, (float)(1.0 / sqrt(var + (double)eps)));
+    }
   }
-  const double m = a / cnt;
-  double var = q / cnt - m * m;
-  if (var < 0.0) var = 0.0;
-  return make_float2((float)m, (float)(1.0 / sqrt(var + (double)eps)));
+  __syncthreads();
 }
 
 __device__ __forceinline__ float tanh_approx(float x) {
@@ -127,19 +142,9 @@ gn_apply_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat1
                 int64_t rows_per_item, int groups, int rpp, int silu, const float* __restrict__ partial, double cnt,
                 float eps) {
   __shared__ float2 stats[64];  // {mean, rstd} of this CTA's item, per group
+  __shared__ double2 fold_scratch[(GN_MAX_THREADS / 32) * 64];
   pdl_wait();
-  {
-    // only the FULL warps fold (the block is vecs x rpp threads, > 192, rarely a multiple of 32: the trailing partial
-    // warp must stay out of the full-mask shuffles)
-    const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31, nfull = blockDim.x >> 5;
-    if (warp < nfull) {
-      for (int g = warp; g < groups; g += nfull) {
-        const float2 st = gn_fold(partial, blockIdx.y, gridDim.x, groups, g, cnt, eps, lane);
-        if (lane == 0) stats[g] = st;
-      }
-    }
-  }
-  __syncthreads();
+  gn_fold_item(partial, blockIdx.y, gridDim.x, groups, cnt, eps, fold_scratch, stats);
   const int C = C1 + C2;
   const int vecs = C >> 3;
   const int cpg = C / groups;
