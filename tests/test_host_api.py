@@ -142,3 +142,31 @@ def test_pipeline_host_pieces():
     assert shapes["transformer_in.proj_in.weight"] == (512, 320)
     t = SyntheticTokenizer()(["a rocket", ""])
     assert t.input_ids.shape == (2, 77) and t.input_ids.dtype == torch.int64
+
+
+def test_peer_window_layout_and_gather_order():
+    """exchange.window_layout: byte offsets of every rank's windows inside its peer-visible buffer, in the reference's
+    gather order (rank 0's list, rank 1's, ... chunk_only.py:133-140)."""
+    from b2v import exchange, planner
+    C, h, w, item = 4, 72, 128, 2
+    frame = C * h * w * item
+    p = planner.plan(24, 4, 0, 4, variant="coherent")   # 12 windows of 6 frames, 3 per rank
+    lay, cap = exchange.window_layout(p, 4, C, h, w, item)
+    assert [[(s, e) for s, e, _ in r] for r in lay] == [p.of_rank(r) for r in range(4)]
+    for r in range(4):
+        off = 0
+        for s, e, o in lay[r]:
+            assert o == off
+            off += (e - s) * frame
+        assert off <= cap
+    assert cap == max(sum((e - s) for s, e in p.of_rank(r)) for r in range(4)) * frame
+    p2 = planner.plan(24, 2, 0, 4, variant="coherent")
+    lay2, cap2 = exchange.window_layout(p2, 2, C, h, w, item)
+    assert lay2 == [[(0, 16, 0)], [(12, 24, 0)]] and cap2 == 16 * frame
+
+
+def test_base64_len_host_side():
+    import b2v
+    lib = b2v._lib.load()
+    for n in (0, 1, 2, 3, 4, 5, 6, 1769472):
+        assert lib.b2v_base64_len(n) == 4 * ((n + 2) // 3)
