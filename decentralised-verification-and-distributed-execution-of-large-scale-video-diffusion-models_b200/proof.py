@@ -16,6 +16,7 @@ import hashlib
 import hmac
 import logging
 import random
+import threading
 from typing import Callable, Dict, List, Optional, Tuple
 
 import numpy as np
@@ -148,15 +149,16 @@ def commit_trajectory_device(latents, noise_preds, timesteps, mode=0):
     return root, digests, paths
 
 
-_PINNED = {}
+_PINNED = threading.local()
 
 
 def _pinned(nbytes):
-    """Page-locked staging buffer, grown on demand and reused (pinning 177 MB costs more than copying it)."""
-    buf = _PINNED.get("buf")
+    """Page-locked staging buffer, grown on demand and reused (pinning 177 MB costs more than copying it). One per
+    thread: the miner serves requests from several axon worker threads without a lock of its own (miner.py:571-600)."""
+    buf = getattr(_PINNED, "buf", None)
     if buf is None or buf.numel() < nbytes:
         buf = torch.empty(max(nbytes, 1 << 20), dtype=torch.uint8, pin_memory=True)
-        _PINNED["buf"] = buf
+        _PINNED.buf = buf
     return buf
 
 
