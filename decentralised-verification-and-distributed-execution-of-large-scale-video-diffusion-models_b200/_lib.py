@@ -63,6 +63,10 @@ _SIGNATURES = {
     "b2v_op_layer_norm": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _f, _vp]),
     "b2v_op_attention": (_i, [_vp, _i64, _vp, _vp, _i64, _vp, _i64, _i, _i, _i, _i, _i, _f, _vp]),
     "b2v_op_temporal_attention": (_i, [_vp, _i64, _i, _i, _i, _vp, _i64, _i, _i, _i64, _i, _f, _vp]),
+    "b2v_op_softmax_rows": (_i, [_vp, _i64, _i, _i64, _f, _vp]),
+    "b2v_op_frames_u8": (_i, [_vp, _i64, _i64, _vp, _vp]),
+    "b2v_op_upsample2x": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
+    "b2v_op_latent_rows": (_i, [_vp, _i, _vp, _i, _i, _i, _i64, _i, _vp]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

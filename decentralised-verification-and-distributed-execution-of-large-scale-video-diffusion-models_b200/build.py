@@ -15,7 +15,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OBJ = os.path.join(CSRC, "_build")
 LIB = os.path.join(HERE, "libb2v.so")
-SOURCES = ["runtime.cu", "sha256.cu", "base64.cu", "step.cu", "norm.cu", "small.cu", "gemm.cu", "attention.cu", "unet.cu", "capi.cu"]
+SOURCES = ["runtime.cu", "sha256.cu", "base64.cu", "step.cu", "norm.cu", "small.cu", "gemm.cu", "attention.cu", "unet.cu", "vae.cu", "capi.cu"]
 
 NVCC_FLAGS = [
     "-gencode", "arch=compute_100a,code=sm_100a",

@@ -271,3 +271,43 @@ def temporal_attention(qkv, B, F, HW, heads, scale=0.125):
     check(lib.b2v_op_temporal_attention(ptr(qkv), qkv.shape[1], 0, D, 2 * D, ptr(out), D, B, F, HW, heads,
                                         float(scale), stream()))
     return out
+
+
+# ---- frame decode pieces (composed by vae.py) --------------------------------------------------
+def softmax_rows_(x, scale):
+    """In-place row softmax of bf16 scores [rows, cols] (the decoder's single 512-wide attention head)."""
+    lib = _lib.load()
+    _cuda(x)
+    rows, cols = x.shape
+    check(lib.b2v_op_softmax_rows(ptr(x), rows, cols, x.stride(0), float(scale), stream()))
+    return x
+
+
+def frames_u8(rows, n_px, out=None):
+    """Decoder output rows [n_px, ld] bf16 (RGB in channels 0..2) -> uint8 [n_px, 3]."""
+    lib = _lib.load()
+    _cuda(rows)
+    if out is None:
+        out = torch.empty((n_px, 3), dtype=torch.uint8, device=rows.device)
+    check(lib.b2v_op_frames_u8(ptr(rows), rows.stride(0), int(n_px), ptr(out), stream()))
+    return out
+
+
+def upsample2x(x):
+    """[N,H,W,C] bf16 -> [N,2H,2W,C] (nearest)."""
+    lib = _lib.load()
+    _cuda(x)
+    N, H, W, Cc = x.shape
+    y = torch.empty((N, 2 * H, 2 * W, Cc), dtype=torch.bfloat16, device=x.device)
+    check(lib.b2v_op_upsample2x(ptr(x), ptr(y), N, H, W, Cc, stream()))
+    return y
+
+
+def latent_rows(x, cpad=64):
+    """[B,C,F,h,w] (fp32/fp16/bf16) -> channels-last bf16 rows [B*F*h*w, cpad], channels >= C zero."""
+    lib = _lib.load()
+    _cuda(x)
+    B, Cc, F, h, w = x.shape
+    y = torch.empty((B * F * h * w, cpad), dtype=torch.bfloat16, device=x.device)
+    check(lib.b2v_op_latent_rows(ptr(x), dtype_tag(x), ptr(y), B, Cc, F, h * w, cpad, stream()))
+    return y

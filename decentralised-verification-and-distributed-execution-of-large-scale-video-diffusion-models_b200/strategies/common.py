@@ -50,6 +50,10 @@ def add_common_args(p, num_frames=32, out_csv="benchmarks.csv", chunking=True):
     p.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                    help="end-of-denoise window exchange: p2p = blend kernel reads the peers' windows over NVLink "
                         "(fused exchange + blend), nccl = all_gather then blend")
+    p.add_argument("--decode", action="store_true",
+                   help="decode the blended latents to frames on rank 0 (b2v.vae, random-init SD VAE decoder) and write "
+                        "the mp4 + boundary metrics like the reference; off by default because the frames of a "
+                        "random-init model are noise and the steps/s metric excludes the decode")
     return p
 
 
@@ -173,6 +177,9 @@ class WindowedDiffuser:
             LOG.info("rank %d: building random-init %s on %s", self.rank, cfg.model_id, self.device)
             pipe = VideoPipeline.from_random(cfg.model_id, device=self.device, seed=getattr(cfg, "seed", 1234),
                                              dtype=self.dtype)
+        if getattr(cfg, "decode", False) and getattr(pipe, "vae", None) is None and self.rank == 0:
+            from ..vae import AutoencoderKL
+            pipe.vae = AutoencoderKL.from_random(device=self.device, seed=getattr(cfg, "seed", 1234) + 1)
         self.pipe = pipe
         self.unet = pipe.unet
         pipe.scheduler.set_timesteps(cfg.steps, device=cfg.device)
@@ -265,7 +272,9 @@ class WindowedDiffuser:
             lat = self._blend(windows, T, plan.overlap)
             self.timings["exchange"] = "nccl" if self.world > 1 else "local"
         self.latents = lat
+        t0d = time.time()
         frames = self.decode(lat)
+        self.timings["decode_s"] = time.time() - t0d
         if self.rank == 0 and frames:
             self.write_video(frames)
         peak_local = torch.cuda.max_memory_allocated(self.device) // 1024 ** 2 if cuda else 0
@@ -293,6 +302,9 @@ class WindowedDiffuser:
         vae = getattr(self.pipe, "vae", None)
         if vae is None:
             return []
+        if hasattr(vae, "decode_frames"):
+            # b2v.vae.AutoencoderKL: the whole loop below on the device, frames leave as bytes in one copy
+            return list(vae.decode_frames(lat).cpu().numpy())
         frames = []
         for i in range(lat.shape[2]):
             z = lat[:, :, i].to(self.device, dtype=self.dtype)

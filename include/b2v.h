@@ -223,6 +223,26 @@ int b2v_op_temporal_attention(const void* qkv_dev, int64_t ld, int q_off, int k_
                               void* out_dev, int64_t ldo, int B, int F, int64_t HW, int heads,
                               float scale, void* stream);
 
+/* ------------------------------------------------------------------------------------------------
+ * Frame decode after the loop  ([UPSTREAM diffusers] pipe.vae.decode(z / 0.18215).sample and the uint8 frame
+ * conversion, chunk_only.py:152-158, fsdp_chunked_coherent.py:219-227, miner.py:594-600). The decoder's
+ * convolutions / projections / GroupNorms are the ops above; these are the remaining pieces. The host-side
+ * composition is b2v/vae.py (AutoencoderKL.decode / decode_frames).
+ * ------------------------------------------------------------------------------------------------ */
+
+/* x[r, 0:cols] = softmax(scale * x[r, 0:cols]) in place, bf16 rows of leading dimension ld, fp32 arithmetic:
+ * the mid-block attention of the decoder is ONE head of width 512 (S = Q K^T and O = P V are b2v_op_gemm calls). */
+int b2v_op_softmax_rows(void* x_dev, int64_t rows, int cols, int64_t ld, float scale, void* stream);
+/* Decoder output rows [n_px, ld] bf16 (channels 0..2 = RGB in [-1,1]) -> out [n_px, 3] bytes:
+ * (v*0.5+0.5).clamp(0,1)*255 truncated (chunk_only.py:157-158 `.byte()`); frames come out as [H,W,3]. */
+int b2v_op_frames_u8(const void* rows_dev, int64_t ld, int64_t n_px, uint8_t* out_dev, void* stream);
+/* Nearest-neighbour x2 (Upsample2D, F.interpolate(scale_factor=2, mode="nearest")): [N,H,W,C] -> [N,2H,2W,C] bf16. */
+int b2v_op_upsample2x(const void* x_dev, void* y_dev, int N, int H, int W, int C, void* stream);
+/* Latents [B,C,F,h,w] of `io_dtype` -> channels-last bf16 rows [(b,f,y,x), Cpad], channels >= C zero: the layout
+ * the tensor-core conv_in / post_quant_conv read. */
+int b2v_op_latent_rows(const void* x_dev, int io_dtype, void* rows_dev, int B, int C, int F, int64_t hw, int Cpad,
+                       void* stream);
+
 #ifdef __cplusplus
 }
 #endif

@@ -1,0 +1,85 @@
+"""not-gpu: the frame-decode oracle (oracle/vae_ref.py) and the host logic of b2v.vae (parameter table, FLOP count).
+PARITY UNPINNED for the decoder arithmetic (diffusers is absent, the reference pins nothing here): the anchors are the
+published parameter total of the SD VAE decoder and its state_dict key set."""
+import math
+from types import SimpleNamespace
+
+import torch
+
+from oracle import vae_ref as V
+
+
+def test_parameter_total_and_keys():
+    # SD VAE: decoder 49 490 179 + post_quant_conv 20 (the full autoencoder's published 83 653 863 minus the encoder
+    # 34 163 592 and quant_conv 72)
+    assert V.param_count() == 49490199 == 83653863 - 34163592 - 72
+    sd = V.AutoencoderKLDecoder(V.SD_VAE).state_dict()
+    assert len(sd) == 140
+    for k in ("post_quant_conv.weight", "decoder.conv_in.weight", "decoder.mid_block.attentions.0.to_q.weight",
+              "decoder.mid_block.attentions.0.to_out.0.bias", "decoder.mid_block.attentions.0.group_norm.weight",
+              "decoder.up_blocks.2.resnets.0.conv_shortcut.weight", "decoder.up_blocks.0.upsamplers.0.conv.weight",
+              "decoder.conv_norm_out.weight", "decoder.conv_out.bias"):
+        assert k in sd, k
+    assert "decoder.up_blocks.3.upsamplers.0.conv.weight" not in sd
+    assert tuple(sd["decoder.up_blocks.3.resnets.0.conv1.weight"].shape) == (128, 256, 3, 3)
+
+
+def test_host_parameter_table_matches_oracle():
+    from b2v import vae
+    for cfg in (V.SD_VAE, V.TINY):
+        shapes = vae.parameter_shapes(cfg.to_dict())
+        sd = V.AutoencoderKLDecoder(cfg).state_dict()
+        assert set(shapes) == set(sd)
+        assert all(tuple(sd[k].shape) == tuple(s) for k, s in shapes.items())
+
+
+def test_decode_shapes_and_frame_bytes():
+    from oracle.unet3d_ref import random_init_
+    m = random_init_(V.AutoencoderKLDecoder(V.TINY), seed=3).eval()
+    lat = torch.randn(1, 4, 2, 8, 8, generator=torch.Generator().manual_seed(0)) * 0.3
+    u8, raw = V.frames_u8(m, lat)
+    assert u8.shape == (2, 64, 64, 3) and u8.dtype == torch.uint8
+    assert float(raw.min()) >= 0 and float(raw.max()) <= 255
+    assert torch.equal(u8, raw.floor().to(torch.uint8))  # `.byte()` truncates
+    with torch.no_grad():
+        one = m.decode(lat[:, :, 1] / 0.18215)
+    assert one.shape == (1, 3, 64, 64)
+    assert torch.equal(((one[0].permute(1, 2, 0) * 0.5 + 0.5).clamp(0, 1) * 255).to(torch.uint8), u8[1])
+
+
+def test_attention_is_one_head_of_full_width():
+    """softmax(q k^T / sqrt(C)) v with the V bias moved behind P V (what the device path does) is the same function."""
+    a = V.Attention(64, 32, 1e-6)
+    x = torch.randn(1, 64, 4, 4, generator=torch.Generator().manual_seed(1))
+    with torch.no_grad():
+        want = a(x)
+        t = a.group_norm(x).view(1, 64, 16).transpose(1, 2)
+        p = torch.softmax(a.to_q(t) @ a.to_k(t).transpose(1, 2) / 8.0, dim=-1)
+        vt = a.to_v.weight @ t[0].t()                                   # V^T without bias
+        o = p[0] @ vt.t() + a.to_v.bias
+        got = x + a.to_out[0](o).t().reshape(1, 64, 4, 4)
+    assert float((got - want).abs().max()) < 1e-5
+
+
+def test_flop_count_matches_module_walk():
+    from b2v import vae
+    for cfg, (h, w) in ((V.TINY, (8, 8)), (V.SD_VAE, (8, 16))):
+        m = V.AutoencoderKLDecoder(cfg).eval()
+        total = [0.0]
+
+        def hook(mod, inp, out):
+            if isinstance(mod, torch.nn.Conv2d):
+                total[0] += 2.0 * out.numel() * mod.in_channels * mod.kernel_size[0] * mod.kernel_size[1]
+            elif isinstance(mod, torch.nn.Linear):
+                total[0] += 2.0 * out.numel() * mod.in_features
+
+        hs = [mod.register_forward_hook(hook) for mod in m.modules()]
+        with torch.no_grad():
+            m.decode(torch.zeros(1, 4, h, w))
+        for x in hs:
+            x.remove()
+        c = list(reversed(cfg.block_out_channels))[0]
+        total[0] += 4.0 * (h * w) ** 2 * c  # Q K^T and P V
+        obj = SimpleNamespace(config=SimpleNamespace(**cfg.to_dict()))
+        got = vae.AutoencoderKL.flops(obj, 1, h, w)
+        assert math.isclose(got, total[0], rel_tol=1e-9), (got, total[0])
