@@ -393,6 +393,12 @@ def gpu_main(args):
         merkle["in_loop"] = in_loop_commit(torch, pipe, emb[:1], dev, h, w)
     except Exception as ex:  # a report, never a reason to lose the line
         merkle["in_loop"] = {"error": repr(ex)}
+    decode = None
+    if world == 1:
+        try:
+            decode = frame_decode(torch, dev, peaks, h, w, cpu=not args.no_cpu_baseline)
+        except Exception as ex:  # a report, never a reason to lose the line
+            decode = {"error": repr(ex)}
     cpu = None
     if world == 1 and not args.no_cpu_baseline:
         try:
@@ -411,12 +417,51 @@ def gpu_main(args):
                    "l2": "no flush: each step streams 2.8 GB of weights + >2 GB of activations (>> 126 MB L2)"},
         "e2e": {"value": e2e_value, "unit": "steps/s", "h2d_bytes_per_step": bi, "d2h_bytes_per_step": bo},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "roofline_step": roofline_step,
-        "merkle": merkle, "cpu_baseline": cpu,
+        "merkle": merkle, "frame_decode": decode, "cpu_baseline": cpu,
     }
     emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def frame_decode(torch, dev, peaks, h, w, cpu=True):
+    """SURVEY.md §8f N1 (chunk_only.py:152-158): the FRAMES blended latents -> uint8 frames, SD VAE decoder with
+    random-init weights. Device time with CUDA events; e2e adds the device->pinned-host copy of the frame bytes."""
+    from b2v.vae import AutoencoderKL
+    net = AutoencoderKL.from_random(device=dev)
+    lat = (torch.randn(1, 4, FRAMES, h, w, generator=torch.Generator().manual_seed(3)) * 0.3).to(dev)
+    host = torch.empty((FRAMES, 8 * h, 8 * w, 3), dtype=torch.uint8).pin_memory()
+    l0 = ops_launches()
+    ms = _time_cuda(torch, lambda: net.decode_frames(lat), iters=2, warm=1)
+    launches = (ops_launches() - l0) // 3
+    ms_e2e = _time_cuda(torch, lambda: host.copy_(net.decode_frames(lat), non_blocking=True), iters=2, warm=1)
+    fl = net.flops(FRAMES, h, w)
+    out = {"workload": "%d frames %dx%d, SD VAE decoder (49.5 M params, random init), bf16" % (FRAMES, 8 * w, 8 * h),
+           "ms": ms, "frames_per_s": FRAMES / ms * 1e3, "e2e_ms": ms_e2e, "e2e_frames_per_s": FRAMES / ms_e2e * 1e3,
+           "d2h_bytes": host.numel(), "gpu_launches": int(launches),
+           "roofline": {"bound": "tensor", "achieved": fl / ms / 1e9, "peak": peaks["bf16_sustained"], "unit": "TFLOP/s",
+                        "frac": fl / ms / 1e9 / peaks["bf16_sustained"],
+                        "what": "algorithmic FLOPs of convs + projections + attention (MAC=2) / CUDA-event time"}}
+    if cpu:
+        from oracle import vae_ref as V  # CPU baseline leg: the oracle as the reported baseline, never the product
+        from oracle.unet3d_ref import random_init_
+        ref = random_init_(V.AutoencoderKLDecoder(V.SD_VAE), seed=4321).eval()
+        ch, cw = 40, 72  # one 576x320 frame: a bounded sample (1.8 TFLOP fp32)
+        z = torch.randn(1, 4, 1, ch, cw, generator=torch.Generator().manual_seed(3)) * 0.3
+        t0 = time.perf_counter()
+        V.frames_u8(ref, z)
+        dt = time.perf_counter() - t0
+        out["cpu_baseline"] = {"value": 1.0 / dt * (ch * cw) / (h * w), "unit": "frames/s at %dx%d" % (8 * w, 8 * h),
+                               "cores": torch.get_num_threads(), "kind": "port",
+                               "sample": "1 frame of 576x320 decoded by oracle/vae_ref.py (fp32 torch CPU) in %.2f s, "
+                                         "scaled by the pixel ratio" % dt}
+    return out
+
+
+def ops_launches():
+    from b2v import ops
+    return ops.launch_count()
 
 
 def _time_cuda(torch, fn, iters=3, warm=2):

@@ -7,6 +7,7 @@ Layout
   _lib.py, ops.py  ctypes binding; torch supplies device memory and streams only
   scheduler.py     DDIMScheduler with the diffusers call surface the strategies/miner use
   unet.py          UNet3DConditionModel: pipe.unet(x, t, encoder_hidden_states=emb).sample
+  vae.py           AutoencoderKL: pipe.vae.decode(z / 0.18215).sample and decode_frames (latents -> uint8 frames)
   pipeline.py      pipe-shaped object (unet, scheduler, synthetic text encoder)
   planner.py       chunk planner / blend weights (host integer logic of chunk_only.py:80-105, 136-150)
   strategies/      chunk_only / fsdp_chunked_coherent / fsdp_chunked / fsdp entry points (same CLI + CSV)
@@ -18,4 +19,4 @@ The directory name is not a Python identifier; ``import b2v`` (repo-root shim) a
 from . import _lib  # noqa: F401
 from ._lib import B2VError, EXPORTED_SYMBOLS  # noqa: F401
 
-__all__ = ["_lib", "ops", "scheduler", "unet", "pipeline", "planner", "proof", "strategies", "B2VError"]
+__all__ = ["_lib", "ops", "scheduler", "unet", "vae", "pipeline", "planner", "proof", "strategies", "B2VError"]
