@@ -316,14 +316,12 @@ def run_unet_step(z_bytes: bytes, eps_bytes: bytes, config: dict, step_i: int) -
         return False
 
 
-def verify_temporal_coherence_spot_check(spot_check_indices: List[int],
-                                         leaves_result: Dict[str, Tuple[str, str, List[str]]],
-                                         timestep_to_step: Dict[int, int], proof_alphas: List[float],
-                                         unet_config: Dict, request_id: str = None, logger=None) -> bool:
-    if logger is None:
-        logger = LOG
+def _coherence_plan(spot_check_indices, leaves_result, timestep_to_step, proof_alphas, unet_config, request_id, logger):
+    """Host half of the temporal-coherence check (proof.py:419-626): everything the reference decides before any
+    arithmetic. Returns (verdict, zs, es, zn, steps, order, early_false): `verdict` is the final answer when no device
+    work is needed, else None and the fp16 frame-0 arrays of every consecutive pair to settle in one launch."""
     if len(spot_check_indices) < 2:
-        return True
+        return True, [], [], [], [], [], False
     leaf = {}
     for t in spot_check_indices:
         item = leaves_result.get(str(t))
@@ -332,7 +330,7 @@ def verify_temporal_coherence_spot_check(spot_check_indices: List[int],
         else:
             logger.warning("[%s] Missing or malformed leaf for timestep %s" % (request_id, t))
     if len(leaf) < 2:
-        return True
+        return True, [], [], [], [], [], False
     order = [t for t in spot_check_indices if t in leaf]
     if len(order) > len(proof_alphas):
         order = order[:len(proof_alphas)]
@@ -340,9 +338,8 @@ def verify_temporal_coherence_spot_check(spot_check_indices: List[int],
         _default_scheduler(len(proof_alphas))
     except Exception as e:
         logger.error("[%s] Error setting up scheduler: %s" % (request_id, e))
-        return False
-    # Collect every consecutive pair, stop at the first one the reference would reject before any arithmetic,
-    # then settle all arithmetic verdicts in ONE launch and apply them in order.
+        return False, [], [], [], [], order, False
+    # Collect every consecutive pair, stop at the first one the reference would reject before any arithmetic
     zs, es, zn, steps = [], [], [], []
     early_false = False
     for t_i, t_j in zip(order[:-1], order[1:]):
@@ -370,18 +367,34 @@ def verify_temporal_coherence_spot_check(spot_check_indices: List[int],
             early_false = True
             break
         zs.append(a); es.append(b); zn.append(c); steps.append(step_i)
+    return None, zs, es, zn, steps, order, early_false
+
+
+def _coherence_verdict(flags, order, early_false, request_id, logger):
+    """Apply the arithmetic verdicts in order (first failing pair decides), then the host-side early rejection."""
+    for k, f in enumerate(flags):
+        if not f & _FLAG_CLOSE:
+            logger.warning("[%s] Cross-step check failed between t=%s and t=%s" % (request_id, order[k], order[k + 1]))
+            return False
+    return not early_false
+
+
+def verify_temporal_coherence_spot_check(spot_check_indices: List[int],
+                                         leaves_result: Dict[str, Tuple[str, str, List[str]]],
+                                         timestep_to_step: Dict[int, int], proof_alphas: List[float],
+                                         unet_config: Dict, request_id: str = None, logger=None) -> bool:
+    if logger is None:
+        logger = LOG
+    verdict, zs, es, zn, steps, order, early_false = _coherence_plan(
+        spot_check_indices, leaves_result, timestep_to_step, proof_alphas, unet_config, request_id, logger)
+    if verdict is not None:
+        return verdict
     try:
-        if zs:
-            flags = spotcheck_flags(zs, es, zn, steps, len(proof_alphas), unet_config)
-            for k, f in enumerate(flags):
-                if not f & _FLAG_CLOSE:
-                    logger.warning("[%s] Cross-step check failed between t=%s and t=%s" % (request_id, order[k],
-                                                                                            order[k + 1]))
-                    return False
+        flags = spotcheck_flags(zs, es, zn, steps, len(proof_alphas), unet_config) if zs else []
+        return _coherence_verdict(flags, order, early_false, request_id, logger)
     except Exception as e:
         logger.error("[%s] Error in temporal coherence computation: %s" % (request_id, e))
         return False
-    return not early_false
 
 
 # ---------------------------------------------------------------------------------------------------------------
