@@ -170,3 +170,22 @@ def test_base64_len_host_side():
     lib = b2v._lib.load()
     for n in (0, 1, 2, 3, 4, 5, 6, 1769472):
         assert lib.b2v_base64_len(n) == 4 * ((n + 2) // 3)
+
+
+def test_select_spot_check_pairs_matches_oracle():
+    """validator.py:641-684 (index draw): same picks as the oracle restatement for seeded generators; duplicates dropped."""
+    import random
+    from b2v.validator import select_spot_check_pairs
+    from oracle import validator_ref as VR
+    ts = [981 - 20 * i for i in range(50)]
+    for seed in range(20):
+        for k in (1, 5, 30, 80):
+            got = select_spot_check_pairs(ts, k, random.Random(seed))
+            assert got == VR.select_pairs(ts, k, random.Random(seed))
+            assert len(got) == len(set(got)) and len(got) % 2 == 0 and len(got) <= 2 * min(k, 49)
+            assert all(ts.index(got[i + 1]) == ts.index(got[i]) + 1 for i in range(0, len(got), 2))
+    assert select_spot_check_pairs([7], 3) == [7] and select_spot_check_pairs([], 3) == []
+    random.seed(3)
+    a = select_spot_check_pairs(ts, 5)   # default generator = the global `random`, as in the reference
+    random.seed(3)
+    assert a == VR.select_pairs(ts, 5)
