@@ -40,6 +40,7 @@ _SIGNATURES = {
     "b2v_merkle_scratch_bytes": (_sz, [_i]),
     "b2v_merkle_build": (_i, [_vp, _i, _vp, _vp, _vp, _vp]),
     "b2v_merkle_verify": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
+    "b2v_merkle_verify_roots": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
     "b2v_base64_len": (_u64, [_u64]),
     "b2v_base64_rows": (_i, [_vp, _i64, _u64, _u64, _vp, _vp]),
     "b2v_spotcheck_ddim": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i64, _vp, _vp]),

@@ -364,7 +364,7 @@ __global__ void merkle_paths_kernel(const uint8_t* __restrict__ levels, int n, i
 }
 
 __global__ void merkle_verify_kernel(const uint8_t* __restrict__ leaf_hashes, const uint8_t* __restrict__ paths,
-                                     int m, int depth, const uint8_t* __restrict__ root,
+                                     int m, int depth, const uint8_t* __restrict__ root, int root_stride,
                                      uint8_t* __restrict__ ok) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i >= m) return;
@@ -376,7 +376,7 @@ __global__ void merkle_verify_kernel(const uint8_t* __restrict__ leaf_hashes, co
 #pragma unroll
     for (int j = 0; j < 8; ++j) cur[j] = o[j];
   }
-  load_node(root, sib);
+  load_node(root + (size_t)i * root_stride, sib);  // stride 0: one tree; 32: one root per leaf (many miners)
   bool eq = true;
 #pragma unroll
   for (int j = 0; j < 8; ++j) eq = eq && (cur[j] == sib[j]);
@@ -483,7 +483,20 @@ extern "C" int b2v_merkle_verify(const uint8_t* leaf_hashes_dev, const uint8_t* 
   B2V_CHECK(leaf_hashes_dev && root_dev && ok_dev && (depth == 0 || paths_dev), "null argument");
   B2V_TRY(b2v_device_check());
   merkle_verify_kernel<<<(m + 63) / 64, 64, 0, (cudaStream_t)stream>>>(leaf_hashes_dev, paths_dev, m, depth,
-                                                                     root_dev, ok_dev);
+                                                                     root_dev, 0, ok_dev);
+  count_launch();
+  B2V_CUDA_OK(launch_check());
+  return 0;
+}
+
+extern "C" int b2v_merkle_verify_roots(const uint8_t* leaf_hashes_dev, const uint8_t* paths_dev, int m, int depth,
+                                       const uint8_t* roots_dev, uint8_t* ok_dev, void* stream) {
+  B2V_CHECK(m >= 0 && depth >= 0, "bad sizes");
+  if (m == 0) return 0;
+  B2V_CHECK(leaf_hashes_dev && roots_dev && ok_dev && (depth == 0 || paths_dev), "null argument");
+  B2V_TRY(b2v_device_check());
+  merkle_verify_kernel<<<(m + 63) / 64, 64, 0, (cudaStream_t)stream>>>(leaf_hashes_dev, paths_dev, m, depth,
+                                                                     roots_dev, 32, ok_dev);
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;

@@ -183,6 +183,18 @@ def merkle_verify(leaf_hashes, paths, root):
     return ok
 
 
+def merkle_verify_roots(leaf_hashes, paths, roots):
+    """Leaves of different trees in one launch: leaf i against roots[i]. All CUDA uint8: [m,32], [m,depth,32], [m,32]."""
+    lib = _lib.load()
+    _cuda(leaf_hashes); _cuda(paths); _cuda(roots)
+    m, depth = paths.shape[0], paths.shape[1]
+    if roots.shape != (m, 32) or leaf_hashes.shape != (m, 32):
+        raise ValueError("merkle_verify_roots: expected [m,32] hashes and roots")
+    ok = torch.empty(m, dtype=torch.uint8, device=leaf_hashes.device)
+    check(lib.b2v_merkle_verify_roots(ptr(leaf_hashes), ptr(paths), m, depth, ptr(roots), ptr(ok), stream()))
+    return ok
+
+
 def spotcheck_ddim(z_list, eps_list, znext_list, a_t, a_prev, C_, F, hw):
     import numpy as np
     lib = _lib.load()

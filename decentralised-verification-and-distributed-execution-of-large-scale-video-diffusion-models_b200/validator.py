@@ -7,8 +7,8 @@ folds the Merkle path, re-derives the DDIM step (``run_unet_step``) and finally 
   * ``select_spot_check_pairs``  the index draw of validator.py:641-684 (global ``random``, duplicate timesteps dropped);
   * ``check_revealed_leaves``    one miner, the reference's order of checks (validator.py:768-830);
   * ``check_miners``             all miners at once: ONE ``b2v_sha256_leaves`` launch over every revealed leaf of every
-                                 miner (bytes staged through one pinned buffer), one ``b2v_merkle_verify`` per
-                                 (miner, path depth), ONE ``b2v_spotcheck_ddim`` launch per scheduler length for all
+                                 miner (bytes staged through one pinned buffer), ONE ``b2v_merkle_verify_roots``
+                                 per path depth (leaf i against its own miner's root), ONE ``b2v_spotcheck_ddim`` launch per scheduler length for all
                                  P4 verdicts and ONE for all temporal-coherence pairs.
 
 Both return exactly what a loop over ``check_revealed_leaves`` returns (``tests/test_gpu_validator.py``). Networking
@@ -151,21 +151,39 @@ def check_miners(subs: Sequence[Submission], request_id: Optional[str] = None, l
         blob[:total].copy_(host, non_blocking=True)
         zs = [blob[o:o + ln] for o, ln in spans[0::2]]
         es = [blob[o:o + ln] for o, ln in spans[1::2]]
-        digests = ops.sha256_leaves(zs, es, [lf[1] for lf in live]).cpu().numpy()
-        # ---- membership: one launch per (miner, depth) ------------------------------------------------------------
-        by_miner: Dict[int, List[int]] = {}
+        digests = ops.sha256_leaves(zs, es, [lf[1] for lf in live])              # [n,32], stays on the device
+        # ---- membership: every leaf of every miner against its own root, ONE launch per path depth ------------------
+        by_depth: Dict[int, List[int]] = {}
+        odd: Dict[int, List[int]] = {}
         for i, lf in enumerate(live):
-            by_miner.setdefault(lf[0], []).append(i)
-        for m, idxs in by_miner.items():
-            try:
-                res = proof.verify_merkle_leaves([digests[i].tobytes() for i in idxs], [live[i][4] for i in idxs],
-                                                 subs[m].merkle_root)
-            except Exception as ex:
-                logger.error("[%s] Merkle verification of miner %s failed: %r", request_id, subs[m].uid, ex)
-                res = [False] * len(idxs)
-            if not all(res):
-                logger.warning("[%s] Merkle verification failed for miner %s", request_id, subs[m].uid)
-                ok[m] = False
+            if len(subs[lf[0]].merkle_root) == 32 and all(len(p) == 32 for p in lf[4]):
+                by_depth.setdefault(len(lf[4]), []).append(i)
+            else:  # nodes that cannot come from this protocol: the generic per-miner path (same answer as hashlib)
+                odd.setdefault(lf[0], []).append(i)
+        for depth, idxs in by_depth.items():
+            sel = torch.tensor(idxs, dtype=torch.long, device=dev)
+            pb = b"".join(b"".join(live[i][4]) for i in idxs)
+            paths = proof._to_dev_bytes(pb, dev).reshape(len(idxs), depth, 32) if depth else \
+                torch.empty((len(idxs), 0, 32), dtype=torch.uint8, device=dev)
+            roots = proof._to_dev_bytes(b"".join(subs[live[i][0]].merkle_root for i in idxs), dev).reshape(len(idxs), 32)
+            res = ops.merkle_verify_roots(digests.index_select(0, sel).contiguous(), paths, roots).cpu().numpy()
+            for i, r in zip(idxs, res):
+                if not r:
+                    logger.warning("[%s] Merkle verification failed for miner %s at t=%s", request_id,
+                                   subs[live[i][0]].uid, live[i][1])
+                    ok[live[i][0]] = False
+        if odd:
+            host_digests = digests.cpu().numpy()
+            for m, idxs in odd.items():
+                try:
+                    res = proof.verify_merkle_leaves([host_digests[i].tobytes() for i in idxs], [live[i][4] for i in idxs],
+                                                     subs[m].merkle_root)
+                except Exception as ex:
+                    logger.error("[%s] Merkle verification of miner %s failed: %r", request_id, subs[m].uid, ex)
+                    res = [False]
+                if not all(res):
+                    logger.warning("[%s] Merkle verification failed for miner %s", request_id, subs[m].uid)
+                    ok[m] = False
         # ---- run_unet_step verdicts: one launch per (scheduler length, latent shape) --------------------------------
         groups: Dict[Tuple, List[int]] = {}
         frames = {}

@@ -81,6 +81,11 @@ int b2v_merkle_build(const uint8_t* leaf_hashes_dev, int n, uint8_t* root_dev, u
 int b2v_merkle_verify(const uint8_t* leaf_hashes_dev, const uint8_t* paths_dev, int m, int depth,
                       const uint8_t* root_dev, uint8_t* ok_dev, void* stream);
 
+/* The same fold for leaves of DIFFERENT trees (a validator round over many miners, neurons/validator.py:768-790):
+ * leaf i is checked against roots_dev[i] ([m][32]). */
+int b2v_merkle_verify_roots(const uint8_t* leaf_hashes_dev, const uint8_t* paths_dev, int m, int depth,
+                            const uint8_t* roots_dev, uint8_t* ok_dev, void* stream);
+
 /* Spot-check DDIM re-check on device (proof.py:307-392 run_unet_step and proof.py:419-626
  * verify_temporal_coherence_spot_check, default-config DDIMScheduler branch, Appendix C of SURVEY.md).
  * For each of m leaf pairs: z_i/eps_i/z_j are fp16 [1,C,F,h,w] device buffers of which only frame 0 is

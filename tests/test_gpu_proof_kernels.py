@@ -124,3 +124,25 @@ def test_base64_rows_fp16_latent(cuda):
     enc = ops.base64_rows(z.to(cuda)).cpu().numpy()
     for i in range(4):
         assert enc[i].tobytes() == base64.b64encode(z[i].numpy().tobytes())
+
+
+def test_merkle_verify_roots_many_trees(cuda):
+    """b2v_merkle_verify_roots: leaves of different trees (a validator round over many miners) in one launch, each
+    against its own root; bit-exact vs the oracle fold."""
+    import hashlib
+    from b2v import ops
+    from oracle import merkle_ref as M
+    trees = []
+    for k in range(5):
+        hashes = [hashlib.sha256(bytes([k, i])).digest() for i in range(9 + k)]   # depth 4 for 9..13 leaves
+        levels = M.tree_levels(hashes)
+        trees.append((hashes, M.sibling_paths(levels), levels[-1][0]))
+    rows = [(k, i) for k in range(5) for i in (0, 3, len(trees[k][0]) - 1)]
+    lh = torch.tensor(list(b"".join(trees[k][0][i] for k, i in rows)), dtype=torch.uint8, device=cuda).view(-1, 32)
+    pt = torch.tensor(list(b"".join(b"".join(trees[k][1][i]) for k, i in rows)), dtype=torch.uint8, device=cuda).view(len(rows), 4, 32)
+    roots = [trees[k][2] for k, _ in rows]
+    roots[4] = trees[0][2]                       # a leaf of tree 1 presented against tree 0's root
+    rt = torch.tensor(list(b"".join(roots)), dtype=torch.uint8, device=cuda).view(-1, 32)
+    ok = ops.merkle_verify_roots(lh, pt, rt).cpu().tolist()
+    want = [int(M.verify_merkle_leaf(trees[k][0][i], trees[k][1][i], roots[j])) for j, (k, i) in enumerate(rows)]
+    assert ok == want and want.count(0) == 1 and want[4] == 0
