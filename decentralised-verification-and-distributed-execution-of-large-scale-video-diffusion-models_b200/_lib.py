@@ -43,6 +43,7 @@ _SIGNATURES = {
     "b2v_merkle_verify_roots": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
     "b2v_base64_len": (_u64, [_u64]),
     "b2v_base64_rows": (_i, [_vp, _i64, _u64, _u64, _vp, _vp]),
+    "b2v_base64_decode_rows": (_i, [_vp, _i64, _u64, _u64, _vp, _u64, _vp, _vp]),
     "b2v_spotcheck_ddim": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _i, _i, _i64, _vp, _vp]),
     "b2v_cfg_ddim_step": (_i, [_vp, _vp, _vp, _f, _i, _f, _f, _f, _i, _vp, _vp, _i, _vp, _vp, _i, _i, _i, _i64, _vp]),
     "b2v_make_unet_input": (_i, [_vp, _vp, _f, _vp, _i, _i, _i, _i, _i64, _vp]),

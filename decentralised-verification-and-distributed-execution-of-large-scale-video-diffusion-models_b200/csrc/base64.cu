@@ -63,10 +63,100 @@ base64_rows_kernel(const uint8_t* __restrict__ src, int64_t n_rows, uint64_t row
   }
 }
 
+// ---- decode (the validator's side of the wire: neurons/validator.py:783-786 `base64.b64decode(z_b)`) ----------------
+// ASCII -> 6-bit value, branch-free; 64 = '=' (padding), 255 = not in the alphabet
+__device__ __forceinline__ uint32_t b64_val(uint32_t c) {
+  uint32_t v = 255u;
+  v = (c - 65u < 26u) ? c - 65u : v;   // 'A'..'Z'
+  v = (c - 97u < 26u) ? c - 71u : v;   // 'a'..'z'
+  v = (c - 48u < 10u) ? c + 4u : v;    // '0'..'9'
+  v = (c == 43u) ? 62u : v;            // '+'
+  v = (c == 47u) ? 63u : v;            // '/'
+  v = (c == 61u) ? 64u : v;            // '='
+  return v;
+}
+
+// One thread = 16 characters -> 12 bytes. Every row has row_chars characters (a multiple of 4). status[row] gets
+// (pad count 0..2) | 0x100 when the row is not canonical base64 (a character outside the alphabet, or '=' anywhere but
+// in the last one or two positions): the caller then decodes that row with the reference's own permissive routine.
+// Trailing non-zero bits in a padded quad are ignored, as binascii does. Padded byte positions are written as zero.
+__global__ void __launch_bounds__(256)
+base64_decode_rows_kernel(const uint8_t* __restrict__ src, int64_t n_rows, uint64_t row_chars, uint64_t row_stride,
+                          uint8_t* __restrict__ dst, uint64_t dst_stride, int* __restrict__ status, int aligned) {
+  const uint64_t groups = (row_chars + 15) / 16;
+  const uint64_t total = (uint64_t)n_rows * groups;
+  for (uint64_t i = (uint64_t)blockIdx.x * blockDim.x + threadIdx.x; i < total; i += (uint64_t)gridDim.x * blockDim.x) {
+    const uint64_t row = i / groups, gidx = i - row * groups;
+    const uint8_t* s = src + row * row_stride + gidx * 16;
+    uint8_t* d = dst + row * dst_stride + gidx * 12;
+    const uint64_t left = row_chars - gidx * 16;
+    const int n = left < 16 ? (int)left : 16;  // characters in this group (multiple of 4)
+    uint32_t w[4] = {0x41414141u, 0x41414141u, 0x41414141u, 0x41414141u};  // "AAAA": decodes to zero
+    if (n == 16 && aligned) {
+      const uint4 u = __ldg(reinterpret_cast<const uint4*>(s));
+      w[0] = u.x; w[1] = u.y; w[2] = u.z; w[3] = u.w;
+    } else {
+      for (int k = 0; k < n; ++k) w[k >> 2] = (w[k >> 2] & ~(255u << (8 * (k & 3)))) | ((uint32_t)s[k] << (8 * (k & 3)));
+    }
+    uint32_t bad = 0, pad = 0;
+    uint8_t o[12];
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      uint32_t v[4];
+#pragma unroll
+      for (int k = 0; k < 4; ++k) v[k] = b64_val((w[q] >> (8 * k)) & 255u);
+      const bool last = (uint64_t)(q * 4 + 4) == left;  // the final quad of the row: '=' allowed in positions 2, 3
+      uint32_t p = 0;
+      if (last && v[3] == 64u) { p = 1; v[3] = 0; if (v[2] == 64u) { p = 2; v[2] = 0; } }
+      pad |= p;
+      bad |= (v[0] | v[1] | v[2] | v[3]) >> 6;  // 64 ('=' elsewhere) or 255 (outside the alphabet)
+      const uint32_t t = ((v[0] & 63u) << 18) | ((v[1] & 63u) << 12) | ((v[2] & 63u) << 6) | (v[3] & 63u);
+      o[3 * q] = (uint8_t)(t >> 16); o[3 * q + 1] = (uint8_t)(t >> 8); o[3 * q + 2] = (uint8_t)t;
+    }
+    const int nb = (n >> 2) * 3;
+    if (nb == 12 && aligned) {
+      uint32_t* d4 = reinterpret_cast<uint32_t*>(d);
+#pragma unroll
+      for (int k = 0; k < 3; ++k)
+        d4[k] = (uint32_t)o[4 * k] | ((uint32_t)o[4 * k + 1] << 8) | ((uint32_t)o[4 * k + 2] << 16) | ((uint32_t)o[4 * k + 3] << 24);
+    } else {
+#pragma unroll
+      for (int k = 0; k < 12; ++k)
+        if (k < nb) d[k] = o[k];
+    }
+    if (bad) atomicOr(status + row, 0x100);
+    if (pad) atomicOr(status + row, (int)pad);
+  }
+}
+
 }  // namespace
 }  // namespace b2v
 
 using namespace b2v;
+
+extern "C" int b2v_base64_decode_rows(const void* src_dev, int64_t n_rows, uint64_t row_chars, uint64_t row_stride,
+                                      void* dst_dev, uint64_t dst_stride, int* status_dev, void* stream) {
+  B2V_CHECK(n_rows >= 0, "n_rows < 0");
+  if (n_rows == 0) return 0;
+  B2V_CHECK(status_dev, "null status");
+  B2V_CHECK(row_chars % 4 == 0, "base64 rows must hold a multiple of 4 characters (got %llu)", (unsigned long long)row_chars);
+  B2V_TRY(b2v_device_check());
+  cudaStream_t s = (cudaStream_t)stream;
+  B2V_CUDA_OK(cudaMemsetAsync(status_dev, 0, sizeof(int) * (size_t)n_rows, s));
+  if (row_chars == 0) return 0;
+  B2V_CHECK(src_dev && dst_dev, "null argument");
+  B2V_CHECK(row_stride >= row_chars && dst_stride >= row_chars / 4 * 3, "row strides shorter than the rows");
+  const int aligned = (((uintptr_t)src_dev | row_stride) & 15) == 0 && (((uintptr_t)dst_dev | dst_stride) & 3) == 0;
+  const uint64_t total = (uint64_t)n_rows * ((row_chars + 15) / 16);
+  uint64_t blocks = (total + 255) / 256;
+  const uint64_t cap = (uint64_t)sm_count() * 16;
+  if (blocks > cap) blocks = cap;
+  base64_decode_rows_kernel<<<(unsigned)blocks, 256, 0, s>>>((const uint8_t*)src_dev, n_rows, row_chars, row_stride,
+                                                             (uint8_t*)dst_dev, dst_stride, status_dev, aligned);
+  count_launch();
+  B2V_CUDA_OK(launch_check());
+  return 0;
+}
 
 extern "C" uint64_t b2v_base64_len(uint64_t nbytes) { return 4 * ((nbytes + 2) / 3); }
 

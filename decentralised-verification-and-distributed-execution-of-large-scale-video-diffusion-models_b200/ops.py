@@ -129,6 +129,22 @@ def base64_rows(buf, n_rows=None):
     return out
 
 
+def base64_decode_rows(buf, row_chars=None):
+    """Rows of base64 text (CUDA uint8 [n, stride], the first row_chars characters of each row) -> (bytes [n, dst_stride]
+    CUDA uint8 with dst_stride = 3*row_chars/4 rounded up to 256, status int32 [n]: pad count | 0x100 if the row is not
+    canonical base64 and must be decoded by the caller's permissive host routine)."""
+    lib = _lib.load()
+    _cuda(buf)
+    n = buf.shape[0]
+    row_chars = buf.shape[1] if row_chars is None else int(row_chars)
+    nbytes = row_chars // 4 * 3
+    stride = max(256, (nbytes + 255) // 256 * 256)
+    out = torch.empty((n, stride), dtype=torch.uint8, device=buf.device)
+    status = torch.empty(n, dtype=torch.int32, device=buf.device)
+    check(lib.b2v_base64_decode_rows(ptr(buf), n, row_chars, buf.stride(0), ptr(out), stride, ptr(status), stream()))
+    return out, status
+
+
 # ---- proof -----------------------------------------------------------------------------------------------------
 def sha256_leaves(a_list, b_list=None, prefixes=None, mode=0):
     """digest[i] = SHA256(prefix_i(2B BE, optional) ‖ bytes(a_i) ‖ bytes(b_i)); tensors are hashed in place on the

@@ -6,10 +6,12 @@ folds the Merkle path, re-derives the DDIM step (``run_unet_step``) and finally 
 
   * ``select_spot_check_pairs``  the index draw of validator.py:641-684 (global ``random``, duplicate timesteps dropped);
   * ``check_revealed_leaves``    one miner, the reference's order of checks (validator.py:768-830);
-  * ``check_miners``             all miners at once: ONE ``b2v_sha256_leaves`` launch over every revealed leaf of every
-                                 miner (bytes staged through one pinned buffer), ONE ``b2v_merkle_verify_roots``
-                                 per path depth (leaf i against its own miner's root), ONE ``b2v_spotcheck_ddim`` launch per scheduler length for all
-                                 P4 verdicts and ONE for all temporal-coherence pairs.
+  * ``check_miners``             all miners at once: the revealed leaves cross PCIe ONCE, as the base64 text they
+                                 arrived in (one pinned matrix per text length), ``b2v_base64_decode_rows`` decodes
+                                 them on the device, ONE ``b2v_sha256_leaves`` launch hashes every leaf of every miner
+                                 in place, ONE ``b2v_merkle_verify_roots`` per path depth checks leaf i against its
+                                 own miner's root, and ONE ``b2v_spotcheck_ddim`` launch settles every run_unet_step
+                                 verdict and every temporal-coherence pair from the same device buffers.
 
 Both return exactly what a loop over ``check_revealed_leaves`` returns (``tests/test_gpu_validator.py``). Networking
 (the ``open_leaves`` RPC), scoring and weights stay the reference's. Nothing here raises: a malformed submission is a
@@ -20,6 +22,7 @@ import logging
 import random
 from typing import Dict, List, Optional, Sequence, Tuple
 
+import numpy as np
 import torch
 
 from . import ops, proof
@@ -100,59 +103,118 @@ def check_revealed_leaves(sub: Submission, request_id: Optional[str] = None, log
         return False
 
 
+def _frames_of(nbytes: int, cfg: Dict) -> int:
+    """Frame count of a leaf image under the reference's view rules (proof.py:321-343); raises where it would raise."""
+    chw = int(cfg["latent_channels"]) * int(cfg["latent_height"]) * int(cfg["latent_width"])
+    if nbytes % 2:
+        raise ValueError("buffer size must be a multiple of element size")
+    n = nbytes // 2
+    if n > chw:
+        if n % chw:
+            raise ValueError("leaf of %d elements is not a whole number of %d-element frames" % (n, chw))
+        return n // chw
+    if n != chw:
+        raise ValueError("leaf of %d elements is smaller than one %d-element frame" % (n, chw))
+    return 1
+
+
+def _decode_on_device(texts: List[bytes], dev) -> List[Optional[torch.Tensor]]:
+    """base64 texts -> device uint8 views of their bytes. Texts of equal length travel as one pinned matrix and are
+    decoded by ONE b2v_base64_decode_rows launch per length; rows the kernel flags as non-canonical (and lengths that
+    are not a multiple of 4) go through Python's permissive base64.b64decode, whose exceptions give None."""
+    out: List[Optional[torch.Tensor]] = [None] * len(texts)
+    by_len: Dict[int, List[int]] = {}
+    for i, t in enumerate(texts):
+        by_len.setdefault(len(t), []).append(i)
+    for chars, idxs in by_len.items():
+        if chars == 0 or chars % 4:
+            flagged = idxs
+        else:
+            stride = (chars + 15) // 16 * 16
+            host = proof._pinned(len(idxs) * stride)[:len(idxs) * stride].view(len(idxs), stride)
+            hv = host.numpy()
+            for r, i in enumerate(idxs):
+                hv[r, :chars] = np.frombuffer(texts[i], dtype=np.uint8)
+            txt = torch.empty((len(idxs), stride), dtype=torch.uint8, device=dev)
+            txt.copy_(host, non_blocking=True)
+            rows, status = ops.base64_decode_rows(txt, chars)
+            st = status.cpu().tolist()  # also orders the pinned buffer's reuse behind the copy
+            flagged = []
+            for r, i in enumerate(idxs):
+                if st[r] & 0x100:
+                    flagged.append(i)
+                else:
+                    out[i] = rows[r, :chars // 4 * 3 - (st[r] & 3)]
+        for i in flagged:
+            try:
+                out[i] = proof._to_dev_bytes(base64.b64decode(texts[i]), dev)
+            except Exception:
+                out[i] = None
+    return out
+
+
 def check_miners(subs: Sequence[Submission], request_id: Optional[str] = None, logger=None) -> List[bool]:
-    """Every miner of a round in a handful of launches; element i == check_revealed_leaves(subs[i])."""
+    """Every miner of a round in a handful of launches; element i == check_revealed_leaves(subs[i]). The revealed
+    leaves cross PCIe once, as the base64 text they arrived in, and are decoded, hashed and re-checked on the device."""
     logger = logger or LOG
     n = len(subs)
     ok = [True] * n
     dev = proof._device()
-    # ---- host pass: decode, collect ------------------------------------------------------------------------------
-    leaves = []   # (miner, t, z_bytes, eps_bytes, path, step, alphas, cfg)
-    meta = []
+
+    def fail(m, msg, *a):
+        logger.warning("[%s] miner %s: " + msg, request_id, subs[m].uid, *a)
+        ok[m] = False
+
+    # ---- host pass: structure only (which leaves, which steps); the payload stays text ------------------------------
+    leaves = []   # [m, t, z_text, eps_text, path, step]
+    meta: List[Tuple[Dict[int, int], List[float]]] = []
     for m, sub in enumerate(subs):
+        meta.append(({}, []))
         try:
             t2s = {int(ts): i for i, ts in enumerate(sub.timesteps)}
             alphas = sub.alphas or sub.unet_config["alphas"]
-            meta.append((t2s, alphas))
+            meta[m] = (t2s, alphas)
+            mine = []
             for t in sub.spot_check_indices:
                 leaf = sub.leaves_result.get(str(t))
                 if not leaf or len(leaf) != 3:
-                    logger.warning("[%s] missing or malformed leaf for t=%s from miner %s", request_id, t, sub.uid)
-                    ok[m] = False
+                    fail(m, "missing or malformed leaf for t=%s", t)
                     break
-                z, e = base64.b64decode(leaf[0]), base64.b64decode(leaf[1])
+                texts = [x.encode("ascii") if isinstance(x, str) else bytes(x) for x in (leaf[0], leaf[1])]
                 path = [base64.b64decode(p) for p in leaf[2]]
                 if not 0 <= int(t) < 65536:
                     raise OverflowError("int too big to convert")
                 step = t2s.get(t)
                 if step is None or step >= len(alphas):
-                    # the reference reaches this only after the Merkle check passed; either way the verdict is False
-                    logger.warning("[%s] invalid step index for t=%s: %s", request_id, t, step)
-                    ok[m] = False
+                    fail(m, "invalid step index for t=%s: %s", t, step)
                     break
-                leaves.append((m, int(t), z, e, path, step, alphas, sub.unet_config))
+                mine.append([m, int(t), texts[0], texts[1], path, step])
+            if ok[m]:
+                leaves += mine
         except Exception as ex:
-            logger.error("[%s] spot check of miner %s failed: %r", request_id, sub.uid, ex)
-            ok[m] = False
-            if len(meta) <= m:
-                meta.append(({}, []))
+            fail(m, "spot check failed: %r", ex)
+    leaves = [lf for lf in leaves if ok[lf[0]]]
+    # ---- decode on the device, validate the shapes from the lengths -------------------------------------------------
+    bufs = _decode_on_device([lf[2] for lf in leaves] + [lf[3] for lf in leaves], dev) if leaves else []
+    nl = len(leaves)
+    views: Dict[Tuple[int, int], Tuple[torch.Tensor, torch.Tensor, int]] = {}   # (miner, t) -> (z, eps, frames)
+    for i, lf in enumerate(leaves):
+        m, t = lf[0], lf[1]
+        z, e = bufs[i], bufs[nl + i]
+        try:
+            if z is None or e is None:
+                raise ValueError("base64 decode error")
+            if e.numel() != z.numel():
+                raise ValueError("eps and z byte lengths differ")
+            views[(m, t)] = (z, e, _frames_of(z.numel(), subs[m].unet_config))
+        except Exception as ex:
+            fail(m, "leaf t=%s rejected: %s", t, ex)
     live = [lf for lf in leaves if ok[lf[0]]]
-    # ---- leaf hashes: one pinned staging buffer, one copy, ONE launch ----------------------------------------------
     if live:
-        total = sum(len(lf[2]) + len(lf[3]) for lf in live)
-        host = proof._pinned(max(total, 1))[:total]
-        hv, off, spans = memoryview(host.numpy()), 0, []
-        for lf in live:
-            for b in (lf[2], lf[3]):
-                hv[off:off + len(b)] = b
-                spans.append((off, len(b)))
-                off += len(b)
-        blob = torch.empty(max(total, 1), dtype=torch.uint8, device=dev)
-        blob[:total].copy_(host, non_blocking=True)
-        zs = [blob[o:o + ln] for o, ln in spans[0::2]]
-        es = [blob[o:o + ln] for o, ln in spans[1::2]]
-        digests = ops.sha256_leaves(zs, es, [lf[1] for lf in live])              # [n,32], stays on the device
-        # ---- membership: every leaf of every miner against its own root, ONE launch per path depth ------------------
+        # ---- leaf hashes: ONE launch over every revealed leaf of every miner ----------------------------------------
+        digests = ops.sha256_leaves([views[(lf[0], lf[1])][0] for lf in live], [views[(lf[0], lf[1])][1] for lf in live],
+                                    [lf[1] for lf in live])
+        # ---- membership: leaf i against its own miner's root, ONE launch per path depth -----------------------------
         by_depth: Dict[int, List[int]] = {}
         odd: Dict[int, List[int]] = {}
         for i, lf in enumerate(live):
@@ -166,12 +228,10 @@ def check_miners(subs: Sequence[Submission], request_id: Optional[str] = None, l
             paths = proof._to_dev_bytes(pb, dev).reshape(len(idxs), depth, 32) if depth else \
                 torch.empty((len(idxs), 0, 32), dtype=torch.uint8, device=dev)
             roots = proof._to_dev_bytes(b"".join(subs[live[i][0]].merkle_root for i in idxs), dev).reshape(len(idxs), 32)
-            res = ops.merkle_verify_roots(digests.index_select(0, sel).contiguous(), paths, roots).cpu().numpy()
+            res = ops.merkle_verify_roots(digests.index_select(0, sel).contiguous(), paths, roots).cpu().tolist()
             for i, r in zip(idxs, res):
                 if not r:
-                    logger.warning("[%s] Merkle verification failed for miner %s at t=%s", request_id,
-                                   subs[live[i][0]].uid, live[i][1])
-                    ok[live[i][0]] = False
+                    fail(live[i][0], "Merkle verification failed at t=%s", live[i][1])
         if odd:
             host_digests = digests.cpu().numpy()
             for m, idxs in odd.items():
@@ -182,73 +242,52 @@ def check_miners(subs: Sequence[Submission], request_id: Optional[str] = None, l
                     logger.error("[%s] Merkle verification of miner %s failed: %r", request_id, subs[m].uid, ex)
                     res = [False]
                 if not all(res):
-                    logger.warning("[%s] Merkle verification failed for miner %s", request_id, subs[m].uid)
-                    ok[m] = False
-        # ---- run_unet_step verdicts: one launch per (scheduler length, latent shape) --------------------------------
-        groups: Dict[Tuple, List[int]] = {}
-        frames = {}
-        for i, lf in enumerate(live):
-            m, _, z, e, _, step, alphas, cfg = lf
-            if not ok[m]:
-                continue
-            try:
-                if len(e) != len(z):
-                    raise ValueError("eps and z byte lengths differ")
-                frames[i] = (proof._frame0_f16(z, cfg), proof._frame0_f16(e, cfg))
-                key = (len(alphas), int(cfg["latent_channels"]), int(cfg["latent_height"]), int(cfg["latent_width"]))
-                groups.setdefault(key, []).append(i)
-            except Exception as ex:
-                logger.error("[%s] Error running UNet step %s of miner %s: %s", request_id, step, subs[m].uid, ex)
-                ok[m] = False
-        for key, idxs in groups.items():
-            cfg = live[idxs[0]][7]
-            try:
-                flags = proof.spotcheck_flags([frames[i][0] for i in idxs], [frames[i][1] for i in idxs],
-                                              [None] * len(idxs), [live[i][5] % key[0] for i in idxs], key[0], cfg)
-            except Exception as ex:
-                logger.error("[%s] step verification launch failed: %r", request_id, ex)
-                flags = [0] * len(idxs)
-            for i, f in zip(idxs, flags):
-                if not (f & proof._FLAG_FINITE and f & proof._FLAG_BOUNDED):
-                    logger.warning("[%s] step verification failed for miner %s at t=%s", request_id, subs[live[i][0]].uid,
-                                   live[i][1])
-                    ok[live[i][0]] = False
-    # ---- temporal coherence: host plans for every miner, ONE launch per scheduler length, verdicts in order ---------
-    plans, cgroups = {}, {}
+                    fail(m, "Merkle verification failed")
+    # ---- DDIM re-checks on the device-resident leaves: run_unet_step for every leaf and the temporal-coherence pairs
+    #      of every miner, ONE launch per (scheduler length, latent shape, frame count) -------------------------------
+    jobs: Dict[Tuple, List[Tuple]] = {}   # key -> [(miner, kind, z, eps, z_next|None, step, label)]
+    for lf in live:
+        m, t, step = lf[0], lf[1], lf[5]
+        if not ok[m]:
+            continue
+        z, e, F = views[(m, t)]
+        cfg, alphas = subs[m].unet_config, meta[m][1]
+        key = (len(alphas), int(cfg["latent_channels"]), int(cfg["latent_height"]), int(cfg["latent_width"]), F)
+        jobs.setdefault(key, []).append((m, "step", z, e, None, step, t))
     for m, sub in enumerate(subs):
-        if len(sub.spot_check_indices) < 2:
+        if not ok[m] or len(sub.spot_check_indices) < 2:
             continue
         t2s, alphas = meta[m]
-        try:
-            plan = proof._coherence_plan(sub.spot_check_indices, sub.leaves_result, t2s, alphas, sub.unet_config,
-                                         request_id, logger)
-        except Exception as ex:
-            logger.error("[%s] temporal coherence of miner %s failed: %r", request_id, sub.uid, ex)
-            ok[m] = False
-            continue
-        if plan[0] is not None:
-            ok[m] = ok[m] and plan[0]
-            continue
-        plans[m] = plan
         cfg = sub.unet_config
-        key = (len(alphas), int(cfg["latent_channels"]), int(cfg["latent_height"]), int(cfg["latent_width"]))
-        cgroups.setdefault(key, []).append(m)
-    for key, ms in cgroups.items():
-        zs, es, zn, steps, owner = [], [], [], [], []
-        for m in ms:
-            _, a, b, c, st, _, _ = plans[m]
-            zs += a; es += b; zn += c; steps += st
-            owner += [m] * len(a)
+        order = list(sub.spot_check_indices)        # every requested leaf is present and well formed here
+        if len(order) > len(alphas):
+            order = order[:len(alphas)]
+        for t_i, t_j in zip(order[:-1], order[1:]):
+            (z, e, F), (zj, _, Fj) = views[(m, t_i)], views[(m, t_j)]
+            if Fj != F:
+                # frame 0 of differently shaped leaves: outside the batched kernel's layout; the per-miner routine decides
+                if not proof.verify_temporal_coherence_spot_check(sub.spot_check_indices, sub.leaves_result, t2s, alphas,
+                                                                  cfg, request_id, logger):
+                    fail(m, "temporal coherence check failed")
+                break
+            key = (len(alphas), int(cfg["latent_channels"]), int(cfg["latent_height"]), int(cfg["latent_width"]), F)
+            jobs.setdefault(key, []).append((m, "pair", z, e, zj, t2s[t_i], (t_i, t_j)))
+    for key, items in jobs.items():
+        n_steps, C_, H_, W_, F = key
         try:
-            flags = proof.spotcheck_flags(zs, es, zn, steps, key[0], subs[ms[0]].unet_config) if zs else []
+            sched = proof._default_scheduler(n_steps)
+            ts = sched.host_timesteps()
+            pairs = [sched.alpha_pair(ts[it[5]]) for it in items]
+            flags = ops.spotcheck_ddim([it[2] for it in items], [it[3] for it in items],
+                                       [it[4] if it[4] is not None else it[2] for it in items],
+                                       [p[0] for p in pairs], [p[1] for p in pairs], C_, F, H_ * W_).cpu().tolist()
         except Exception as ex:
-            logger.error("[%s] temporal coherence launch failed: %r", request_id, ex)
-            for m in ms:
-                ok[m] = False
-            continue
-        for m in ms:
-            mine = [f for f, o in zip(flags, owner) if o == m]
-            if not proof._coherence_verdict(mine, plans[m][5], plans[m][6], request_id, logger):
-                logger.warning("[%s] temporal coherence check failed for miner %s", request_id, subs[m].uid)
-                ok[m] = False
+            logger.error("[%s] DDIM re-check launch failed: %r", request_id, ex)
+            flags = [0] * len(items)
+        for it, f in zip(items, flags):
+            if it[1] == "step":
+                if not (f & proof._FLAG_FINITE and f & proof._FLAG_BOUNDED):
+                    fail(it[0], "step verification failed at t=%s", it[6])
+            elif not f & proof._FLAG_CLOSE:
+                fail(it[0], "cross-step check failed between t=%s and t=%s", *it[6])
     return ok

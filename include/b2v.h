@@ -142,6 +142,13 @@ int b2v_blend_overlap(const void* const* chunk_ptrs_host, const int* starts_host
 uint64_t b2v_base64_len(uint64_t nbytes);
 int b2v_base64_rows(const void* src_dev, int64_t n_rows, uint64_t row_bytes, uint64_t row_stride,
                     void* dst_dev, void* stream);
+/* The validator's side (neurons/validator.py:783-786 `base64.b64decode(z_b)` per revealed leaf): n_rows rows of
+ * row_chars characters (a multiple of 4; row i at src_dev + i*row_stride) -> bytes at dst_dev + i*dst_stride
+ * (3*row_chars/4 bytes written, padded positions as zero). status_dev[i] = number of '=' padding characters (0..2),
+ * | 0x100 when the row is not canonical base64 (character outside the alphabet, '=' before the end): Python's
+ * permissive decoder skips such characters, so the caller decodes those rows on the host to keep its semantics. */
+int b2v_base64_decode_rows(const void* src_dev, int64_t n_rows, uint64_t row_chars, uint64_t row_stride,
+                           void* dst_dev, uint64_t dst_stride, int* status_dev, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * UNet3DConditionModel forward  ([UPSTREAM diffusers] pipe.unet(x, t, encoder_hidden_states=emb).sample,

@@ -146,3 +146,49 @@ def test_merkle_verify_roots_many_trees(cuda):
     ok = ops.merkle_verify_roots(lh, pt, rt).cpu().tolist()
     want = [int(M.verify_merkle_leaf(trees[k][0][i], trees[k][1][i], roots[j])) for j, (k, i) in enumerate(rows)]
     assert ok == want and want.count(0) == 1 and want[4] == 0
+
+
+@pytest.mark.parametrize("nbytes", [0, 1, 2, 3, 4, 11, 12, 13, 47, 48, 1000, 3 * 4096 + 1, 1769472])
+def test_base64_decode_rows_bit_exact(cuda, nbytes):
+    """b2v_base64_decode_rows == base64.b64decode on canonical text, every byte, with the pad count reported."""
+    import base64
+    import numpy as np
+    from b2v import ops
+    rng = np.random.default_rng(nbytes)
+    rows = [rng.integers(0, 256, nbytes, dtype=np.uint8).tobytes() for _ in range(3)]
+    txt = [base64.b64encode(r) for r in rows]
+    chars = len(txt[0])
+    stride = max(16, (chars + 15) // 16 * 16)
+    host = np.zeros((3, stride), dtype=np.uint8)
+    for i, t in enumerate(txt):
+        host[i, :chars] = np.frombuffer(t, dtype=np.uint8)
+    out, status = ops.base64_decode_rows(torch.from_numpy(host).to(cuda), chars)
+    st = status.cpu().tolist()
+    assert st == [(3 - nbytes % 3) % 3] * 3
+    o = out.cpu().numpy()
+    for i, r in enumerate(rows):
+        assert o[i, :nbytes].tobytes() == r == base64.b64decode(txt[i])
+
+
+def test_base64_decode_flags_non_canonical_rows(cuda):
+    """Rows Python's permissive decoder would treat specially (foreign characters, '=' before the end) are flagged
+    0x100 and left to the host routine; trailing bits of a padded quad are ignored like binascii does."""
+    import numpy as np
+    from b2v import ops
+    texts = [b"QUJDRA==", b"QUJD\nA==", b"QU=DRA==", b"QUJDRB==", b"QUJDR===", b"QUJDRE-G", b"QUJDREVG"]
+    host = np.zeros((len(texts), 16), dtype=np.uint8)
+    for i, t in enumerate(texts):
+        host[i, :8] = np.frombuffer(t, dtype=np.uint8)
+    out, status = ops.base64_decode_rows(torch.from_numpy(host).to(cuda), 8)
+    st = status.cpu().tolist()
+    assert st[0] == 2 and st[3] == 2 and st[6] == 0
+    assert all(st[i] & 0x100 for i in (1, 2, 4, 5))
+    o = out.cpu().numpy()
+    assert o[0, :4].tobytes() == b"ABCD" and o[3, :4].tobytes() == b"ABCD" and o[6, :6].tobytes() == b"ABCDEF"
+    # unaligned source rows take the byte path
+    big = torch.from_numpy(np.frombuffer(b"x" + b"QUJDREVG" * 5, dtype=np.uint8).copy()).to(cuda)
+    from b2v._lib import check, load
+    dst = torch.zeros(32, dtype=torch.uint8, device=cuda)
+    stt = torch.zeros(1, dtype=torch.int32, device=cuda)
+    check(load().b2v_base64_decode_rows(big.data_ptr() + 1, 1, 40, 40, ops.ptr(dst), 32, ops.ptr(stt), ops.stream()))
+    assert dst[:30].cpu().numpy().tobytes() == b"ABCDEF" * 5 and int(stt[0]) == 0
