@@ -11,6 +11,7 @@ Layout
   pipeline.py      pipe-shaped object (unet, scheduler, synthetic text encoder)
   planner.py       chunk planner / blend weights (host integer logic of chunk_only.py:80-105, 136-150)
   strategies/      chunk_only / fsdp_chunked_coherent / fsdp_chunked / fsdp entry points (same CLI + CSV)
+  validator.py     spot-check round over many miners (validator.py:641-845): text in, four launches
   proof.py         derive_seed, build_merkle_root, verify_merkle_leaf, run_unet_step, ... (same signatures)
 
 There is no CPU fallback: compute entry points raise when libb2v.so or an sm_100 device is missing.
@@ -19,4 +20,4 @@ The directory name is not a Python identifier; ``import b2v`` (repo-root shim) a
 from . import _lib  # noqa: F401
 from ._lib import B2VError, EXPORTED_SYMBOLS  # noqa: F401
 
-__all__ = ["_lib", "ops", "scheduler", "unet", "vae", "pipeline", "planner", "proof", "strategies", "B2VError"]
+__all__ = ["_lib", "ops", "scheduler", "unet", "vae", "pipeline", "planner", "proof", "validator", "miner", "exchange", "strategies", "B2VError"]
