@@ -120,3 +120,122 @@ def nccl_all_gather(my_windows, plan, rank, world, device):
             out.append((s, e, recv[r, :, off:off + (e - s)].unsqueeze(0).contiguous()))
             off += e - s
     return out, dt
+
+
+# ---- per-step halo exchange ---------------------------------------------------------------
+def halo_neighbours(plan, world):
+    """Global window order and, for every window, its overlap (in frames) with the previous / next window.
+    Returns (windows, halos): windows = [(s, e, rank, index on that rank)] sorted by start; halos[i] = (ov_left, ov_right).
+    Raises ValueError when a frame is covered by more than two windows or two windows share a start (padded plans):
+    the per-step exchange is defined between adjacent windows only."""
+    wins = sorted(((s, e, r, j) for r in range(world) for j, (s, e) in enumerate(plan.of_rank(r))), key=lambda x: (x[0], x[1]))
+    for a, b in zip(wins[:-1], wins[1:]):
+        if b[0] <= a[0] or b[1] <= a[1]:
+            raise ValueError("halo exchange needs strictly advancing windows, got %r then %r" % (a[:2], b[:2]))
+    for a, c in zip(wins[:-2], wins[2:]):
+        if c[0] < a[1]:
+            raise ValueError("halo exchange needs at most two windows per frame, %r and %r overlap" % (a[:2], c[:2]))
+    halos = []
+    for i, wdw in enumerate(wins):
+        left = max(0, wins[i - 1][1] - wdw[0]) if i > 0 else 0
+        right = max(0, wdw[1] - wins[i + 1][0]) if i + 1 < len(wins) else 0
+        halos.append((left, right))
+    return wins, halos
+
+
+def crossfade(ov):
+    """Partition-of-unity weights over an overlap of `ov` frames: (earlier window's, later window's), fp32; the later
+    window's weight of overlap frame k is (k + 0.5) / ov, the earlier one's is 1 minus that — computed once so both
+    sides multiply by identical numbers."""
+    later = torch.tensor([(k + 0.5) / ov for k in range(ov)], dtype=torch.float32)
+    return (1.0 - later), later
+
+
+class HaloSync:
+    """After EVERY denoising step adjacent windows exchange their overlapping frames and both replace them with the same
+    crossfade, so the windows evolve as one video instead of drifting apart until the final blend (the reference's
+    windows never talk during the loop: this is the N4 variant, opt-in, with its own single-process oracle).
+
+    Each rank publishes the first / last halo frames of its windows into a peer-mapped buffer (two parity slots, one
+    device-side barrier per step); the blend kernel then reads the NEIGHBOUR's published frames straight out of its
+    HBM over NVLink together with the local window: exchange and crossfade are one kernel, as in PeerWindows.
+    world == 1 uses a plain device buffer and no barrier. Chunks are always accumulated earlier-window-first, so the
+    two owners of an overlap frame compute bit-identical values."""
+
+    def __init__(self, plan, world, rank, C_, h, w, dtype, device, group=None):
+        self.world, self.rank, self.device, self.dtype = world, rank, device, dtype
+        self.C, self.h, self.w = C_, h, w
+        self.itemsize = torch.empty((), dtype=dtype).element_size()
+        self.wins, self.halos = halo_neighbours(plan, world)
+        self.n_local = [len(plan.of_rank(r)) for r in range(world)]
+        ov_max = max([max(l, r) for l, r in self.halos] + [1])
+        self.slot = (C_ * ov_max * h * w * self.itemsize + 255) // 256 * 256
+        cap = 2 * 2 * max(self.n_local) * self.slot                       # parity x (head, tail) x windows
+        if world > 1:
+            import torch.distributed._symmetric_memory as symm_mem
+            self.buf = symm_mem.empty(cap, dtype=torch.uint8, device=device)
+            self.hdl = symm_mem.rendezvous(self.buf, group if group is not None else dist.group.WORLD)
+            self.base_ptrs = [int(p) for p in self.hdl.buffer_ptrs]
+            if len(self.base_ptrs) != world or any(p == 0 for p in self.base_ptrs):
+                raise RuntimeError("peer mapping failed: %r" % (self.base_ptrs,))
+        else:
+            self.buf, self.hdl = torch.empty(cap, dtype=torch.uint8, device=device), None
+            self.base_ptrs = [self.buf.data_ptr()]
+        self.mine = [i for i, wdw in enumerate(self.wins) if wdw[2] == rank]  # global indices of my windows, by start
+        self.mine.sort(key=lambda i: self.wins[i][3])                       # ... in this rank's own window order
+        self.step = 0
+
+    def _offset(self, parity, j, side):
+        return ((parity * max(self.n_local) + j) * 2 + side) * self.slot
+
+    def _slot_view(self, parity, j, side, ov):
+        off = self._offset(parity, j, side)
+        n = self.C * ov * self.h * self.w * self.itemsize
+        return self.buf[off:off + n].view(self.dtype).view(self.C, ov, self.h, self.w)
+
+    def sync(self, lats):
+        """lats: this rank's window latents [1,C,len,h,w] (the rank's window order). Returns the synchronised latents."""
+        from . import ops
+        parity = self.step & 1
+        for gi, lat in zip(self.mine, lats):
+            (s, e, _, j), (ovl, ovr) = self.wins[gi], self.halos[gi]
+            if lat.shape[2] != e - s or lat.dtype != self.dtype:
+                raise ValueError("window %r: latent %s does not match the plan" % ((s, e), tuple(lat.shape)))
+            if ovl:
+                self._slot_view(parity, j, 0, ovl).copy_(lat[0, :, :ovl])
+            if ovr:
+                self._slot_view(parity, j, 1, ovr).copy_(lat[0, :, e - s - ovr:])
+        if self.hdl is not None:
+            self.hdl.barrier(channel=parity)      # every rank's halo frames of this step are published
+        out = []
+        for gi, lat in zip(self.mine, lats):
+            (s, e, _, _), (ovl, ovr) = self.wins[gi], self.halos[gi]
+            n = e - s
+            own_w = torch.ones(n, dtype=torch.float32)
+            ptrs, ranges, weights = [], [], []
+            if ovl:
+                _, _, lr, lj = self.wins[gi - 1]
+                earlier, later = crossfade(ovl)
+                ptrs.append(self.base_ptrs[lr] + self._offset(parity, lj, 1))      # the left window's published tail
+                ranges.append((0, ovl))
+                weights.append(earlier)
+                own_w[:ovl] = later
+            ptrs.append(lat.data_ptr())
+            ranges.append((0, n))
+            if ovr:
+                earlier, later = crossfade(ovr)
+                own_w[n - ovr:] = earlier
+            weights.append(own_w)
+            if ovr:
+                _, _, rr, rj = self.wins[gi + 1]
+                ptrs.append(self.base_ptrs[rr] + self._offset(parity, rj, 0))      # the right window's published head
+                ranges.append((n - ovr, n))
+                weights.append(later)
+            if len(ptrs) == 1:
+                out.append(lat)
+                continue
+            _, full = ops.blend_overlap_ptrs(ptrs, ranges, weights, n, self.C, self.h, self.w, self.dtype, self.device,
+                                             return_full=True)
+            out.append(full)
+        self.step += 1
+        return out

@@ -50,6 +50,10 @@ def add_common_args(p, num_frames=32, out_csv="benchmarks.csv", chunking=True):
     p.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                    help="end-of-denoise window exchange: p2p = blend kernel reads the peers' windows over NVLink "
                         "(fused exchange + blend), nccl = all_gather then blend")
+    p.add_argument("--halo_sync", action="store_true",
+                   help="per-step halo exchange (not in the reference): after every DDIM step adjacent windows swap "
+                        "their overlapping frames over NVLink and adopt the same crossfade, so windows evolve as one "
+                        "video; needs a plan where at most two windows cover a frame")
     p.add_argument("--decode", action="store_true",
                    help="decode the blended latents to frames on rank 0 (b2v.vae, random-init SD VAE decoder) and write "
                         "the mp4 + boundary metrics like the reference; off by default because the frames of a "
@@ -110,6 +114,27 @@ class CudaDenoiser:
                 self.on_step(i, t, lat, eps2)
             lat, x = sched.fused_cfg_step(lat, eps2, t, self.gs, ctx=self.ctx, ctx_w=self.ctx_w, n_dup=n_dup, xnext=x)
         return lat
+
+
+    def lockstep(self, lats, halo, on_sync=None):
+        """all of this rank's windows advance one DDIM step at a time; after every step the windows
+        (here and on the peer GPUs) exchange their overlapping frames and adopt the common crossfade
+        (exchange.HaloSync), then the next UNet inputs are rebuilt from the synchronised latents."""
+        sched, unet = self.pipe.scheduler, self.pipe.unet
+        n_dup = 2 if self.gs is not None else 1
+        xs = [ops.make_unet_input(lat, n_dup, ctx=self.ctx, ctx_w=self.ctx_w) for lat in lats]
+        eps = [torch.empty_like(x) for x in xs]
+        for i, t in enumerate(sched.host_timesteps()):
+            for k in range(len(lats)):
+                unet.forward_into(xs[k], t, self.emb, eps[k])
+                self.unet_forwards += 1
+                lats[k], _ = sched.fused_cfg_step(lats[k], eps[k], t, self.gs, ctx=self.ctx, ctx_w=self.ctx_w, n_dup=n_dup,
+                                                  xnext=xs[k])
+            lats = halo.sync(lats)
+            if on_sync is not None:
+                on_sync(i, t, lats)
+            xs = [ops.make_unet_input(lat, n_dup, ctx=self.ctx, ctx_w=self.ctx_w) for lat in lats]
+        return lats
 
 
 def exchange_windows(my_windows, plan, rank, world, device):
@@ -233,12 +258,29 @@ class WindowedDiffuser:
 
     # ---- the run ------------------------------------------------------------------------------------------
     def denoise_my_windows(self, plan, base):
+        if getattr(self.cfg, "halo_sync", False) and self._denoise_fn is None:
+            return self.denoise_my_windows_lockstep(plan, base)
         out = []
         for s, e in plan.of_rank(self.rank):
             chunk = base[:, :, s:e].clone()
             with torch.no_grad():
                 out.append((s, e, self._denoise(chunk)))
         return out
+
+    def denoise_my_windows_lockstep(self, plan, base, on_sync=None):
+        """--halo_sync (N4): per-step halo exchange between adjacent windows instead of independent windows."""
+        ranges = plan.of_rank(self.rank)
+        lats = [base[:, :, s:e].clone() for s, e in ranges]
+        if getattr(self, "_halo", None) is None:
+            self._halo = exchange.HaloSync(plan, self.world, self.rank, base.shape[1], base.shape[3], base.shape[4],
+                                           base.dtype, self.device)
+        self._halo.step = 0
+        if getattr(self, "_cuda_denoiser", None) is None:
+            self._cuda_denoiser = CudaDenoiser(self.pipe, self.uncond_emb, self.cond_emb, self.guidance_scale,
+                                               ctx=self.ctx, context_weight=self.context_weight if self.use_ctx else 0.0)
+        with torch.no_grad():
+            lats = self._cuda_denoiser.lockstep(lats, self._halo, on_sync=on_sync)
+        return [(s, e, lat) for (s, e), lat in zip(ranges, lats)]
 
     def __call__(self):
         cfg = self.cfg

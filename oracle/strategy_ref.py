@@ -147,3 +147,47 @@ def run_strategy(unet, sched, base, uncond_emb, cond_emb, world, guidance_scale=
         gathered.append(mine)
     lat, full, weight = blend(gathered, T, ov, base)
     return dict(lat=lat, full=full, weight=weight, chunks=gathered, ranges=ranges, cs=cs, ov=ov, ctx=ctx)
+
+
+# ---------------------------------------------------------------------------------------------------------------
+# Per-step halo exchange variant. NOT in the reference (its windows never communicate during
+# the loop; the idea is sketched in Distribution/legacy/Latent Chunking/precond_overlap/run_worker.py:165-173): this is
+# the single-process statement of the algorithm that b2v's --halo_sync runs across GPUs, so the two can be compared.
+# ---------------------------------------------------------------------------------------------------------------
+def halo_sync(lats, ranges):
+    """Adjacent windows (sorted by start, at most two per frame) replace their overlapping frames by the same
+    crossfade: later window's weight of overlap frame k = (k + 0.5) / ov, earlier window's = 1 - that."""
+    order = sorted(range(len(ranges)), key=lambda i: ranges[i])
+    out = [l.clone() for l in lats]
+    for a, b in zip(order[:-1], order[1:]):
+        ov = ranges[a][1] - ranges[b][0]
+        if ov <= 0:
+            continue
+        later = torch.tensor([(k + 0.5) / ov for k in range(ov)], dtype=torch.float32).view(1, 1, ov, 1, 1)
+        la = ranges[a][1] - ranges[a][0]
+        mix = (1.0 - later) * lats[a][:, :, la - ov:].float() + later * lats[b][:, :, :ov].float()
+        out[a][:, :, la - ov:] = mix.to(lats[a].dtype)
+        out[b][:, :, :ov] = mix.to(lats[b].dtype)
+    return out
+
+
+def denoise_halo_sync(unet, sched, base, ranges, uncond_emb, cond_emb, guidance_scale, ctx=None, context_weight=0.35,
+                      record=None):
+    """All windows in lockstep: one DDIM step each (as `denoise`), then `halo_sync`. Returns the windows' latents.
+    `record(step, t, [latents after the sync])`."""
+    emb = torch.cat([uncond_emb, cond_emb], 0)
+    lats = [base[:, :, s:e].clone() for s, e in ranges]
+    for i, t in enumerate(sched.timesteps):
+        nxt = []
+        for lat in lats:
+            x = sched.scale_model_input(torch.cat([lat] * 2), t)
+            if ctx is not None:
+                x = x + context_weight * ctx.repeat(1, 1, lat.shape[2], 1, 1)
+            with torch.no_grad():
+                noise = unet(x, t, emb)
+            u, c = noise.chunk(2)
+            nxt.append(sched.step(u + guidance_scale * (c - u), t, lat).prev_sample)
+        lats = halo_sync(nxt, ranges)
+        if record is not None:
+            record(i, int(t), lats)
+    return lats
