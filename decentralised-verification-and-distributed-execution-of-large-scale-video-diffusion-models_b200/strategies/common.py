@@ -167,7 +167,7 @@ def append_csv(path, row):
 
 def finish_row(res, mode, num_frames, t0):
     elapsed = time.time() - t0
-    res.update({"timestamp": datetime.datetime.utcnow().isoformat(timespec="seconds"), "host": socket.gethostname(),
+    res.update({"timestamp": datetime.datetime.now(datetime.timezone.utc).replace(tzinfo=None).isoformat(timespec="seconds"), "host": socket.gethostname(),
                 "mode": mode, "latency_s": elapsed, "throughput_fps": round(num_frames / elapsed, 3)})
     return res
 

@@ -189,3 +189,45 @@ def test_select_spot_check_pairs_matches_oracle():
     a = select_spot_check_pairs(ts, 5)   # default generator = the global `random`, as in the reference
     random.seed(3)
     assert a == VR.select_pairs(ts, 5)
+
+
+def test_halo_neighbours_and_crossfade_host_logic():
+    """SURVEY.md §8f N4 host side: window adjacency of the BASELINE plans, the crossfade is a partition of unity, plans
+    the exchange is not defined for are rejected."""
+    import pytest
+    import torch
+    from b2v import exchange, planner
+    wins, halos = exchange.halo_neighbours(planner.plan(24, 2, 0, 4, variant="chunk_only"), 2)
+    assert wins == [(0, 16, 0, 0), (12, 24, 1, 0)] and halos == [(0, 4), (4, 0)]
+    wins, halos = exchange.halo_neighbours(planner.plan(96, 8, 0, 4, variant="chunk_only"), 8)
+    assert [w[:2] for w in wins] == [(12 * k, min(12 * k + 16, 96)) for k in range(8)]
+    assert halos == [(0, 4)] + [(4, 4)] * 6 + [(4, 0)]
+    wins, halos = exchange.halo_neighbours(planner.plan(16, 2, 6, 2, variant="chunk_only"), 2)
+    assert [w[2] for w in wins] == [0, 1, 0, 1]          # neighbours live on the other rank
+    for ov in (1, 2, 3, 4, 7):
+        a, b = exchange.crossfade(ov)
+        assert a.dtype == torch.float32 and torch.equal(a + b, torch.ones(ov)) and bool((b[1:] > b[:-1]).all() if ov > 1 else True)
+        assert torch.equal(a, b.flip(0)) or ov in (3, 7)  # symmetric whenever the weights are exact in fp32
+    with pytest.raises(ValueError):
+        exchange.halo_neighbours(planner.plan(24, 4, 0, 4, variant="coherent"), 4)   # three windows per frame
+    with pytest.raises(ValueError):
+        exchange.halo_neighbours(planner.plan(24, 1, 10, 3, variant="chunk_only"), 1)  # tail window inside its neighbour
+
+
+def test_oracle_halo_sync_properties():
+    """oracle/strategy_ref.halo_sync: constant latents stay constant (weights sum to one), both owners of an overlap
+    frame agree, frames outside overlaps are untouched."""
+    import torch
+    from oracle import strategy_ref as S
+    ranges = [(0, 6), (4, 10), (8, 12)]
+    g = torch.Generator().manual_seed(0)
+    lats = [torch.randn(1, 4, e - s, 3, 5, generator=g) for s, e in ranges]
+    out = S.halo_sync(lats, ranges)
+    assert torch.equal(out[0][:, :, 4:], out[1][:, :, :2]) and torch.equal(out[1][:, :, 4:], out[2][:, :, :2])
+    assert torch.equal(out[0][:, :, :4], lats[0][:, :, :4]) and torch.equal(out[1][:, :, 2:4], lats[1][:, :, 2:4])
+    ones = [torch.full_like(l, 3.0) for l in lats]
+    assert all(torch.allclose(o, torch.full_like(o, 3.0), atol=1e-6) for o in S.halo_sync(ones, ranges))
+    # rank order of the list does not matter (windows are matched by their ranges)
+    perm = [2, 0, 1]
+    out_p = S.halo_sync([lats[i] for i in perm], [ranges[i] for i in perm])
+    assert all(torch.equal(out_p[k], out[i]) for k, i in enumerate(perm))
