@@ -67,6 +67,24 @@ class Trajectory:
                 "latents": zs, "noise_preds": es, "alphas": list(self.alphas), "leaf_data": leaf_b64}
 
 
+def decode_final_frames(pipe, z, reference_view=True):
+    """InferNet/neurons/miner.py:593-600: the final latents [B,C,T,h,w] -> ``pipe.vae.decode(flat / scaling).sample``
+    over all B*T frames at once -> numpy [T,H,W,3] in the decoder's [-1,1] range (the array ``export_to_video`` gets).
+
+    Reference quirk, reproduced by default because the video bytes enter the signed message (proof.py:56-58):
+    ``flat = z.view(B*T, C, H, W)`` REINTERPRETS the channel-major memory of [B,C,T,h,w] as T images — image i is made of
+    4 consecutive (channel, frame) planes, not of frame i's 4 channels. ``reference_view=False`` decodes the actual
+    frames (``z.permute(0,2,1,3,4)``). ``pipe.vae`` is b2v.vae.AutoencoderKL (or anything with that call surface)."""
+    B, Cc, T, H, W = z.shape
+    if reference_view:
+        flat = z.contiguous().view(B * T, Cc, H, W)
+    else:
+        flat = z.permute(0, 2, 1, 3, 4).reshape(B * T, Cc, H, W)
+    decoded = pipe.vae.decode(flat / pipe.vae.config.scaling_factor).sample
+    decoded = decoded.view(B, T, *decoded.shape[-3:])
+    return decoded[0].permute(0, 2, 3, 1).float().cpu().numpy()
+
+
 def leaves_b64(tensors) -> List[str]:
     """``[base64.b64encode(t.cpu().numpy().tobytes()).decode('ascii') for t in tensors]`` (miner.py:655-656) with the
     encoding done on the device: equally sized tensors that sit back to back in one buffer (the trajectory buffers of

@@ -125,3 +125,28 @@ def test_reexecution_spot_check(cuda):
     rev_b = dict(revealed); rev_b[t0] = (bytes(zb), revealed[t0][1], revealed[t0][2])
     rep_b = miner.reexecute_spot_check(pipe, e_dev, rev_b, root, traj.timesteps, shape, steps)
     assert not rep_b["ok"] and not rep_b["leaves"][t0]["member"]
+
+
+def test_decode_final_frames_reference_view(cuda):
+    """miner.py:593-600: final latents -> frames through pipe.vae, with the reference's `z.view(B*T, C, H, W)` memory
+    reinterpretation (default) and with true frames; against the fp32 oracle decoder, rel-l2 <= 2.5e-2."""
+    from types import SimpleNamespace
+    from b2v import miner
+    from b2v.vae import AutoencoderKL
+    from oracle import vae_ref as V
+    from oracle.unet3d_ref import random_init_
+    ref = random_init_(V.AutoencoderKLDecoder(V.TINY), seed=9, round_bf16=True).eval()
+    vae = AutoencoderKL(V.TINY.to_dict(), device=cuda).load_state_dict(ref.state_dict())
+    pipe = SimpleNamespace(vae=vae)
+    z = torch.randn(1, 4, 3, 8, 8, generator=torch.Generator().manual_seed(1)) * 0.4
+    for ref_view in (True, False):
+        got = miner.decode_final_frames(pipe, z.to(cuda), reference_view=ref_view)
+        flat = z.view(3, 4, 8, 8) if ref_view else z.permute(0, 2, 1, 3, 4).reshape(3, 4, 8, 8)
+        with torch.no_grad():
+            want = ref.decode(flat / 0.18215).permute(0, 2, 3, 1)
+        assert got.shape == (3, 64, 64, 3)
+        rel = float((torch.from_numpy(got) - want).norm() / want.norm())
+        assert rel <= 2.5e-2, rel
+    a = miner.decode_final_frames(pipe, z.to(cuda))
+    b = miner.decode_final_frames(pipe, z.to(cuda), reference_view=False)
+    assert not (a == b).all()  # the quirk is real: the two readings are different videos
