@@ -1,4 +1,4 @@
-"""GPU box: error budget of the bf16 UNet path vs the fp32 CPU oracle on the TINY config: single forward, guided eps,
+"""Test infrastructure (lives under tests/ because it runs the oracle). GPU box: error budget of the bf16 UNet path vs the fp32 CPU oracle on the TINY config: single forward, guided eps,
 per-step latents for several guidance scales. Prints numbers used to state the tolerances in tests/."""
 import sys
 import torch

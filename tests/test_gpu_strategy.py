@@ -126,7 +126,7 @@ def _cfg(**kw):
     return argparse.Namespace(**d)
 
 
-# Tolerance (measured, tools/err_budget.py, recorded in DESIGN.md "Parity"): one bf16 UNet forward is within
+# Tolerance (measured, tests/err_budget.py, recorded in DESIGN.md "Parity"): one bf16 UNet forward is within
 # 1.0-1.6e-2 relative L2 of the fp32 oracle (8-bit mantissa, ~150 sequential roundings; cosine >= 0.9998).
 # Classifier-free guidance forms u + gs (c - u) with |c - u| ~ 0.1-0.3 |u|, which amplifies that noise by ~gs/2:
 # gs = 7.5 -> guided eps 6.5e-2, per-step latents 4.2-4.6e-2 (flat over steps: DDIM contracts it, 3.6e-2 at step 25);

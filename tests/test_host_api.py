@@ -231,3 +231,19 @@ def test_oracle_halo_sync_properties():
     perm = [2, 0, 1]
     out_p = S.halo_sync([lats[i] for i in perm], [ranges[i] for i in perm])
     assert all(torch.equal(out_p[k], out[i]) for k, i in enumerate(perm))
+
+
+def test_only_test_infrastructure_touches_the_oracle():
+    """The oracle is the checker, never the product: nothing in the package or in tools/ imports it (bench.py's CPU
+    baseline legs, __graft_entry__.smoke() and tests/ are the only users)."""
+    import re
+    pkg = os.path.dirname(os.path.abspath(__import__("b2v").__file__))
+    roots = [pkg, os.path.join(ROOT, "tools")]
+    pat = re.compile(r"^\s*(from\s+oracle|import\s+oracle)", re.M)
+    bad = []
+    for r in roots:
+        for d, _, files in os.walk(r):
+            for f in files:
+                if f.endswith(".py") and pat.search(open(os.path.join(d, f)).read()):
+                    bad.append(os.path.join(d, f))
+    assert not bad, bad

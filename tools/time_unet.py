@@ -1,6 +1,5 @@
 """GPU box: time one full-size Zeroscope UNet3D forward and print a per-kernel breakdown (torch.profiler / CUPTI).
 usage: python tools/time_unet.py [B F H W] [--profile]"""
-import math
 import sys
 import time
 
@@ -9,22 +8,8 @@ import torch
 sys.path.insert(0, ".")
 import b2v  # noqa: E402
 from b2v.unet import UNet3DConditionModel  # noqa: E402
-from oracle import unet3d_ref as R  # shapes only (meta device); no oracle compute  # noqa: E402
-
-
-def random_state_dict(cfg, device, seed=1234):
-    with torch.device("meta"):
-        m = R.UNet3DConditionModel(cfg)
-    g = torch.Generator(device=device).manual_seed(seed)
-    sd = {}
-    for name, p in m.state_dict().items():
-        if p.ndim == 1:
-            v = (1.0 + 0.1 * torch.randn(p.shape, device=device, generator=g)) if name.endswith("weight") \
-                else 0.05 * torch.randn(p.shape, device=device, generator=g)
-        else:
-            v = torch.randn(p.shape, device=device, generator=g) / math.sqrt(p[0].numel())
-        sd[name] = v
-    return sd
+from b2v.pipeline import random_state_dict  # noqa: E402
+from b2v.unet import ZEROSCOPE_CONFIG  # noqa: E402
 
 
 def main():
@@ -32,8 +17,8 @@ def main():
     B, F, H, W = (int(a) for a in args) if len(args) == 4 else (2, 16, 72, 128)
     dev = torch.device("cuda:0")
     t0 = time.time()
-    net = UNet3DConditionModel(R.ZEROSCOPE.to_dict(), device=dev)
-    net.load_state_dict(random_state_dict(R.ZEROSCOPE, dev))
+    net = UNet3DConditionModel(ZEROSCOPE_CONFIG, device=dev)
+    net.load_state_dict(random_state_dict(net.config.__dict__, dev))
     print("weights loaded in %.1fs, params %d" % (time.time() - t0, net.param_count()), flush=True)
     x = torch.randn(B, 4, F, H, W, device=dev, dtype=torch.bfloat16)
     ehs = torch.randn(B, 77, 1024, device=dev, dtype=torch.bfloat16)
