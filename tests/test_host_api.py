@@ -247,3 +247,31 @@ def test_only_test_infrastructure_touches_the_oracle():
                 if f.endswith(".py") and pat.search(open(os.path.join(d, f)).read()):
                     bad.append(os.path.join(d, f))
     assert not bad, bad
+
+
+def test_validator_shape_rule_equals_frame0_view_rule():
+    """b2v.validator._frames_of (lengths only, used when the leaves stay on the device) accepts exactly the buffers
+    proof._frame0_f16 (the host view rule of proof.py:321-343) accepts, with the same frame count."""
+    import numpy as np
+    from b2v import proof, validator
+    cfg = {"latent_channels": 4, "latent_height": 3, "latent_width": 5}
+    chw = 60
+    for n_elems in list(range(0, 4 * chw + 3)) + [10 * chw, 10 * chw + 1]:
+        for odd in (0, 1):
+            nbytes = 2 * n_elems + odd
+            buf = bytes(nbytes)
+            try:
+                want = proof._frame0_f16(buf, cfg)
+                frames = max(1, n_elems // chw)
+                assert want.shape == (4, 3, 5)
+            except Exception:
+                frames = None
+            try:
+                got = validator._frames_of(nbytes, cfg)
+            except Exception:
+                got = None
+            assert got == frames, (nbytes, got, frames)
+    # frame 0 under the device layout rule = the host rule's slice
+    x = np.arange(3 * chw, dtype=np.float16)
+    f0 = proof._frame0_f16(x.tobytes(), cfg)
+    assert np.array_equal(f0, x.reshape(4, 3, 3, 5)[:, 0])
