@@ -275,3 +275,19 @@ def test_validator_shape_rule_equals_frame0_view_rule():
     x = np.arange(3 * chw, dtype=np.float16)
     f0 = proof._frame0_f16(x.tobytes(), cfg)
     assert np.array_equal(f0, x.reshape(4, 3, 3, 5)[:, 0])
+
+
+def test_frame_decode_and_validator_have_no_cpu_path():
+    """The new ends of the path fail loudly off-GPU, like the rest of the package (no CPU fallback)."""
+    import torch
+    from b2v import B2VError
+    from b2v.vae import AutoencoderKL, parameter_shapes, SD_VAE_CONFIG
+    with pytest.raises(B2VError):
+        AutoencoderKL(device="cpu")
+    assert sum(int(torch.tensor(s).prod()) for s in parameter_shapes(SD_VAE_CONFIG).values()) == 49490199
+    if not torch.cuda.is_available():
+        from b2v import ops
+        with pytest.raises(B2VError):
+            ops.softmax_rows_(torch.zeros(4, 8, dtype=torch.bfloat16), 1.0)
+        with pytest.raises(B2VError):
+            ops.base64_decode_rows(torch.zeros(1, 16, dtype=torch.uint8))
