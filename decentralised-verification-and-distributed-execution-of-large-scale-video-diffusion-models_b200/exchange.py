@@ -128,7 +128,8 @@ def halo_neighbours(plan, world):
     Returns (windows, halos): windows = [(s, e, rank, index on that rank)] sorted by start; halos[i] = (ov_left, ov_right).
     Raises ValueError when a frame is covered by more than two windows or two windows share a start (padded plans):
     the per-step exchange is defined between adjacent windows only."""
-    wins = sorted(((s, e, r, j) for r in range(world) for j, (s, e) in enumerate(plan.of_rank(r))), key=lambda x: (x[0], x[1]))
+    wins = sorted(((s, e, r, j) for r in range(world) for j, (s, e) in enumerate(plan.of_rank(r))),
+                  key=lambda x: (x[0], x[1]))
     for a, b in zip(wins[:-1], wins[1:]):
         if b[0] <= a[0] or b[1] <= a[1]:
             raise ValueError("halo exchange needs strictly advancing windows, got %r then %r" % (a[:2], b[:2]))

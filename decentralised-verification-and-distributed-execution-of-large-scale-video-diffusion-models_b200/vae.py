@@ -78,7 +78,8 @@ def random_state_dict(cfg, device, seed=4321):
     sd = {}
     for name, shape in parameter_shapes(cfg).items():
         if len(shape) == 1:
-            v = 1.0 + 0.1 * torch.randn(shape, generator=g) if name.endswith("weight") else 0.05 * torch.randn(shape, generator=g)
+            r = torch.randn(shape, generator=g)
+            v = 1.0 + 0.1 * r if name.endswith("weight") else 0.05 * r
         else:
             v = torch.randn(shape, generator=g) / math.sqrt(math.prod(shape[1:]))
         sd[name] = v.to(torch.bfloat16).float().to(device)

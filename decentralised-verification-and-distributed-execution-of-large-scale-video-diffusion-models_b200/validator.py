@@ -77,7 +77,8 @@ def check_revealed_leaves(sub: Submission, request_id: Optional[str] = None, log
             z, e = base64.b64decode(leaf[0]), base64.b64decode(leaf[1])
             path = [base64.b64decode(p) for p in leaf[2]]
             dev = proof._device()
-            h = ops.sha256_leaves([proof._to_dev_bytes(z, dev)], [proof._to_dev_bytes(e, dev)], [t]).cpu().numpy()[0].tobytes()
+            digest = ops.sha256_leaves([proof._to_dev_bytes(z, dev)], [proof._to_dev_bytes(e, dev)], [t])
+            h = digest.cpu().numpy()[0].tobytes()
             if not proof.verify_merkle_leaf(h, path, sub.merkle_root):
                 logger.warning("[%s] Merkle verification failed for miner %s at t=%s", request_id, sub.uid, t)
                 ok = False
