@@ -86,6 +86,25 @@ def random_state_dict(cfg, device, seed=4321):
     return sd
 
 
+_LEGACY_ATTENTION_KEYS = {"query": "to_q", "key": "to_k", "value": "to_v", "proj_attn": "to_out.0"}
+
+
+def canonical_keys(sd):
+    """Checkpoints saved by older diffusers releases (the 2023 Zeroscope / SD VAE files among them) name the mid-block
+    attention projections ``query / key / value / proj_attn``; diffusers renames them to ``to_q / to_k / to_v /
+    to_out.0`` on load. Same here; encoder / quant_conv tensors (never used by decode) are dropped."""
+    out = {}
+    for k, v in sd.items():
+        if k.startswith(("encoder.", "quant_conv.")):
+            continue
+        parts = k.split(".")
+        if len(parts) >= 2 and ".attentions." in k and parts[-2] in _LEGACY_ATTENTION_KEYS:
+            parts[-2:-1] = _LEGACY_ATTENTION_KEYS[parts[-2]].split(".")
+            k = ".".join(parts)
+        out[k] = v
+    return out
+
+
 class AutoencoderKL:
     def __init__(self, config=None, device="cuda"):
         cfg = dict(SD_VAE_CONFIG)
@@ -109,10 +128,13 @@ class AutoencoderKL:
     def load_state_dict(self, sd):
         cfg, dev = self.config.__dict__, self.device
         shapes = parameter_shapes(cfg)
+        sd = canonical_keys(sd)
         missing = [k for k in shapes if k not in sd]
         if missing:
             raise _lib.B2VError("vae state_dict misses %d tensors, e.g. %s" % (len(missing), missing[:3]))
         for k, shp in shapes.items():
+            if len(shp) == 2 and tuple(sd[k].shape) == tuple(shp) + (1, 1):
+                continue  # LDM-style checkpoints keep the attention projections as 1x1 convolutions
             if tuple(sd[k].shape) != tuple(shp):
                 raise _lib.B2VError("vae tensor %s has shape %s, expected %s" % (k, tuple(sd[k].shape), shp))
         f32 = lambda k: sd[k].detach().to(dev, torch.float32).contiguous()  # noqa: E731

@@ -83,3 +83,22 @@ def test_flop_count_matches_module_walk():
         obj = SimpleNamespace(config=SimpleNamespace(**cfg.to_dict()))
         got = vae.AutoencoderKL.flops(obj, 1, h, w)
         assert math.isclose(got, total[0], rel_tol=1e-9), (got, total[0])
+
+
+def test_legacy_checkpoint_key_names_are_accepted():
+    """Older diffusers checkpoints name the VAE attention projections query/key/value/proj_attn; they map onto the
+    current names, encoder tensors are ignored, everything else passes through untouched."""
+    from b2v import vae
+    sd = V.AutoencoderKLDecoder(V.TINY).state_dict()
+    legacy = {}
+    for k, v in sd.items():
+        for new, old in (("to_q", "query"), ("to_k", "key"), ("to_v", "value"), ("to_out.0", "proj_attn")):
+            if ".attentions.0." + new + "." in k:
+                k = k.replace("." + new + ".", "." + old + ".")
+        legacy[k] = v
+    assert any(".query." in k for k in legacy) and not any(".to_q." in k for k in legacy)
+    legacy["encoder.conv_in.weight"] = torch.zeros(1)
+    legacy["quant_conv.weight"] = torch.zeros(1)
+    back = vae.canonical_keys(legacy)
+    assert set(back) == set(sd) and all(back[k] is sd[k] for k in sd)
+    assert vae.canonical_keys(sd).keys() == sd.keys()   # idempotent on current names
