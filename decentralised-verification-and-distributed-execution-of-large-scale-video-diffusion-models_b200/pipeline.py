@@ -13,6 +13,7 @@ seeded [n,77,1024] embedding so the strategies' tokenizer -> text_encoder call s
 """
 import hashlib
 import math
+import os
 from types import SimpleNamespace
 
 import torch
@@ -184,6 +185,28 @@ class VideoPipeline:
         unet = UNet3DConditionModel(cfg, device=device)
         unet.load_state_dict(random_state_dict(unet.config.__dict__, unet.device, seed))
         return cls(unet, DDIMScheduler.from_pipeline_config(), text_dim=cfg["cross_attention_dim"], dtype=dtype)
+
+    @classmethod
+    def from_pretrained(cls, path, device="cuda", dtype=torch.bfloat16, torch_dtype=None, **_):
+        """The reference's ``TextToVideoSDPipeline.from_pretrained(model_id, torch_dtype=...)`` (chunk_only.py:44-56) for
+        a LOCAL diffusers-layout directory: unet (+ vae when present) weights and the scheduler config are read from
+        disk; tokenizer / text encoder stay the synthetic stand-ins unless the caller attaches real ones (the CLIP text
+        tower is outside the accelerated path)."""
+        from . import checkpoint
+        from .vae import AutoencoderKL
+        if not os.path.isdir(path):
+            raise FileNotFoundError("%r is not a local directory (no network: pass a downloaded checkpoint folder)" % (path,))
+        sd, cfg = checkpoint.read_component(path, "unet")
+        ucfg = dict(ZEROSCOPE_CONFIG)
+        ucfg.update(checkpoint.unet_config(cfg))
+        unet = UNet3DConditionModel(ucfg, device=device).load_state_dict(sd)
+        sched = DDIMScheduler(**{**dict(DDIMScheduler.from_pipeline_config().config.__dict__),
+                                 **checkpoint.scheduler_config(path)})
+        vae = None
+        if os.path.isdir(os.path.join(path, "vae")):
+            vsd, vcfg = checkpoint.read_component(path, "vae")
+            vae = AutoencoderKL(checkpoint.vae_config(vcfg), device=device).load_state_dict(vsd)
+        return cls(unet, sched, text_dim=ucfg["cross_attention_dim"], dtype=torch_dtype or dtype, vae=vae)
 
     @classmethod
     def from_state_dict(cls, state_dict, config=None, device="cuda", dtype=torch.bfloat16):

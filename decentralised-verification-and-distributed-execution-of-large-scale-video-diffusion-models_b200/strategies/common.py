@@ -199,9 +199,13 @@ class WindowedDiffuser:
         self.dtype = torch_dtype(getattr(cfg, "dtype", "bf16"))
         if pipe is None:
             from ..pipeline import VideoPipeline
-            LOG.info("rank %d: building random-init %s on %s", self.rank, cfg.model_id, self.device)
-            pipe = VideoPipeline.from_random(cfg.model_id, device=self.device, seed=getattr(cfg, "seed", 1234),
-                                             dtype=self.dtype)
+            if os.path.isdir(cfg.model_id):  # a downloaded diffusers-layout checkpoint (chunk_only.py:44-56)
+                LOG.info("rank %d: loading %s on %s", self.rank, cfg.model_id, self.device)
+                pipe = VideoPipeline.from_pretrained(cfg.model_id, device=self.device, dtype=self.dtype)
+            else:                            # no network here: the named architecture with seeded random weights
+                LOG.info("rank %d: building random-init %s on %s", self.rank, cfg.model_id, self.device)
+                pipe = VideoPipeline.from_random(cfg.model_id, device=self.device, seed=getattr(cfg, "seed", 1234),
+                                                 dtype=self.dtype)
         if getattr(cfg, "decode", False) and getattr(pipe, "vae", None) is None and self.rank == 0:
             from ..vae import AutoencoderKL
             pipe.vae = AutoencoderKL.from_random(device=self.device, seed=getattr(cfg, "seed", 1234) + 1)
