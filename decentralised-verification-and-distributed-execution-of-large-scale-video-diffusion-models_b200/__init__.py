@@ -8,7 +8,8 @@ Layout
   scheduler.py     DDIMScheduler with the diffusers call surface the strategies/miner use
   unet.py          UNet3DConditionModel: pipe.unet(x, t, encoder_hidden_states=emb).sample
   vae.py           AutoencoderKL: pipe.vae.decode(z / 0.18215).sample and decode_frames (latents -> uint8 frames)
-  pipeline.py      pipe-shaped object (unet, scheduler, synthetic text encoder)
+  pipeline.py      pipe-shaped object (unet, scheduler, vae, synthetic text encoder); from_pretrained(local dir)
+  checkpoint.py    reader of diffusers-layout checkpoint folders (safetensors / sharded / .bin), host only
   planner.py       chunk planner / blend weights (host integer logic of chunk_only.py:80-105, 136-150)
   strategies/      chunk_only / fsdp_chunked_coherent / fsdp_chunked / fsdp entry points (same CLI + CSV)
   validator.py     spot-check round over many miners (validator.py:641-845): text in, four launches
