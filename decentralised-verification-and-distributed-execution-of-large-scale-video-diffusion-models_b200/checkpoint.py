@@ -66,8 +66,10 @@ def scheduler_config(root):
 def unet_config(config):
     """diffusers UNet3DConditionModel config.json -> the keys b2v.unet.UNet3DConditionModel takes."""
     out = {}
+    # transformer_in_heads is not a diffusers key (diffusers hard-codes 8 heads for transformer_in); the narrow test
+    # configurations of this repo carry it, real checkpoints fall back to the default 8
     for k in ("in_channels", "out_channels", "layers_per_block", "cross_attention_dim", "attention_head_dim",
-              "norm_num_groups", "norm_eps"):
+              "norm_num_groups", "norm_eps", "transformer_in_heads"):
         if k in config:
             out[k] = config[k]
     if "block_out_channels" in config:

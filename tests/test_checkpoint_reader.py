@@ -54,6 +54,10 @@ def test_read_components(tmp_path, shard, fmt):
     ucfg = checkpoint.unet_config(cfg)
     assert ucfg["block_out_channels"] == (64, 128, 256, 256) and ucfg["cross_attention_dim"] == 128
     assert "_class_name" not in ucfg and "sample_size" not in ucfg
+    assert ucfg["transformer_in_heads"] == 2   # repo-specific key of the narrow test config; absent in real checkpoints
+    from b2v.unet import ZEROSCOPE_CONFIG
+    real = {k: v for k, v in cfg.items() if k != "transformer_in_heads"}
+    assert {**ZEROSCOPE_CONFIG, **checkpoint.unet_config(real)}["transformer_in_heads"] == 8
     vs, vcfg = checkpoint.read_component(str(tmp_path), "vae")
     assert set(vs) == set(vsd)
     assert checkpoint.vae_config(vcfg) == {"latent_channels": 4, "out_channels": 3, "layers_per_block": 2,
