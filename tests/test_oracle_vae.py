@@ -102,3 +102,39 @@ def test_legacy_checkpoint_key_names_are_accepted():
     back = vae.canonical_keys(legacy)
     assert set(back) == set(sd) and all(back[k] is sd[k] for k in sd)
     assert vae.canonical_keys(sd).keys() == sd.keys()   # idempotent on current names
+
+
+def test_weight_repack_host_logic():
+    """AutoencoderKL.load_state_dict is torch-only plumbing (permute / pad / cast), so it can be driven on the CPU with a
+    stand-in object: padded conv_in / conv_out / post_quant_conv tiles, `/scaling_factor` folded into the second
+    post_quant copy, and a legacy-named checkpoint with 1x1-conv attention projections repacks to the same tensors."""
+    from b2v import vae
+    from oracle.unet3d_ref import random_init_
+    ref = random_init_(V.AutoencoderKLDecoder(V.TINY), seed=1, round_bf16=True)
+    cfg = SimpleNamespace(**{**vae.SD_VAE_CONFIG, **V.TINY.to_dict()})
+    a = SimpleNamespace(config=cfg, device=torch.device("cpu"), _w=None)
+    vae.AutoencoderKL.load_state_dict(a, ref.state_dict())
+    assert a.n_params == V.param_count(V.TINY)
+    w_in, _ = a._w["decoder.conv_in"]
+    assert w_in.shape == (128, 3, 3, 64) and w_in.dtype == torch.bfloat16 and float(w_in[..., 4:].abs().max()) == 0
+    assert torch.equal(w_in[..., :4].float(), ref.decoder.conv_in.weight.permute(0, 2, 3, 1))
+    w_out, b_out = a._w["decoder.conv_out"]
+    assert w_out.shape == (64, 3, 3, 64) and float(w_out[3:].abs().max()) == 0 and float(b_out[3:].abs().max()) == 0
+    pq, pqb = a._w["pq"]
+    pqs, _ = a._w["pq_scaled"]
+    assert pq.shape == (64, 64) and float(pq[4:].abs().max()) == 0 and float(pq[:, 4:].abs().max()) == 0
+    want = (ref.post_quant_conv.weight.view(4, 4) / 0.18215).to(torch.bfloat16)
+    assert torch.equal(pqs[:4, :4], want) and torch.equal(pqb[:4], ref.post_quant_conv.bias)
+    legacy = {}
+    for k, v in ref.state_dict().items():
+        for new, old in (("to_q", "query"), ("to_k", "key"), ("to_v", "value"), ("to_out.0", "proj_attn")):
+            if ".attentions.0." + new + "." in k:
+                k = k.replace("." + new + ".", "." + old + ".")
+                if k.endswith("weight"):
+                    v = v[:, :, None, None]
+        legacy[k] = v
+    b = SimpleNamespace(config=cfg, device=torch.device("cpu"), _w=None)
+    vae.AutoencoderKL.load_state_dict(b, legacy)
+    assert all(torch.equal(a._w[k][0], b._w[k][0]) and torch.equal(a._w[k][1], b._w[k][1]) for k in a._w)
+    with __import__("pytest").raises(vae._lib.B2VError):
+        vae.AutoencoderKL.load_state_dict(b, {k: v for k, v in legacy.items() if "conv_out" not in k})
