@@ -107,6 +107,10 @@ def test_cli_flags_and_defaults():
     assert f.num_frames == 25 and f.out_csv == "legacy.csv" and not hasattr(f, "guidance_scale")
     with pytest.raises(SystemExit):
         fsdp.parse_args(["--overlap", "2"])
+    # additions of this build are off by default: the reference's behaviour is what runs without flags
+    assert (c.halo_sync, c.decode, c.exchange) == (False, False, "p2p")
+    on = chunk_only.parse_args(["--halo_sync", "--decode", "--exchange", "nccl"])
+    assert (on.halo_sync, on.decode, on.exchange) == (True, True, "nccl")
     # the experiment driver's command line (full_experiments_ZeroscopeXL.sh:25) parses
     chunk_only.parse_args("--emu_bw_mbps 500 --emu_rtt_ms 3.01 --emu_jitter_ms 3.53 --model_id cerspense/zeroscope_v2_XL "
                           "--out_csv ZeroscopeXL/wifi_results.csv".split())
