@@ -24,7 +24,7 @@ class UNet3DConfigC(C.Structure):
         ("in_channels", C.c_int), ("out_channels", C.c_int), ("block_out_channels", C.c_int * 4),
         ("layers_per_block", C.c_int), ("cross_attention_dim", C.c_int), ("attention_head_dim", C.c_int),
         ("norm_num_groups", C.c_int), ("norm_eps", C.c_float), ("transformer_in_heads", C.c_int),
-        ("text_len", C.c_int),
+        ("text_len", C.c_int), ("act_dtype", C.c_int),
     ]
 
 
@@ -57,18 +57,18 @@ _SIGNATURES = {
     "b2v_unet3d_workspace_bytes": (_sz, [_vp, _i, _i, _i, _i]),
     "b2v_unet3d_forward": (_i, [_vp, _vp, _f, _vp, _vp, _i, _i, _i, _i, _i, _vp, _sz, _vp]),
     "b2v_unet3d_flops": (C.c_double, [_vp, _i, _i, _i, _i]),
-    "b2v_op_gemm": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _i64, _i, _i, _i, _i64, _i64, _i, _vp]),
+    "b2v_op_gemm": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _i64, _i, _i, _i, _i64, _i64, _i, _i, _vp]),
     "b2v_op_conv3x3_scratch_bytes": (_sz, [_i, _i, _i, _i, _i, _i]),
-    "b2v_op_conv3x3": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _vp]),
-    "b2v_op_group_norm": (_i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _i64, _i64, _i, _f, _i, _vp, _vp]),
+    "b2v_op_conv3x3": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _i, _vp]),
+    "b2v_op_group_norm": (_i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _i64, _i64, _i, _f, _i, _vp, _i, _vp]),
     "b2v_op_group_norm_scratch_bytes": (_sz, [_i64, _i64, _i]),
-    "b2v_op_layer_norm": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _f, _vp]),
-    "b2v_op_attention": (_i, [_vp, _i64, _vp, _vp, _i64, _vp, _i64, _i, _i, _i, _i, _i, _f, _vp]),
-    "b2v_op_temporal_attention": (_i, [_vp, _i64, _i, _i, _i, _vp, _i64, _i, _i, _i64, _i, _f, _vp]),
+    "b2v_op_layer_norm": (_i, [_vp, _vp, _vp, _vp, _i64, _i, _f, _i, _vp]),
+    "b2v_op_attention": (_i, [_vp, _i64, _vp, _vp, _i64, _vp, _i64, _i, _i, _i, _i, _i, _f, _i, _vp]),
+    "b2v_op_temporal_attention": (_i, [_vp, _i64, _i, _i, _i, _vp, _i64, _i, _i, _i64, _i, _f, _i, _vp]),
     "b2v_op_softmax_rows": (_i, [_vp, _i64, _i, _i64, _f, _vp]),
     "b2v_op_frames_u8": (_i, [_vp, _i64, _i64, _vp, _vp]),
     "b2v_op_upsample2x": (_i, [_vp, _vp, _i, _i, _i, _i, _vp]),
-    "b2v_op_latent_rows": (_i, [_vp, _i, _vp, _i, _i, _i, _i64, _i, _vp]),
+    "b2v_op_latent_rows": (_i, [_vp, _i, _vp, _i, _i, _i, _i64, _i, _i, _vp]),
 }
 
 EXPORTED_SYMBOLS = tuple(_SIGNATURES)

@@ -48,6 +48,7 @@ struct AttnParams {
   float scale_log2;  // scale * log2(e)
 };
 
+template <bool F16>
 __global__ void __launch_bounds__(AT_THREADS, 2)
 attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
             const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
@@ -103,8 +104,8 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       }
     }
   } else if (warp == 1) {
-    constexpr uint32_t idesc_qk = umma_idesc_bf16(128, 128);
-    constexpr uint32_t idesc_pv = umma_idesc_bf16(128, 64) | (1u << 16);  // B (=V) is MN-major
+    constexpr uint32_t idesc_qk = umma_idesc_16(128, 128, F16, F16);
+    constexpr uint32_t idesc_pv = umma_idesc_16(128, 64, F16, F16) | (1u << 16);  // B (=V) is MN-major
     auto issue_qk = [&](int j) {
       const int st = j & 1;
       mbar_wait(k_full0 + 8 * st, (j >> 1) & 1);
@@ -203,7 +204,7 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
         const float e0 = ex2(x0), e1 = ex2(x1);
         if (i & 1) sumB = add2(sumB, pack2(e0, e1));
         else sumA = add2(sumA, pack2(e0, e1));
-        pk[i] = pack_bf16x2(e0, e1);
+        pk[i] = pack_act2<F16>(e0, e1);
       }
       float s0, s1;
       unpack2(add2(sumA, sumB), s0, s1);
@@ -249,10 +250,10 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
 #pragma unroll
       for (int q = 0; q < 8; ++q) {
         uint4 u;
-        u.x = pack_bf16x2(__uint_as_float(ov[8 * q]) * inv, __uint_as_float(ov[8 * q + 1]) * inv);
-        u.y = pack_bf16x2(__uint_as_float(ov[8 * q + 2]) * inv, __uint_as_float(ov[8 * q + 3]) * inv);
-        u.z = pack_bf16x2(__uint_as_float(ov[8 * q + 4]) * inv, __uint_as_float(ov[8 * q + 5]) * inv);
-        u.w = pack_bf16x2(__uint_as_float(ov[8 * q + 6]) * inv, __uint_as_float(ov[8 * q + 7]) * inv);
+        u.x = pack_act2<F16>(__uint_as_float(ov[8 * q]) * inv, __uint_as_float(ov[8 * q + 1]) * inv);
+        u.y = pack_act2<F16>(__uint_as_float(ov[8 * q + 2]) * inv, __uint_as_float(ov[8 * q + 3]) * inv);
+        u.z = pack_act2<F16>(__uint_as_float(ov[8 * q + 4]) * inv, __uint_as_float(ov[8 * q + 5]) * inv);
+        u.w = pack_act2<F16>(__uint_as_float(ov[8 * q + 6]) * inv, __uint_as_float(ov[8 * q + 7]) * inv);
         dst[q] = u;
       }
     }
@@ -274,16 +275,23 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
 //   O = P V   : P is the S accumulator re-packed (FA2 register trick); lane (g, tg) holds d in [8 g, 8 g + 8) of
 //               kv frames 2 tg, 2 tg + 1, 2 tg + 8, 2 tg + 9 (V), byte-permuted into (frame, frame+1) pairs
 // ------------------------------------------------------------------------------------------------
-__device__ __forceinline__ void mma_bf16_16816(float* d, const uint32_t* a, uint32_t b0, uint32_t b1) {
-  asm volatile(
-      "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
-      : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
-      : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+template <bool F16>
+__device__ __forceinline__ void mma_16816(float* d, const uint32_t* a, uint32_t b0, uint32_t b1) {
+  if constexpr (F16)
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.f16.f16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
+  else
+    asm volatile(
+        "mma.sync.aligned.m16n8k16.row.col.f32.bf16.bf16.f32 {%0,%1,%2,%3}, {%4,%5,%6,%7}, {%8,%9}, {%0,%1,%2,%3};"
+        : "+f"(d[0]), "+f"(d[1]), "+f"(d[2]), "+f"(d[3])
+        : "r"(a[0]), "r"(a[1]), "r"(a[2]), "r"(a[3]), "r"(b0), "r"(b1));
 }
 
 constexpr int TA_WARPS = 8;
 
-template <int FT>  // number of 16-frame tiles: F <= 16 * FT
+template <int FT, bool F16>  // FT = number of 16-frame tiles: F <= 16 * FT
 __global__ void __launch_bounds__(TA_WARPS * 32)
 temporal_attn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int q_off, int k_off, int v_off,
                      __nv_bfloat16* __restrict__ out, int64_t ldo, int B, int F, int64_t HW, int heads,
@@ -350,7 +358,7 @@ temporal_attn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int q_of
 #pragma unroll
         for (int s = 0; s < 4; ++s) {
           const uint32_t a[4] = {q0[2 * s], q1[2 * s], q0[2 * s + 1], q1[2 * s + 1]};
-          mma_bf16_16816(sacc[nt], a, kr[nt][2 * s], kr[nt][2 * s + 1]);
+          mma_16816<F16>(sacc[nt], a, kr[nt][2 * s], kr[nt][2 * s + 1]);
         }
       }
       // ---- softmax over kv frames (row g: [0],[1]; row g+8: [2],[3]); columns nt*8 + 2 tg + {0,1}
@@ -382,10 +390,10 @@ temporal_attn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int q_of
       for (int nt = 0; nt < 8; ++nt) oacc[nt][0] = oacc[nt][1] = oacc[nt][2] = oacc[nt][3] = 0.f;
 #pragma unroll
       for (int ks = 0; ks < FT; ++ks) {
-        const uint32_t a[4] = {pack_bf16x2(sacc[2 * ks][0] * i0, sacc[2 * ks][1] * i0),
-                               pack_bf16x2(sacc[2 * ks][2] * i1, sacc[2 * ks][3] * i1),
-                               pack_bf16x2(sacc[2 * ks + 1][0] * i0, sacc[2 * ks + 1][1] * i0),
-                               pack_bf16x2(sacc[2 * ks + 1][2] * i1, sacc[2 * ks + 1][3] * i1)};
+        const uint32_t a[4] = {pack_act2<F16>(sacc[2 * ks][0] * i0, sacc[2 * ks][1] * i0),
+                               pack_act2<F16>(sacc[2 * ks][2] * i1, sacc[2 * ks][3] * i1),
+                               pack_act2<F16>(sacc[2 * ks + 1][0] * i0, sacc[2 * ks + 1][1] * i0),
+                               pack_act2<F16>(sacc[2 * ks + 1][2] * i1, sacc[2 * ks + 1][3] * i1)};
         const uint32_t v0[4] = {vr[ks][0].x, vr[ks][0].y, vr[ks][0].z, vr[ks][0].w};
         const uint32_t v1[4] = {vr[ks][1].x, vr[ks][1].y, vr[ks][1].z, vr[ks][1].w};
         const uint32_t v2[4] = {vr[ks][2].x, vr[ks][2].y, vr[ks][2].z, vr[ks][2].w};
@@ -395,7 +403,7 @@ temporal_attn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int q_of
           const uint32_t sel = (nt & 1) ? 0x7632u : 0x5410u;  // (frame, frame+1) pair of element nt
           const uint32_t b0 = __byte_perm(v0[nt >> 1], v1[nt >> 1], sel);
           const uint32_t b1 = __byte_perm(v2[nt >> 1], v3[nt >> 1], sel);
-          mma_bf16_16816(oacc[nt], a, b0, b1);
+          mma_16816<F16>(oacc[nt], a, b0, b1);
         }
       }
       // ---- store: row g holds d = 16 tg + nt ([0]) and 16 tg + 8 + nt ([1]); row g+8: [2], [3]
@@ -403,17 +411,17 @@ temporal_attn_kernel(const __nv_bfloat16* __restrict__ qkv, int64_t ld, int q_of
       const int64_t orow = ((int64_t)b * F * HW + pix) * ldo + h * 64 + tg * 16;
       if (f0 < F) {
         uint4* dst = reinterpret_cast<uint4*>(out + orow + f0 * HW * ldo);
-        dst[0] = make_uint4(pack_bf16x2(oacc[0][0], oacc[1][0]), pack_bf16x2(oacc[2][0], oacc[3][0]),
-                            pack_bf16x2(oacc[4][0], oacc[5][0]), pack_bf16x2(oacc[6][0], oacc[7][0]));
-        dst[1] = make_uint4(pack_bf16x2(oacc[0][1], oacc[1][1]), pack_bf16x2(oacc[2][1], oacc[3][1]),
-                            pack_bf16x2(oacc[4][1], oacc[5][1]), pack_bf16x2(oacc[6][1], oacc[7][1]));
+        dst[0] = make_uint4(pack_act2<F16>(oacc[0][0], oacc[1][0]), pack_act2<F16>(oacc[2][0], oacc[3][0]),
+                            pack_act2<F16>(oacc[4][0], oacc[5][0]), pack_act2<F16>(oacc[6][0], oacc[7][0]));
+        dst[1] = make_uint4(pack_act2<F16>(oacc[0][1], oacc[1][1]), pack_act2<F16>(oacc[2][1], oacc[3][1]),
+                            pack_act2<F16>(oacc[4][1], oacc[5][1]), pack_act2<F16>(oacc[6][1], oacc[7][1]));
       }
       if (f1 < F) {
         uint4* dst = reinterpret_cast<uint4*>(out + orow + f1 * HW * ldo);
-        dst[0] = make_uint4(pack_bf16x2(oacc[0][2], oacc[1][2]), pack_bf16x2(oacc[2][2], oacc[3][2]),
-                            pack_bf16x2(oacc[4][2], oacc[5][2]), pack_bf16x2(oacc[6][2], oacc[7][2]));
-        dst[1] = make_uint4(pack_bf16x2(oacc[0][3], oacc[1][3]), pack_bf16x2(oacc[2][3], oacc[3][3]),
-                            pack_bf16x2(oacc[4][3], oacc[5][3]), pack_bf16x2(oacc[6][3], oacc[7][3]));
+        dst[0] = make_uint4(pack_act2<F16>(oacc[0][2], oacc[1][2]), pack_act2<F16>(oacc[2][2], oacc[3][2]),
+                            pack_act2<F16>(oacc[4][2], oacc[5][2]), pack_act2<F16>(oacc[6][2], oacc[7][2]));
+        dst[1] = make_uint4(pack_act2<F16>(oacc[0][3], oacc[1][3]), pack_act2<F16>(oacc[2][3], oacc[3][3]),
+                            pack_act2<F16>(oacc[4][3], oacc[5][3]), pack_act2<F16>(oacc[6][3], oacc[7][3]));
       }
     }
   }
@@ -427,10 +435,13 @@ int attention(const AttnArgs& a, cudaStream_t s) {
             "attention: bad shape");
   B2V_CHECK(a.ldq % 8 == 0 && a.ldkv % 8 == 0 && a.ldo % 8 == 0, "attention: leading dims must be multiples of 8");
   B2V_CHECK(a.heads <= 65535 && a.nb <= 65535, "attention: grid too large");
+  B2V_CHECK(act_ok(a.adt), "attention: activation dtype must be bf16 or fp16");
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(attn_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);
+    attr_err = cudaFuncSetAttribute(attn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);
+    if (attr_err == cudaSuccess)
+      attr_err = cudaFuncSetAttribute(attn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);
   });
   if (attr_err != cudaSuccess) return fail(B2V_ERR_CUDA, "attention smem attr: %s", cudaGetErrorString(attr_err));
   CUtensorMap tmQ, tmK, tmV;
@@ -453,15 +464,17 @@ int attention(const AttnArgs& a, cudaStream_t s) {
   p.nkv = (a.Skv + 127) / 128;
   p.scale_log2 = a.scale * 1.4426950408889634f;
   dim3 grid((unsigned)((a.Sq + 127) / 128), (unsigned)a.heads, (unsigned)a.nb);
-  B2V_CUDA_OK(launch_pdl(attn_kernel, grid, dim3(AT_THREADS), AT_SMEM, s, tmQ, tmK, tmV, p));
+  if (a.adt == B2V_F16) B2V_CUDA_OK(launch_pdl(attn_kernel<true>, grid, dim3(AT_THREADS), AT_SMEM, s, tmQ, tmK, tmV, p));
+  else B2V_CUDA_OK(launch_pdl(attn_kernel<false>, grid, dim3(AT_THREADS), AT_SMEM, s, tmQ, tmK, tmV, p));
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;
 }
 
-int temporal_attention(const void* qkv, int64_t ld, int q_off, int k_off, int v_off, void* out, int64_t ldo, int B,
-                       int F, int64_t HW, int heads, float scale, cudaStream_t s) {
+int temporal_attention(int adt, const void* qkv, int64_t ld, int q_off, int k_off, int v_off, void* out, int64_t ldo,
+                       int B, int F, int64_t HW, int heads, float scale, cudaStream_t s) {
   B2V_CHECK(qkv && out, "temporal_attention: null pointer");
+  B2V_CHECK(act_ok(adt), "temporal_attention: activation dtype must be bf16 or fp16");
   B2V_CHECK(F >= 1 && F <= 32, "temporal_attention: F=%d must be in [1,32]", F);
   B2V_CHECK(ld % 8 == 0 && ldo % 8 == 0 && q_off % 8 == 0 && k_off % 8 == 0 && v_off % 8 == 0,
             "temporal_attention: offsets must be multiples of 8");
@@ -470,14 +483,13 @@ int temporal_attention(const void* qkv, int64_t ld, int q_off, int k_off, int v_
   const int64_t cap = (int64_t)sm_count() * 8;
   if (grid > cap) grid = cap;
   B2V_CHECK(ld % 8 == 0 && ((uintptr_t)qkv & 15) == 0 && ((uintptr_t)out & 15) == 0, "temporal_attention: 16-byte alignment");
-  if (F <= 16)
-    B2V_CUDA_OK(launch_pdl(temporal_attn_kernel<1>, dim3((unsigned)grid), dim3(TA_WARPS * 32), 0, s,
-                           (const __nv_bfloat16*)qkv, ld, q_off, k_off, v_off, (__nv_bfloat16*)out, ldo, B, F, HW, heads,
-                           scale * 1.4426950408889634f));
-  else
-    B2V_CUDA_OK(launch_pdl(temporal_attn_kernel<2>, dim3((unsigned)grid), dim3(TA_WARPS * 32), 0, s,
-                           (const __nv_bfloat16*)qkv, ld, q_off, k_off, v_off, (__nv_bfloat16*)out, ldo, B, F, HW, heads,
-                           scale * 1.4426950408889634f));
+#define B2V_TA(FT, F16)                                                                                             \
+  B2V_CUDA_OK(launch_pdl(temporal_attn_kernel<FT, F16>, dim3((unsigned)grid), dim3(TA_WARPS * 32), 0, s,                \
+                         (const __nv_bfloat16*)qkv, ld, q_off, k_off, v_off, (__nv_bfloat16*)out, ldo, B, F, HW, heads, \
+                         scale * 1.4426950408889634f))
+  if (adt == B2V_F16) { if (F <= 16) B2V_TA(1, true); else B2V_TA(2, true); }
+  else { if (F <= 16) B2V_TA(1, false); else B2V_TA(2, false); }
+#undef B2V_TA
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;

@@ -7,10 +7,12 @@ using namespace b2v;
 
 extern "C" int b2v_op_gemm(const void* a_dev, const void* w_dev, const float* bias_dev, const float* rowbias_dev,
                            int64_t rows_per_group, const void* residual_dev, void* out_dev, int64_t M, int N, int Kc,
-                           int taps, int64_t tap_row_stride, int64_t rows_per_batch, int flags, void* stream) {
+                           int taps, int64_t tap_row_stride, int64_t rows_per_batch, int flags, int act_dtype,
+                           void* stream) {
   B2V_CHECK(a_dev && w_dev && out_dev, "null argument");
   B2V_TRY(b2v_device_check());
   GemmArgs g;
+  g.adt = act_dtype;
   g.a = a_dev; g.w = w_dev; g.bias = bias_dev; g.rowbias = rowbias_dev; g.rows_per_group = rows_per_group;
   g.residual = residual_dev; g.out = out_dev; g.M = M; g.N = N; g.Kc = Kc; g.taps = taps;
   g.tap_row_stride = tap_row_stride; g.rows_per_batch = rows_per_batch; g.flags = flags;
@@ -25,12 +27,14 @@ extern "C" size_t b2v_op_conv3x3_scratch_bytes(int N, int H, int W, int Cin, int
 
 extern "C" int b2v_op_conv3x3(const void* x_dev, const void* w_dev, const float* bias_dev, const float* rowbias_dev,
                               int64_t rows_per_group, const void* residual_dev, void* out_dev, int N, int H, int W,
-                              int Cin, int Cout, int stride, int mode, void* scratch_dev, void* stream) {
+                              int Cin, int Cout, int stride, int mode, void* scratch_dev, int act_dtype,
+                              void* stream) {
   B2V_CHECK(x_dev && w_dev && out_dev, "null argument");
   B2V_TRY(b2v_device_check());
   cudaStream_t s = (cudaStream_t)stream;
   if (mode == 0) {
     ConvArgs c;
+    c.adt = act_dtype;
     c.x = x_dev; c.w = w_dev; c.bias = bias_dev; c.rowbias = rowbias_dev; c.rows_per_group = rows_per_group;
     c.residual = residual_dev; c.out = out_dev; c.N = N; c.H = H; c.W = W; c.Cin = Cin; c.Cout = Cout; c.stride = stride;
     return conv3x3_im2col(c, s);
@@ -39,6 +43,7 @@ extern "C" int b2v_op_conv3x3(const void* x_dev, const void* w_dev, const float*
   B2V_TRY(im2col3x3(x_dev, scratch_dev, N, H, W, Cin, stride, s));
   const int64_t P = (H - 1) / stride + 1, Q = (W - 1) / stride + 1;
   GemmArgs g;
+  g.adt = act_dtype;
   g.a = scratch_dev; g.w = w_dev; g.bias = bias_dev; g.rowbias = rowbias_dev; g.rows_per_group = rows_per_group;
   g.residual = residual_dev; g.out = out_dev; g.M = (int64_t)N * P * Q; g.N = Cout; g.Kc = 9 * Cin; g.taps = 1;
   return gemm_tiled(g, s);
@@ -46,10 +51,10 @@ extern "C" int b2v_op_conv3x3(const void* x_dev, const void* w_dev, const float*
 
 extern "C" int b2v_op_group_norm(const void* x_dev, int C1, const void* x2_dev, int C2, const float* gamma_dev,
                                  const float* beta_dev, void* y_dev, int64_t n_items, int64_t rows_per_item,
-                                 int groups, float eps, int silu, void* stats_dev, void* stream) {
+                                 int groups, float eps, int silu, void* stats_dev, int act_dtype, void* stream) {
   B2V_CHECK(x_dev && gamma_dev && beta_dev && y_dev && stats_dev, "null argument");
   B2V_TRY(b2v_device_check());
-  return group_norm(x_dev, C1, x2_dev, C2, gamma_dev, beta_dev, y_dev, n_items, rows_per_item, groups, eps, silu,
+  return group_norm(act_dtype, x_dev, C1, x2_dev, C2, gamma_dev, beta_dev, y_dev, n_items, rows_per_item, groups, eps, silu,
                     stats_dev, (cudaStream_t)stream);
 }
 
@@ -58,17 +63,18 @@ extern "C" size_t b2v_op_group_norm_scratch_bytes(int64_t n_items, int64_t rows_
 }
 
 extern "C" int b2v_op_layer_norm(const void* x_dev, const float* gamma_dev, const float* beta_dev, void* y_dev,
-                                 int64_t rows, int C, float eps, void* stream) {
+                                 int64_t rows, int C, float eps, int act_dtype, void* stream) {
   B2V_CHECK(x_dev && gamma_dev && beta_dev && y_dev, "null argument");
   B2V_TRY(b2v_device_check());
-  return layer_norm(x_dev, gamma_dev, beta_dev, y_dev, rows, C, eps, (cudaStream_t)stream);
+  return layer_norm(act_dtype, x_dev, gamma_dev, beta_dev, y_dev, rows, C, eps, (cudaStream_t)stream);
 }
 
 extern "C" int b2v_op_attention(const void* q_dev, int64_t ldq, const void* k_dev, const void* v_dev, int64_t ldkv,
                                 void* out_dev, int64_t ldo, int nb, int heads, int Sq, int Skv, int kv_group,
-                                float scale, void* stream) {
+                                float scale, int act_dtype, void* stream) {
   B2V_TRY(b2v_device_check());
   AttnArgs a;
+  a.adt = act_dtype;
   a.q = q_dev; a.k = k_dev; a.v = v_dev; a.out = out_dev; a.ldq = ldq; a.ldkv = ldkv; a.ldo = ldo;
   a.nb = nb; a.heads = heads; a.Sq = Sq; a.Skv = Skv; a.kv_group = kv_group; a.scale = scale;
   return attention(a, (cudaStream_t)stream);
@@ -76,8 +82,8 @@ extern "C" int b2v_op_attention(const void* q_dev, int64_t ldq, const void* k_de
 
 extern "C" int b2v_op_temporal_attention(const void* qkv_dev, int64_t ld, int q_off, int k_off, int v_off,
                                          void* out_dev, int64_t ldo, int B, int F, int64_t HW, int heads, float scale,
-                                         void* stream) {
+                                         int act_dtype, void* stream) {
   B2V_TRY(b2v_device_check());
-  return temporal_attention(qkv_dev, ld, q_off, k_off, v_off, out_dev, ldo, B, F, HW, heads, scale,
+  return temporal_attention(act_dtype, qkv_dev, ld, q_off, k_off, v_off, out_dev, ldo, B, F, HW, heads, scale,
                             (cudaStream_t)stream);
 }

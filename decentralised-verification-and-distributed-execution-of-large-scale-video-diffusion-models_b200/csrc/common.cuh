@@ -114,6 +114,40 @@ __device__ __forceinline__ float2 unpack_bf16x2(uint32_t u) {
   return __bfloat1622float2(v);
 }
 
+// ---- 2-byte activation element: bf16 (default) or fp16 (the reference's torch_dtype=float16, chunk_only.py:44-47).
+// Kernels are templated on `bool F16`; both formats run at the same tensor-core rate (tcgen05 kind::f16). ----
+template <bool F16>
+__device__ __forceinline__ uint32_t pack_act2(float lo, float hi) {
+  if constexpr (F16) {
+    __half2 v = __floats2half2_rn(lo, hi);
+    return *reinterpret_cast<uint32_t*>(&v);
+  } else {
+    return pack_bf16x2(lo, hi);
+  }
+}
+template <bool F16>
+__device__ __forceinline__ float2 unpack_act2(uint32_t u) {
+  if constexpr (F16) {
+    __half2 v = *reinterpret_cast<__half2*>(&u);
+    return __half22float2(v);
+  } else {
+    return unpack_bf16x2(u);
+  }
+}
+template <bool F16>
+__device__ __forceinline__ uint16_t to_act(float x) {
+  if constexpr (F16) return __half_as_ushort(__float2half_rn(x));
+  else return __bfloat16_as_ushort(__float2bfloat16_rn(x));
+}
+static inline bool act_ok(int adt) { return adt == B2V_BF16 || adt == B2V_F16; }
+// run `...` with a constexpr bool F16 selected by the activation dtype tag
+#define B2V_DISPATCH_ACT(adt, F16, ...)                                                    \
+  do {                                                                                     \
+    if ((adt) == B2V_F16) { constexpr bool F16 = true; __VA_ARGS__; }                      \
+    else if ((adt) == B2V_BF16) { constexpr bool F16 = false; __VA_ARGS__; }               \
+    else return ::b2v::fail(B2V_ERR_ARG, "activation dtype %d is neither bf16 nor fp16", (int)(adt)); \
+  } while (0)
+
 __device__ __forceinline__ float warp_sum(float v) {
 #pragma unroll
   for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);

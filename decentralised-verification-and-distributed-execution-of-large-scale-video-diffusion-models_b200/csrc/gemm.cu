@@ -78,8 +78,8 @@ struct GemmParams {
   const float* bias;        // [N] (GEGLU: packed like W)
   const float* rowbias;     // [M / rows_per_group, N] or null
   int64_t rows_per_group;
-  const __nv_bfloat16* residual;  // [M, ldo] or null
-  __nv_bfloat16* out;
+  const void* residual;  // [M, ldo] or null (2-byte activations)
+  void* out;
   int64_t ldo;
   int gelu;
   // EPI_NCFHW (conv_out): out_raw[((b*nc_cout + co)*nc_F + f)*nc_HW + pix] of dtype nc_dtype, row = (b*nc_F + f)*nc_HW + pix
@@ -134,7 +134,7 @@ __device__ __forceinline__ uint64_t gelu_fast2(uint64_t x2) {
 // GEMMs were bound by the LSU/L2 request rate of the latter). With RES the residual panel ARRIVES in the same buffer by
 // TMA load and is updated in place; when a tile is one panel wide (all but BN = 256) two buffers alternate so the
 // residual of the NEXT tile is already in flight while this one is processed.
-template <int BN, int MODE, bool GEGLU, bool RES, int CG>
+template <int BN, int MODE, bool GEGLU, bool RES, int CG, bool F16>
 __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtensorMap* tmO, const CUtensorMap* tmR,
                                               uint8_t* stage0, uint32_t rbar0, uint32_t tmem_base, uint32_t tfull0,
                                               uint32_t tempty0, int warp, int lane, int num_tiles) {
@@ -298,15 +298,15 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
         const uint32_t dst = srow + (pos << 4);
         if (RES) {
           const uint4 r = lds128(dst);
-          const float2 a = unpack_bf16x2(r.x), b = unpack_bf16x2(r.y), cc = unpack_bf16x2(r.z), d = unpack_bf16x2(r.w);
+          const float2 a = unpack_act2<F16>(r.x), b = unpack_act2<F16>(r.y), cc = unpack_act2<F16>(r.z), d = unpack_act2<F16>(r.w);
           f[8 * j] += a.x; f[8 * j + 1] += a.y; f[8 * j + 2] += b.x; f[8 * j + 3] += b.y;
           f[8 * j + 4] += cc.x; f[8 * j + 5] += cc.y; f[8 * j + 6] += d.x; f[8 * j + 7] += d.y;
         }
         uint4 o;
-        o.x = pack_bf16x2(f[8 * j], f[8 * j + 1]);
-        o.y = pack_bf16x2(f[8 * j + 2], f[8 * j + 3]);
-        o.z = pack_bf16x2(f[8 * j + 4], f[8 * j + 5]);
-        o.w = pack_bf16x2(f[8 * j + 6], f[8 * j + 7]);
+        o.x = pack_act2<F16>(f[8 * j], f[8 * j + 1]);
+        o.y = pack_act2<F16>(f[8 * j + 2], f[8 * j + 3]);
+        o.z = pack_act2<F16>(f[8 * j + 4], f[8 * j + 5]);
+        o.w = pack_act2<F16>(f[8 * j + 6], f[8 * j + 7]);
         sts128(dst, o);
       }
       if (k == CH_PER_PANEL - 1) {
@@ -372,7 +372,7 @@ __device__ __forceinline__ void epilogue_loop_ncfhw(const GemmParams& p, uint32_
 }
 
 // MODE 0: A through a 3-D tiled tensor map (channels, rows, slabs); MODE 1: A through a 4-D im2col map.
-template <int BN, int MODE, int EPI, bool RES, int CG>
+template <int BN, int MODE, int EPI, bool RES, int CG, bool F16>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR, const GemmParams p) {
@@ -471,7 +471,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   } else if (warp == 1) {
     // ===================== MMA issuer (the leader CTA of a pair) =====================
     if (rank == 0) {
-      constexpr uint32_t idesc = umma_idesc_bf16(BM * CG, BN);
+      constexpr uint32_t idesc = umma_idesc_16(BM * CG, BN, F16, F16);
       int stage = 0;
       uint32_t phase = 0;
       int acc = 0;
@@ -511,10 +511,10 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if constexpr (EPI == EPI_NCFHW)
       epilogue_loop_ncfhw<Cfg::ACC_STRIDE>(p, tmem_base, tfull0, tempty0, warp, lane, num_tiles);
     else
-      epilogue_loop<BN, MODE, EPI == EPI_GEGLU_T, RES, CG>(p, &tmO, &tmR,
-                                                           sEpi + (warp - 2) * Cfg::NBUF * Cfg::PANEL_BYTES,
-                                                           rbar0 + 16 * (warp - 2), tmem_base, tfull0, tempty0, warp,
-                                                           lane, num_tiles);
+      epilogue_loop<BN, MODE, EPI == EPI_GEGLU_T, RES, CG, F16>(p, &tmO, &tmR,
+                                                                sEpi + (warp - 2) * Cfg::NBUF * Cfg::PANEL_BYTES,
+                                                                rbar0 + 16 * (warp - 2), tmem_base, tfull0, tempty0,
+                                                                warp, lane, num_tiles);
   }
 
   tc_fence_before();
@@ -527,7 +527,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   }
 }
 
-template <int BN, int MODE, int EPI, bool RES, int CG>
+template <int BN, int MODE, int EPI, bool RES, int CG, bool F16>
 int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int64_t out_rows_per_slab,
                 int64_t out_slabs, cudaStream_t s) {
   using Cfg = TileCfg<BN, EPI == EPI_GEGLU_T, RES, CG>;
@@ -543,14 +543,14 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(gemm_kernel<BN, MODE, EPI, RES, CG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    attr_err = cudaFuncSetAttribute(gemm_kernel<BN, MODE, EPI, RES, CG, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     Cfg::SMEM_BYTES);
   });
   if (attr_err != cudaSuccess) return fail(B2V_ERR_CUDA, "gemm smem attr: %s", cudaGetErrorString(attr_err));
   const int units = p.num_m_units * p.num_n_tiles;
   if (CG == 1) {
     const int grid = units < sm_count() ? units : sm_count();
-    B2V_CUDA_OK(launch_pdl(gemm_kernel<BN, MODE, EPI, RES, CG>, dim3((unsigned)grid), dim3(NUM_THREADS), Cfg::SMEM_BYTES, s,
+    B2V_CUDA_OK(launch_pdl(gemm_kernel<BN, MODE, EPI, RES, CG, F16>, dim3((unsigned)grid), dim3(NUM_THREADS), Cfg::SMEM_BYTES, s,
                            tmA, tmB, tmO, tmR, p));
   } else {
     // one CTA pair (cluster of 2 = the two SMs of a TPC) per work unit, persistent over the units
@@ -567,34 +567,42 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
     attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
     cfg.attrs = attr;
     cfg.numAttrs = 2;
-    B2V_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_kernel<BN, MODE, EPI, RES, CG>, tmA, tmB, tmO, tmR, p));
+    B2V_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_kernel<BN, MODE, EPI, RES, CG, F16>, tmA, tmB, tmO, tmR, p));
   }
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;
 }
 
-template <int BN, int MODE, int CG>
+template <int BN, int MODE, int CG, bool F16>
 int launch_plain(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int64_t orows, int64_t oslabs,
                  cudaStream_t s) {
-  if (p.residual) return launch_gemm<BN, MODE, EPI_PLAIN, true, CG>(tmA, tmB, p, orows, oslabs, s);
-  return launch_gemm<BN, MODE, EPI_PLAIN, false, CG>(tmA, tmB, p, orows, oslabs, s);
+  if (p.residual) return launch_gemm<BN, MODE, EPI_PLAIN, true, CG, F16>(tmA, tmB, p, orows, oslabs, s);
+  return launch_gemm<BN, MODE, EPI_PLAIN, false, CG, F16>(tmA, tmB, p, orows, oslabs, s);
 }
 
-template <int MODE, int CG>
-int dispatch_gemm(int bn, bool geglu, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
-                  int64_t orows, int64_t oslabs, cudaStream_t s) {
+template <int MODE, int CG, bool F16>
+int dispatch_gemm_t(int bn, bool geglu, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
+                    int64_t orows, int64_t oslabs, cudaStream_t s) {
   if (geglu) {
-    if (bn == 256) return launch_gemm<256, MODE, EPI_GEGLU_T, false, CG>(tmA, tmB, p, orows, oslabs, s);
+    if (bn == 256) return launch_gemm<256, MODE, EPI_GEGLU_T, false, CG, F16>(tmA, tmB, p, orows, oslabs, s);
     return fail(B2V_ERR_ARG, "GEGLU epilogue needs N %% 256 == 0");
   }
   switch (bn) {
-    case 256: return launch_plain<256, MODE, CG>(tmA, tmB, p, orows, oslabs, s);
-    case 160: return launch_plain<160, MODE, CG>(tmA, tmB, p, orows, oslabs, s);
-    case 128: return launch_plain<128, MODE, CG>(tmA, tmB, p, orows, oslabs, s);
-    case 64: return launch_plain<64, MODE, CG>(tmA, tmB, p, orows, oslabs, s);
+    case 256: return launch_plain<256, MODE, CG, F16>(tmA, tmB, p, orows, oslabs, s);
+    case 160: return launch_plain<160, MODE, CG, F16>(tmA, tmB, p, orows, oslabs, s);
+    case 128: return launch_plain<128, MODE, CG, F16>(tmA, tmB, p, orows, oslabs, s);
+    case 64: return launch_plain<64, MODE, CG, F16>(tmA, tmB, p, orows, oslabs, s);
   }
   return fail(B2V_ERR_ARG, "no tile for N");
+}
+
+// adt: activation / weight element type of this call (B2V_BF16 or B2V_F16)
+template <int MODE, int CG>
+int dispatch_gemm(int adt, int bn, bool geglu, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
+                  int64_t orows, int64_t oslabs, cudaStream_t s) {
+  if (adt == B2V_F16) return dispatch_gemm_t<MODE, CG, true>(bn, geglu, tmA, tmB, p, orows, oslabs, s);
+  return dispatch_gemm_t<MODE, CG, false>(bn, geglu, tmA, tmB, p, orows, oslabs, s);
 }
 
 // CTA pairs (256-row units, each CTA stages its own A rows and half of B) win or tie on every shape of the census since
@@ -658,6 +666,7 @@ int gemm_tiled(const GemmArgs& g, cudaStream_t s) {
             g.Kc, g.taps, g.flags, g.residual != nullptr, (long long)g.rows_per_batch, (long long)g.tap_row_stride);
   const bool geglu = (g.flags & B2V_EPI_GEGLU) != 0;
   B2V_CHECK(g.Kc % BK == 0 && g.Kc > 0, "GEMM Kc=%d must be a multiple of 64", g.Kc);
+  B2V_CHECK(act_ok(g.adt), "GEMM: activation dtype must be bf16 or fp16");
   B2V_CHECK(g.taps == 1 || g.taps == 3, "tiled GEMM supports 1 or 3 taps");
   B2V_CHECK(!(geglu && (g.residual || g.rowbias)), "the GEGLU epilogue takes no residual / row bias");
   const int64_t rpb = g.rows_per_batch > 0 ? g.rows_per_batch : g.M;
@@ -690,12 +699,12 @@ int gemm_tiled(const GemmArgs& g, cudaStream_t s) {
   p.num_m_units = (int)(slabs * p.m_units_per_batch);
   p.num_n_tiles = g.N / bn;
   p.bias = g.bias; p.rowbias = g.rowbias; p.rows_per_group = g.rows_per_group > 0 ? g.rows_per_group : 1;
-  p.residual = (const __nv_bfloat16*)g.residual;
-  p.out = (__nv_bfloat16*)g.out;
+  p.residual = g.residual;
+  p.out = g.out;
   p.ldo = g.ldo > 0 ? g.ldo : (geglu ? g.N / 2 : g.N);
   p.gelu = (g.flags & B2V_EPI_GELU) ? 1 : 0;
-  if (cg == 2) return dispatch_gemm<0, 2>(bn, geglu, tmA, tmB, p, rpb, slabs, s);
-  return dispatch_gemm<0, 1>(bn, geglu, tmA, tmB, p, rpb, slabs, s);
+  if (cg == 2) return dispatch_gemm<0, 2>(g.adt, bn, geglu, tmA, tmB, p, rpb, slabs, s);
+  return dispatch_gemm<0, 1>(g.adt, bn, geglu, tmA, tmB, p, rpb, slabs, s);
 }
 
 // 3x3 / pad 1 / stride {1,2} convolution over NHWC through the TMA im2col path.
@@ -703,6 +712,7 @@ int conv3x3_im2col(const ConvArgs& c, cudaStream_t s) {
   if (trace_on())
     fprintf(stderr, "B2VTRACE conv N=%d H=%d W=%d Cin=%d Cout=%d stride=%d\n", c.N, c.H, c.W, c.Cin, c.Cout, c.stride);
   B2V_CHECK(c.Cin % BK == 0, "conv Cin=%d must be a multiple of 64", c.Cin);
+  B2V_CHECK(act_ok(c.adt), "conv: activation dtype must be bf16 or fp16");
   B2V_CHECK(c.stride == 1 || c.stride == 2, "conv stride must be 1 or 2");
   const int P = (c.H - 1) / c.stride + 1, Q = (c.W - 1) / c.stride + 1;
   const int64_t m_tiles = ((int64_t)c.N * P * Q + BM - 1) / BM;
@@ -733,8 +743,8 @@ int conv3x3_im2col(const ConvArgs& c, cudaStream_t s) {
   p.num_n_tiles = c.Cout / bn;
   p.P = P; p.Q = Q; p.conv_stride = c.stride;
   p.bias = c.bias; p.rowbias = c.rowbias; p.rows_per_group = c.rows_per_group > 0 ? c.rows_per_group : 1;
-  p.residual = (const __nv_bfloat16*)c.residual;
-  p.out = (__nv_bfloat16*)c.out;
+  p.residual = c.residual;
+  p.out = c.out;
   p.ldo = c.Cout;
   p.gelu = 0;
   if (c.ncfhw_out) {
@@ -743,10 +753,11 @@ int conv3x3_im2col(const ConvArgs& c, cudaStream_t s) {
               "conv NCFHW epilogue: needs a 64-row padded weight, <= 16 real channels, stride 1");
     p.out_raw = c.ncfhw_out; p.nc_dtype = c.ncfhw_dtype; p.nc_cout = c.ncfhw_cout; p.nc_F = c.ncfhw_F;
     p.nc_HW = (int64_t)P * Q;
-    return launch_gemm<64, 1, EPI_NCFHW, false, 1>(tmA, tmB, p, p.M, 1, s);
+    if (c.adt == B2V_F16) return launch_gemm<64, 1, EPI_NCFHW, false, 1, true>(tmA, tmB, p, p.M, 1, s);
+    return launch_gemm<64, 1, EPI_NCFHW, false, 1, false>(tmA, tmB, p, p.M, 1, s);
   }
-  if (cg == 2) return dispatch_gemm<1, 2>(bn, false, tmA, tmB, p, p.M, 1, s);
-  return dispatch_gemm<1, 1>(bn, false, tmA, tmB, p, p.M, 1, s);
+  if (cg == 2) return dispatch_gemm<1, 2>(c.adt, bn, false, tmA, tmB, p, p.M, 1, s);
+  return dispatch_gemm<1, 1>(c.adt, bn, false, tmA, tmB, p, p.M, 1, s);
 }
 
 }  // namespace b2v

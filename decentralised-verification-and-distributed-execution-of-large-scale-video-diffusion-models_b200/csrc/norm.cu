@@ -27,6 +27,7 @@ __device__ __forceinline__ uint4 gn_load(const __nv_bfloat16* __restrict__ x1, i
   return __ldg(reinterpret_cast<const uint4*>(x2 + grow * C2 + (c - C1)));
 }
 
+template <bool F16>
 __global__ void __launch_bounds__(GN_MAX_THREADS)
 gn_stats_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat16* __restrict__ x2, int C2,
                 int64_t rows_per_item, int groups, int rpp, float* __restrict__ partial /*[item][split][group][2]*/) {
@@ -56,7 +57,7 @@ gn_stats_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat1
       const uint32_t uu[4] = {u[k].x, u[k].y, u[k].z, u[k].w};
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const float2 f = unpack_bf16x2(uu[j]);
+        const float2 f = unpack_act2<F16>(uu[j]);
         s[j] += f.x + f.y;
         ss[j] += f.x * f.x + f.y * f.y;
       }
@@ -136,6 +137,7 @@ __device__ __forceinline__ float silu_fast(float x) {
 
 // pass 2: y = x * scale + shift with scale = rstd*gamma, shift = beta - mean*rstd*gamma folded once per thread
 // (a thread owns one fixed 8-channel vector and walks rows), optional SiLU. Same mapping / grid as the stats pass.
+template <bool F16>
 __global__ void __launch_bounds__(GN_MAX_THREADS)
 gn_apply_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat16* __restrict__ x2, int C2,
                 const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
@@ -179,7 +181,7 @@ gn_apply_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat1
         float f[8];
 #pragma unroll
         for (int j = 0; j < 4; ++j) {
-          const float2 t = unpack_bf16x2(uu[j]);
+          const float2 t = unpack_act2<F16>(uu[j]);
           f[2 * j] = fmaf(t.x, sc[2 * j], sh[2 * j]);
           f[2 * j + 1] = fmaf(t.y, sc[2 * j + 1], sh[2 * j + 1]);
         }
@@ -188,8 +190,8 @@ gn_apply_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat1
           for (int j = 0; j < 8; ++j) f[j] = silu_fast(f[j]);
         }
         uint4 o;
-        o.x = pack_bf16x2(f[0], f[1]); o.y = pack_bf16x2(f[2], f[3]);
-        o.z = pack_bf16x2(f[4], f[5]); o.w = pack_bf16x2(f[6], f[7]);
+        o.x = pack_act2<F16>(f[0], f[1]); o.y = pack_act2<F16>(f[2], f[3]);
+        o.z = pack_act2<F16>(f[4], f[5]); o.w = pack_act2<F16>(f[6], f[7]);
         *reinterpret_cast<uint4*>(y + (base + rr) * C + c) = o;
       }
     }
@@ -199,7 +201,7 @@ gn_apply_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat1
 // ---------------- LayerNorm: LPR lanes per row, V 16-byte vectors per lane, row cached in registers ----------------
 // A warp handles 32/LPR rows at once; lane l of a row group loads vectors l, l+LPR, ... (each load instruction reads
 // LPR*16 contiguous bytes per row: full sectors, every lane busy, V independent loads in flight per lane).
-template <int LPR, int V>
+template <int LPR, int V, bool F16>
 __global__ void __launch_bounds__(256)
 layer_norm_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__ gamma, const float* __restrict__ beta,
                   __nv_bfloat16* __restrict__ y, int64_t rows, int C, float eps) {
@@ -224,7 +226,7 @@ layer_norm_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__
       const uint32_t uu[4] = {u[i].x, u[i].y, u[i].z, u[i].w};
 #pragma unroll
       for (int j = 0; j < 4; ++j) {
-        const float2 t = unpack_bf16x2(uu[j]);
+        const float2 t = unpack_act2<F16>(uu[j]);
         f[i][2 * j] = t.x; f[i][2 * j + 1] = t.y;
         s += t.x + t.y;
       }
@@ -252,8 +254,8 @@ layer_norm_kernel(const __nv_bfloat16* __restrict__ x, const float* __restrict__
 #pragma unroll
         for (int j = 0; j < 8; ++j) o[j] = (f[i][j] - mean) * rstd * gm[j] + bt[j];
         uint4 w;
-        w.x = pack_bf16x2(o[0], o[1]); w.y = pack_bf16x2(o[2], o[3]);
-        w.z = pack_bf16x2(o[4], o[5]); w.w = pack_bf16x2(o[6], o[7]);
+        w.x = pack_act2<F16>(o[0], o[1]); w.y = pack_act2<F16>(o[2], o[3]);
+        w.z = pack_act2<F16>(o[4], o[5]); w.w = pack_act2<F16>(o[6], o[7]);
         *reinterpret_cast<uint4*>(y + r * C + c) = w;
       }
     }
@@ -368,9 +370,10 @@ size_t group_norm_scratch_bytes(int64_t n_items, int64_t rows_per_item, int grou
   return ((partial + 255) & ~(size_t)255) + sizeof(float2) * (size_t)n_items * groups;
 }
 
-int group_norm(const void* x1, int C1, const void* x2, int C2, const float* gamma, const float* beta, void* y,
-               int64_t n_items, int64_t rows_per_item, int groups, float eps, int silu, void* scratch,
-               cudaStream_t s) {
+template <bool F16>
+static int group_norm_t(const void* x1, int C1, const void* x2, int C2, const float* gamma, const float* beta, void* y,
+                        int64_t n_items, int64_t rows_per_item, int groups, float eps, int silu, void* scratch,
+                        cudaStream_t s) {
   const int C = C1 + C2;
   B2V_CHECK(C % 8 == 0 && C1 % 8 == 0 && C % groups == 0 && (C / groups) % 2 == 0, "group_norm: C=%d (C1=%d) groups=%d unsupported", C, C1, groups);
   B2V_CHECK(C <= GN_MAX_THREADS * 8, "group_norm: C=%d too wide (max %d)", C, GN_MAX_THREADS * 8);
@@ -379,17 +382,17 @@ int group_norm(const void* x1, int C1, const void* x2, int C2, const float* gamm
   const int rpp = gn_rpp(C);
   const int threads = (C >> 3) * rpp;
   const size_t shb = sizeof(float) * 2 * rpp * (C >> 1);
-  const int s1 = resident_slots(gn_stats_kernel, threads, shb), s2 = resident_slots(gn_apply_kernel, threads, 0);
+  const int s1 = resident_slots(gn_stats_kernel<F16>, threads, shb), s2 = resident_slots(gn_apply_kernel<F16>, threads, 0);
   const int splits = gn_splits(n_items, rows_per_item, s1 < s2 ? s1 : s2);
   float* partial = (float*)scratch;
   const size_t pbytes = sizeof(float) * 2 * (size_t)n_items * splits * groups;
   B2V_CHECK(pbytes + 256 + sizeof(float2) * (size_t)n_items * groups <= group_norm_scratch_bytes(n_items, rows_per_item, groups) + 256,
             "group_norm: scratch too small for %d splits", splits);
   dim3 grid((unsigned)splits, (unsigned)n_items);
-  B2V_CUDA_OK(launch_pdl(gn_stats_kernel, grid, dim3(threads), shb, s, (const __nv_bfloat16*)x1, C1,
+  B2V_CUDA_OK(launch_pdl(gn_stats_kernel<F16>, grid, dim3(threads), shb, s, (const __nv_bfloat16*)x1, C1,
                          (const __nv_bfloat16*)x2, C2, rows_per_item, groups, rpp, partial));
   count_launch();
-  B2V_CUDA_OK(launch_pdl(gn_apply_kernel, grid, dim3(threads), 0, s, (const __nv_bfloat16*)x1, C1,
+  B2V_CUDA_OK(launch_pdl(gn_apply_kernel<F16>, grid, dim3(threads), 0, s, (const __nv_bfloat16*)x1, C1,
                          (const __nv_bfloat16*)x2, C2, gamma, beta, (__nv_bfloat16*)y, rows_per_item, groups, rpp, silu,
                          (const float*)partial, (double)rows_per_item * (double)(C / groups), eps));
   count_launch();
@@ -397,8 +400,17 @@ int group_norm(const void* x1, int C1, const void* x2, int C2, const float* gamm
   return 0;
 }
 
-int layer_norm(const void* x, const float* gamma, const float* beta, void* y, int64_t rows, int C, float eps,
+int group_norm(int adt, const void* x1, int C1, const void* x2, int C2, const float* gamma, const float* beta, void* y,
+               int64_t n_items, int64_t rows_per_item, int groups, float eps, int silu, void* scratch,
                cudaStream_t s) {
+  B2V_DISPATCH_ACT(adt, F16, return group_norm_t<F16>(x1, C1, x2, C2, gamma, beta, y, n_items, rows_per_item, groups, eps,
+                                                      silu, scratch, s));
+  return 0;
+}
+
+template <bool F16>
+static int layer_norm_t(const void* x, const float* gamma, const float* beta, void* y, int64_t rows, int C, float eps,
+                        cudaStream_t s) {
   B2V_CHECK(C % 64 == 0 && C <= 2048 && rows > 0, "layer_norm: C=%d unsupported (multiple of 64, <= 2048)", C);
   const int vecs = C >> 3;
   // lanes per row x vectors per lane = vecs, with <= 8 vectors per lane and every lane of the warp busy
@@ -409,9 +421,9 @@ int layer_norm(const void* x, const float* gamma, const float* beta, void* y, in
   const int64_t warps = (rows + (32 / lpr) - 1) / (32 / lpr);
 #define B2V_LN(L, V)                                                                                                 \
   if (lpr == L && v == V) {                                                                                          \
-    const int grid = grid_resident(layer_norm_kernel<L, V>, warps * 32, 256);                                        \
-    B2V_CUDA_OK(launch_pdl(layer_norm_kernel<L, V>, dim3(grid), dim3(256), 0, s, (const __nv_bfloat16*)x, gamma, beta,    \
-                           (__nv_bfloat16*)y, rows, C, eps));                                                         \
+    const int grid = grid_resident(layer_norm_kernel<L, V, F16>, warps * 32, 256);                                   \
+    B2V_CUDA_OK(launch_pdl(layer_norm_kernel<L, V, F16>, dim3(grid), dim3(256), 0, s, (const __nv_bfloat16*)x, gamma,   \
+                           beta, (__nv_bfloat16*)y, rows, C, eps));                                                   \
     launched = true;                                                                                                 \
   }
   bool launched = false;
@@ -422,6 +434,12 @@ int layer_norm(const void* x, const float* gamma, const float* beta, void* y, in
   if (!launched) return fail(B2V_ERR_ARG, "layer_norm: C=%d (lanes %d x vectors %d) not instantiated", C, lpr, v);
   count_launch();
   B2V_CUDA_OK(launch_check());
+  return 0;
+}
+
+int layer_norm(int adt, const void* x, const float* gamma, const float* beta, void* y, int64_t rows, int C, float eps,
+               cudaStream_t s) {
+  B2V_DISPATCH_ACT(adt, F16, return layer_norm_t<F16>(x, gamma, beta, y, rows, C, eps, s));
   return 0;
 }
 

@@ -281,10 +281,13 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
   d |= (uint64_t)2 << 61;                        // SWIZZLE_128B
   return d;
 }
-// instruction descriptor: bf16 x bf16 -> f32, both operands K-major, M x N tile
-__host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) {
-  return (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(N >> 3) << 17) | ((uint32_t)(M >> 4) << 24);
+// instruction descriptor of kind::f16: fp32 accumulator (bits [4,6) = 1), A format bits [7,10) and B format bits
+// [10,13) (0 = fp16, 1 = bf16), both operands K-major, M x N tile
+__host__ __device__ constexpr uint32_t umma_idesc_16(int M, int N, bool a_f16, bool b_f16) {
+  return (1u << 4) | ((a_f16 ? 0u : 1u) << 7) | ((b_f16 ? 0u : 1u) << 10) | ((uint32_t)(N >> 3) << 17) |
+         ((uint32_t)(M >> 4) << 24);
 }
+__host__ __device__ constexpr uint32_t umma_idesc_bf16(int M, int N) { return umma_idesc_16(M, N, false, false); }
 
 // Packed fp32 pairs (Blackwell FFMA2 / FADD2: two lanes of fp32 per instruction on the FMA pipe).
 __device__ __forceinline__ uint64_t pack2(float a, float b) {

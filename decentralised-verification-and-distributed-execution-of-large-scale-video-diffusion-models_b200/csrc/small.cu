@@ -43,8 +43,8 @@ __global__ void timestep_sinusoid_kernel(const float* __restrict__ t_dev, int di
 
 // NCFHW (io dtype) -> channels-last bf16 rows [B*F*HW, Cpad] (channels >= Cin are zero): the tensor-core conv_in reads
 // the latent as a 64-channel image. One thread per (pixel, 8-channel vector): 16-byte coalesced stores.
-template <typename T>
-__global__ void ncfhw_to_rows_kernel(const T* __restrict__ x, __nv_bfloat16* __restrict__ y, int B, int Cin, int F,
+template <typename T, bool F16>
+__global__ void ncfhw_to_rows_kernel(const T* __restrict__ x, uint16_t* __restrict__ y, int B, int Cin, int F,
                                      int64_t HW, int Cpad) {
   const int vecs = Cpad >> 3;
   const int64_t total = (int64_t)B * F * HW * vecs;
@@ -61,16 +61,16 @@ __global__ void ncfhw_to_rows_kernel(const T* __restrict__ x, __nv_bfloat16* __r
       e[j] = ci < Cin ? DT<T>::ld(x + ((b * Cin + ci) * F + f) * HW + pix) : 0.f;
     }
     uint4 o;
-    o.x = pack_bf16x2(e[0], e[1]); o.y = pack_bf16x2(e[2], e[3]);
-    o.z = pack_bf16x2(e[4], e[5]); o.w = pack_bf16x2(e[6], e[7]);
+    o.x = pack_act2<F16>(e[0], e[1]); o.y = pack_act2<F16>(e[2], e[3]);
+    o.z = pack_act2<F16>(e[4], e[5]); o.w = pack_act2<F16>(e[6], e[7]);
     reinterpret_cast<uint4*>(y)[i] = o;
   }
 }
 
-template <typename T>
-__global__ void to_bf16_kernel(const T* __restrict__ x, __nv_bfloat16* __restrict__ y, int64_t n) {
+template <typename T, bool F16>
+__global__ void to_act_kernel(const T* __restrict__ x, uint16_t* __restrict__ y, int64_t n) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    y[i] = __float2bfloat16_rn(DT<T>::ld(x + i));
+    y[i] = to_act<F16>(DT<T>::ld(x + i));
 }
 
 __global__ void set_scalar_kernel(float* dst, float v) { *dst = v; }
@@ -113,25 +113,27 @@ int time_embedding(const float* timestep_dev, int B, int dim0, const float* w1, 
   return 0;
 }
 
-int ncfhw_to_rows(const void* x, int io_dtype, void* y, int B, int Cin, int F, int64_t HW, int Cpad, cudaStream_t s) {
+int ncfhw_to_rows(const void* x, int io_dtype, void* y, int adt, int B, int Cin, int F, int64_t HW, int Cpad,
+                  cudaStream_t s) {
   B2V_CHECK(Cpad % 8 == 0 && Cin <= Cpad, "ncfhw_to_rows: bad channels %d -> %d", Cin, Cpad);
   const int64_t total = (int64_t)B * F * HW * (Cpad >> 3);
   int64_t grid = (total + 255) / 256;
   const int64_t cap = (int64_t)sm_count() * 16;
   if (grid > cap) grid = cap;
-  B2V_DISPATCH_DTYPE(io_dtype, T, (ncfhw_to_rows_kernel<T><<<(unsigned)grid, 256, 0, s>>>((const T*)x, (__nv_bfloat16*)y, B,
-                                                                                     Cin, F, HW, Cpad)));
+  B2V_DISPATCH_ACT(adt, F16, B2V_DISPATCH_DTYPE(io_dtype, T, (ncfhw_to_rows_kernel<T, F16><<<(unsigned)grid, 256, 0, s>>>(
+                                                                  (const T*)x, (uint16_t*)y, B, Cin, F, HW, Cpad))));
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;
 }
 
-int to_bf16(const void* x, int dtype, void* y, int64_t n, cudaStream_t s) {
+int convert_to_act(const void* x, int dtype, void* y, int adt, int64_t n, cudaStream_t s) {
   int64_t grid = (n + 255) / 256;
   const int64_t cap = (int64_t)sm_count() * 8;
   if (grid > cap) grid = cap;
   if (grid < 1) grid = 1;
-  B2V_DISPATCH_DTYPE(dtype, T, (to_bf16_kernel<T><<<(unsigned)grid, 256, 0, s>>>((const T*)x, (__nv_bfloat16*)y, n)));
+  B2V_DISPATCH_ACT(adt, F16, B2V_DISPATCH_DTYPE(dtype, T, (to_act_kernel<T, F16><<<(unsigned)grid, 256, 0, s>>>(
+                                                               (const T*)x, (uint16_t*)y, n))));
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;

@@ -4,6 +4,8 @@
 #include <cuda_runtime.h>
 #include <stdint.h>
 
+#include "../../include/b2v.h"
+
 namespace b2v {
 
 // bf16 tensor, 128-byte swizzle, zero fill out of bounds.
@@ -17,7 +19,8 @@ int tmap_im2col_bf16(CUtensorMap* out, const void* base, int rank, const uint64_
                      const uint32_t* elem_strides);
 
 struct GemmArgs {
-  const void* a = nullptr;  // bf16 [M, lda]
+  int adt = B2V_BF16;       // element type of a / w / residual / out: B2V_BF16 or B2V_F16
+  const void* a = nullptr;  // [M, lda]
   int64_t lda = 0;          // 0 -> Kc
   const void* w = nullptr;  // bf16 [N, taps*Kc]
   const float* bias = nullptr;
@@ -36,7 +39,8 @@ struct GemmArgs {
 };
 
 struct ConvArgs {
-  const void* x = nullptr;  // bf16 NHWC
+  int adt = B2V_BF16;       // element type of x / w / residual / out: B2V_BF16 or B2V_F16
+  const void* x = nullptr;  // NHWC
   const void* w = nullptr;  // bf16 [Cout][3][3][Cin]
   const float* bias = nullptr;
   const float* rowbias = nullptr;

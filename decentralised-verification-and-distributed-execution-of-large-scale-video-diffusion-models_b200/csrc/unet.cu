@@ -3,10 +3,11 @@
 // Distribution/strategies/chunk_only.py:71, fsdp_chunked_coherent.py:140 and InferNet/neurons/miner.py:581
 // ([UPSTREAM diffusers] UNet3DConditionModel, Zeroscope / ModelScope-T2V configuration; module list in
 // SURVEY.md §8a U1-U8). Weights arrive under their diffusers state_dict names and are repacked once:
-//   * every GEMM operand to bf16, K-major [N][K]; conv kernels to [Cout][tap][Cin]
+//   * every GEMM operand to the handle's activation dtype (bf16, or fp16 = the reference's torch_dtype), K-major [N][K];
+//     conv kernels to [Cout][tap][Cin]
 //   * q/k/v projections fused into one [3C][C] operand; GEGLU value/gate rows interleaved per 128 columns
 //   * biases, norm affines, the time MLP and conv_in/conv_out stay fp32
-// Activations are channels-last bf16 rows [(b,f,y,x), C]; the (b f) c h w <-> b c f h w permutes of the
+// Activations are channels-last 2-byte rows [(b,f,y,x), C]; the (b f) c h w <-> b c f h w permutes of the
 // reference vanish because temporal ops address frames by a row stride.
 #include <map>
 #include <memory>
@@ -20,7 +21,7 @@
 namespace b2v {
 namespace {
 
-typedef __nv_bfloat16 bf16;
+typedef uint16_t bf16;  // opaque 2-byte activation / operand element: bf16 or fp16 bits, per the handle's act_dtype
 
 // ------------------------------------------------------------------------------------------------
 // weight packing kernels
@@ -30,22 +31,24 @@ __global__ void cast_to_f32_kernel(const TI* __restrict__ in, float* __restrict_
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
     out[i] = DT<TI>::ld(in + i);
 }
-__global__ void f32_to_bf16_kernel(const float* __restrict__ in, bf16* __restrict__ out, int64_t n) {
+template <bool F16>
+__global__ void f32_to_act_kernel(const float* __restrict__ in, bf16* __restrict__ out, int64_t n) {
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x)
-    out[i] = __float2bfloat16_rn(in[i]);
+    out[i] = to_act<F16>(in[i]);
 }
 // [Cout][Cin][taps] -> [Cout][taps][Cin]
-template <typename TO>
-__global__ void permute_taps_kernel(const float* __restrict__ in, TO* __restrict__ out, int Cout, int Cin, int taps) {
+template <bool F16>
+__global__ void permute_taps_kernel(const float* __restrict__ in, bf16* __restrict__ out, int Cout, int Cin, int taps) {
   const int64_t n = (int64_t)Cout * Cin * taps;
   for (int64_t i = (int64_t)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.x * blockDim.x) {
     const int ci = (int)(i % Cin);
     const int tap = (int)((i / Cin) % taps);
     const int co = (int)(i / ((int64_t)Cin * taps));
-    DT<TO>::st(out + i, in[((int64_t)co * Cin + ci) * taps + tap]);
+    out[i] = to_act<F16>(in[((int64_t)co * Cin + ci) * taps + tap]);
   }
 }
-// [Cout][Cin][taps] fp32 -> [CoutPad][taps][CinPad] bf16, zero padded (conv_in: Cin 4 -> 64; conv_out: Cout 4 -> 64)
+// [Cout][Cin][taps] fp32 -> [CoutPad][taps][CinPad], zero padded (conv_in: Cin 4 -> 64; conv_out: Cout 4 -> 64)
+template <bool F16>
 __global__ void permute_taps_pad_kernel(const float* __restrict__ in, bf16* __restrict__ out, int Cout, int Cin,
                                         int taps, int CoutPad, int CinPad) {
   const int64_t n = (int64_t)CoutPad * CinPad * taps;
@@ -54,12 +57,13 @@ __global__ void permute_taps_pad_kernel(const float* __restrict__ in, bf16* __re
     const int tap = (int)((i / CinPad) % taps);
     const int co = (int)(i / ((int64_t)CinPad * taps));
     const float v = (co < Cout && ci < Cin) ? in[((int64_t)co * Cin + ci) * taps + tap] : 0.f;
-    out[i] = __float2bfloat16_rn(v);
+    out[i] = to_act<F16>(v);
   }
 }
 // GEGLU: proj.weight rows [0,H) are the value half, [H,2H) the gate half (H = 4*dim).
 // packed row j*256 + i       (i < 128) = value row j*128 + i
 // packed row j*256 + 128 + i (i < 128) = gate  row j*128 + i
+template <bool F16>
 __global__ void pack_geglu_kernel(const float* __restrict__ w, const float* __restrict__ b, bf16* __restrict__ wo,
                                   float* __restrict__ bo, int H, int K) {
   const int64_t n = (int64_t)2 * H * K;
@@ -68,7 +72,7 @@ __global__ void pack_geglu_kernel(const float* __restrict__ w, const float* __re
     const int r = (int)(i / K);
     const int tile = r / 256, within = r % 256;
     const int src = within < 128 ? tile * 128 + within : H + tile * 128 + (within - 128);
-    wo[i] = __float2bfloat16_rn(w[(int64_t)src * K + k]);
+    wo[i] = to_act<F16>(w[(int64_t)src * K + k]);
     if (k == 0) bo[r] = b[src];
   }
 }
@@ -178,6 +182,7 @@ using namespace b2v;
 
 struct b2v_unet3d {
   b2v_unet3d_config cfg;
+  int adt = B2V_BF16;  // activation / GEMM-operand element type of this handle (cfg.act_dtype)
   int device = 0;
   bool finalized = false;
   int64_t param_count = 0;
@@ -223,6 +228,7 @@ struct Loader {
   b2v_unet3d* u;
   std::string err;
   cudaStream_t s = 0;
+  bool f16() const { return u->adt == B2V_F16; }
 
   template <typename T>
   T* dalloc(size_t n) {
@@ -258,7 +264,10 @@ struct Loader {
   }
   bf16* mat_bf16(const float* src, int64_t n) {
     bf16* d = dalloc<bf16>((size_t)n);
-    if (d && src) f32_to_bf16_kernel<<<ew_grid(n), 256, 0, s>>>(src, d, n);
+    if (d && src) {
+      if (f16()) f32_to_act_kernel<true><<<ew_grid(n), 256, 0, s>>>(src, d, n);
+      else f32_to_act_kernel<false><<<ew_grid(n), 256, 0, s>>>(src, d, n);
+    }
     return d;
   }
   Lin lin(const std::string& p, int N, int K, bool bias) {
@@ -274,7 +283,11 @@ struct Loader {
     l.w = dalloc<bf16>((size_t)l.N * K);
     for (size_t i = 0; i < names.size(); ++i) {
       const float* w = get(names[i] + ".weight", {Neach, K});
-      if (w && l.w) f32_to_bf16_kernel<<<ew_grid((int64_t)Neach * K), 256, 0, s>>>(w, l.w + i * (size_t)Neach * K, (int64_t)Neach * K);
+      if (w && l.w) {
+        const int64_t n = (int64_t)Neach * K;
+        if (f16()) f32_to_act_kernel<true><<<ew_grid(n), 256, 0, s>>>(w, l.w + i * (size_t)n, n);
+        else f32_to_act_kernel<false><<<ew_grid(n), 256, 0, s>>>(w, l.w + i * (size_t)n, n);
+      }
     }
     return l;
   }
@@ -285,14 +298,20 @@ struct Loader {
     const float* b = get(p + ".bias", {2 * H});
     l.w = dalloc<bf16>((size_t)2 * H * dim);
     l.b = dalloc<float>((size_t)2 * H);
-    if (w && b && l.w && l.b) pack_geglu_kernel<<<ew_grid((int64_t)2 * H * dim), 256, 0, s>>>(w, b, l.w, l.b, H, dim);
+    if (w && b && l.w && l.b) {
+      if (f16()) pack_geglu_kernel<true><<<ew_grid((int64_t)2 * H * dim), 256, 0, s>>>(w, b, l.w, l.b, H, dim);
+      else pack_geglu_kernel<false><<<ew_grid((int64_t)2 * H * dim), 256, 0, s>>>(w, b, l.w, l.b, H, dim);
+    }
     return l;
   }
   Conv conv3x3(const std::string& p, int Cout, int Cin) {
     Conv c; c.Cout = Cout; c.Cin = Cin;
     const float* w = get(p + ".weight", {Cout, Cin, 3, 3});
     c.w = dalloc<bf16>((size_t)Cout * Cin * 9);
-    if (w && c.w) permute_taps_kernel<bf16><<<ew_grid((int64_t)Cout * Cin * 9), 256, 0, s>>>(w, c.w, Cout, Cin, 9);
+    if (w && c.w) {
+      if (f16()) permute_taps_kernel<true><<<ew_grid((int64_t)Cout * Cin * 9), 256, 0, s>>>(w, c.w, Cout, Cin, 9);
+      else permute_taps_kernel<false><<<ew_grid((int64_t)Cout * Cin * 9), 256, 0, s>>>(w, c.w, Cout, Cin, 9);
+    }
     c.b = vec(p + ".bias", Cout);
     return c;
   }
@@ -307,7 +326,10 @@ struct Loader {
     Lin l; l.N = C; l.K = 3 * C;
     const float* w = get(p + ".weight", {C, C, 3, 1, 1});
     l.w = dalloc<bf16>((size_t)C * C * 3);
-    if (w && l.w) permute_taps_kernel<bf16><<<ew_grid((int64_t)C * C * 3), 256, 0, s>>>(w, l.w, C, C, 3);
+    if (w && l.w) {
+      if (f16()) permute_taps_kernel<true><<<ew_grid((int64_t)C * C * 3), 256, 0, s>>>(w, l.w, C, C, 3);
+      else permute_taps_kernel<false><<<ew_grid((int64_t)C * C * 3), 256, 0, s>>>(w, l.w, C, C, 3);
+    }
     l.b = vec(p + ".bias", C);
     return l;
   }
@@ -405,6 +427,7 @@ void gemm(Ctx& c, const bf16* a, int64_t M, const Lin& l, const bf16* residual, 
   c.flops += 2.0 * (double)M * l.N * l.K;
   if (!c.live()) return;
   GemmArgs g;
+  g.adt = c.u->adt;
   g.a = a; g.lda = lda; g.w = l.w; g.bias = l.b; g.residual = residual; g.out = out;
   g.M = M; g.N = l.N; g.Kc = l.K; g.taps = 1; g.rows_per_batch = M; g.flags = flags;
   c.run(gemm_tiled(g, c.s));
@@ -413,7 +436,7 @@ void gemm(Ctx& c, const bf16* a, int64_t M, const Lin& l, const bf16* residual, 
 void gn(Ctx& c, const bf16* x1, int C1, const bf16* x2, int C2, const Norm& n, bf16* y, int64_t items, int64_t rows_per,
         float eps, int silu) {
   void* stats = c.bytes(group_norm_scratch_bytes(items, rows_per, c.u->cfg.norm_num_groups));
-  if (c.live()) c.run(group_norm(x1, C1, x2, C2, n.g, n.b, y, items, rows_per, c.u->cfg.norm_num_groups, eps, silu, stats, c.s));
+  if (c.live()) c.run(group_norm(c.u->adt, x1, C1, x2, C2, n.g, n.b, y, items, rows_per, c.u->cfg.norm_num_groups, eps, silu, stats, c.s));
   c.free(stats);
 }
 
@@ -423,6 +446,7 @@ void conv(Ctx& c, const bf16* x, int N, int H, int W, const Conv& w, int stride,
   c.flops += 2.0 * (double)N * P * Q * w.Cout * 9.0 * (real_cin ? real_cin : w.Cin);  // algorithmic: padding not counted
   if (!c.live()) return;
   ConvArgs a;
+  a.adt = c.u->adt;
   a.x = x; a.w = w.w; a.bias = w.b; a.rowbias = rowbias; a.rows_per_group = rows_per_group; a.residual = residual;
   a.out = out; a.N = N; a.H = H; a.W = W; a.Cin = w.Cin; a.Cout = w.Cout; a.stride = stride;
   c.run(conv3x3_im2col(a, c.s));
@@ -475,6 +499,7 @@ Act temp_conv(Ctx& c, const TempConvW& t, const Act& x) {
     c.flops += 2.0 * (double)M * t.C * 3.0 * t.C;
     if (c.live()) {
       GemmArgs g;
+      g.adt = c.u->adt;
       g.a = n; g.w = t.c[i].w; g.bias = t.c[i].b; g.residual = (i == 3) ? x.p : nullptr; g.out = o;
       g.M = M; g.N = t.C; g.Kc = t.C; g.taps = 3; g.tap_row_stride = HW; g.rows_per_batch = (int64_t)c.F * HW;
       c.run(gemm_tiled(g, c.s));
@@ -489,7 +514,7 @@ Act temp_conv(Ctx& c, const TempConvW& t, const Act& x) {
 
 void feed_forward(Ctx& c, const BlockW& b, bf16* h, int64_t M) {
   bf16* l = c.act(M, b.dim);
-  if (c.live()) c.run(layer_norm(h, b.ln3.g, b.ln3.b, l, M, b.dim, 1e-5f, c.s));
+  if (c.live()) c.run(layer_norm(c.u->adt, h, b.ln3.g, b.ln3.b, l, M, b.dim, 1e-5f, c.s));
   bf16* g = c.act(M, 4 * b.dim);
   gemm(c, l, M, b.ff1, nullptr, g, B2V_EPI_GEGLU);
   c.free(l);
@@ -510,7 +535,7 @@ Act spatial(Ctx& c, const SpatialW& a, const Act& x) {
   const BlockW& b = a.blk;
   {  // self attention
     bf16* l = c.act(M, C);
-    if (c.live()) c.run(layer_norm(h, b.ln1.g, b.ln1.b, l, M, C, 1e-5f, c.s));
+    if (c.live()) c.run(layer_norm(c.u->adt, h, b.ln1.g, b.ln1.b, l, M, C, 1e-5f, c.s));
     bf16* qkv = c.act(M, 3 * C);
     gemm(c, l, M, b.qkv1, nullptr, qkv);
     c.free(l);
@@ -518,6 +543,7 @@ Act spatial(Ctx& c, const SpatialW& a, const Act& x) {
     c.flops += 4.0 * (double)N * heads * (double)HW * (double)HW * 64.0;
     if (c.live()) {
       AttnArgs t;
+      t.adt = c.u->adt;
       t.q = qkv; t.k = qkv + C; t.v = qkv + 2 * C; t.out = o;
       t.ldq = 3 * C; t.ldkv = 3 * C; t.ldo = C; t.nb = N; t.heads = heads; t.Sq = (int)HW; t.Skv = (int)HW;
       t.kv_group = 1; t.scale = scale;
@@ -530,7 +556,7 @@ Act spatial(Ctx& c, const SpatialW& a, const Act& x) {
   {  // cross attention against the text tokens (K/V depend only on the prompt: B*77 rows, shared by all frames)
     const int TL = c.u->cfg.text_len;
     bf16* l = c.act(M, C);
-    if (c.live()) c.run(layer_norm(h, b.ln2.g, b.ln2.b, l, M, C, 1e-5f, c.s));
+    if (c.live()) c.run(layer_norm(c.u->adt, h, b.ln2.g, b.ln2.b, l, M, C, 1e-5f, c.s));
     bf16* q = c.act(M, C);
     gemm(c, l, M, b.q2, nullptr, q);
     c.free(l);
@@ -540,6 +566,7 @@ Act spatial(Ctx& c, const SpatialW& a, const Act& x) {
     c.flops += 4.0 * (double)N * heads * (double)HW * (double)TL * 64.0;
     if (c.live()) {
       AttnArgs t;
+      t.adt = c.u->adt;
       t.q = q; t.k = kv; t.v = kv + C; t.out = o;
       t.ldq = C; t.ldkv = 2 * C; t.ldo = C; t.nb = N; t.heads = heads; t.Sq = (int)HW; t.Skv = TL;
       t.kv_group = c.F; t.scale = scale;
@@ -573,13 +600,13 @@ Act temporal(Ctx& c, const TemporalW& a, const Act& x) {
     const Lin& qkvw = which == 0 ? b.qkv1 : b.qkv2;
     const Lin& ow = which == 0 ? b.o1 : b.o2;
     bf16* l = c.act(M, D);
-    if (c.live()) c.run(layer_norm(h, ln.g, ln.b, l, M, D, 1e-5f, c.s));
+    if (c.live()) c.run(layer_norm(c.u->adt, h, ln.g, ln.b, l, M, D, 1e-5f, c.s));
     bf16* qkv = c.act(M, 3 * D);
     gemm(c, l, M, qkvw, nullptr, qkv);
     c.free(l);
     bf16* o = c.act(M, D);
     c.flops += 4.0 * (double)c.B * HW * heads * (double)c.F * (double)c.F * 64.0;
-    if (c.live()) c.run(temporal_attention(qkv, 3 * D, 0, D, 2 * D, o, D, c.B, c.F, HW, heads, scale, c.s));
+    if (c.live()) c.run(temporal_attention(c.u->adt, qkv, 3 * D, 0, D, 2 * D, o, D, c.B, c.F, HW, heads, scale, c.s));
     c.free(qkv);
     gemm(c, o, M, ow, h, h);
     c.free(o);
@@ -615,7 +642,7 @@ int forward_impl(b2v_unet3d* u, Ctx& c, int io_dtype, int H, int W) {
   bf16* text = (bf16*)c.bytes((size_t)text_n * 2);
   c.text = text;
   if (c.live()) {
-    c.run(to_bf16(ehs, io_dtype, text, text_n, c.s));
+    c.run(convert_to_act(ehs, io_dtype, text, u->adt, text_n, c.s));
     c.run(time_embedding(u->t_dev, B, C0, u->te_w1, u->te_b1, u->te_w2, u->te_b2, u->temb_dim, u->temb_scratch, c.s));
     for (ResnetW* r : u->all_resnets)
       c.run(small_linear(u->temb_scratch, r->temb_w, r->temb_b, r->rowbias, B, r->Cout, u->temb_dim, c.s));
@@ -624,7 +651,7 @@ int forward_impl(b2v_unet3d* u, Ctx& c, int io_dtype, int H, int W) {
   Act x{c.act((int64_t)N * H * W, C0), (int64_t)N * H * W, C0, H, W};
   {
     bf16* xin = c.act((int64_t)N * H * W, u->conv_in.Cin);
-    if (c.live()) c.run(ncfhw_to_rows(sample, io_dtype, xin, B, cfg.in_channels, F, (int64_t)H * W, u->conv_in.Cin, c.s));
+    if (c.live()) c.run(ncfhw_to_rows(sample, io_dtype, xin, u->adt, B, cfg.in_channels, F, (int64_t)H * W, u->conv_in.Cin, c.s));
     conv(c, xin, N, H, W, u->conv_in, 1, nullptr, 0, nullptr, x.p, cfg.in_channels);
     c.free(xin);
   }
@@ -713,6 +740,7 @@ int forward_impl(b2v_unet3d* u, Ctx& c, int io_dtype, int H, int W) {
   c.flops += 2.0 * (double)N * H * W * cfg.out_channels * 9.0 * C0;
   if (c.live()) {
     ConvArgs a;
+    a.adt = u->adt;
     a.x = hn; a.w = u->conv_out.w; a.bias = u->conv_out.b; a.N = N; a.H = H; a.W = W; a.Cin = C0; a.Cout = u->conv_out.Cout;
     a.stride = 1; a.ncfhw_out = out; a.ncfhw_dtype = io_dtype; a.ncfhw_cout = cfg.out_channels; a.ncfhw_F = F;
     c.run(conv3x3_im2col(a, c.s));
@@ -739,8 +767,10 @@ extern "C" int b2v_unet3d_create(const b2v_unet3d_config* cfg, b2v_unet3d** out)
             "bad config");
   B2V_CHECK(cfg->out_channels >= 1 && cfg->out_channels <= 16 && cfg->in_channels >= 1 && cfg->in_channels <= 64,
             "in/out channels unsupported");
+  B2V_CHECK(cfg->act_dtype == 0 || act_ok(cfg->act_dtype), "act_dtype must be 0 (= bf16), B2V_BF16 or B2V_F16");
   auto* u = new b2v_unet3d();
   u->cfg = *cfg;
+  u->adt = cfg->act_dtype == B2V_F16 ? B2V_F16 : B2V_BF16;
   cudaGetDevice(&u->device);
   u->temb_dim = cfg->block_out_channels[0] * 4;
   if (cudaStreamCreateWithFlags(&u->cap_stream, cudaStreamNonBlocking) != cudaSuccess) {
@@ -779,14 +809,19 @@ extern "C" int b2v_unet3d_load_tensor(b2v_unet3d* u, const char* name, const voi
                       (attr.type == cudaMemoryTypeDevice || attr.type == cudaMemoryTypeManaged);
   cudaGetLastError();
   const void* src = data;
-  if (!on_dev) {
+  if (!on_dev && dtype != B2V_F32) {
     B2V_CUDA_OK(cudaMalloc(&stage, es * (size_t)n));
     B2V_CUDA_OK(cudaMemcpy(stage, data, es * (size_t)n, cudaMemcpyHostToDevice));
     src = stage;
   }
-  B2V_DISPATCH_DTYPE(dtype, T, (cast_to_f32_kernel<T><<<ew_grid(n), 256>>>((const T*)src, dst, n)));
-  count_launch();
-  B2V_CUDA_OK(cudaDeviceSynchronize());
+  if (dtype == B2V_F32) {
+    // fp32 sources (what b2v/unet.py sends) are copied, not cast: no kernel launch per tensor
+    B2V_CUDA_OK(cudaMemcpy(dst, src, sizeof(float) * (size_t)n, cudaMemcpyDefault));
+  } else {
+    B2V_DISPATCH_DTYPE(dtype, T, (cast_to_f32_kernel<T><<<ew_grid(n), 256>>>((const T*)src, dst, n)));
+    count_launch();
+    B2V_CUDA_OK(cudaDeviceSynchronize());
+  }
   if (stage) cudaFree(stage);
   auto it = u->raw.find(name);
   if (it != u->raw.end()) { cudaFree(it->second.first); u->param_count -= 0; }
@@ -810,7 +845,10 @@ extern "C" int b2v_unet3d_finalize(b2v_unet3d* u) {
     u->conv_in.Cout = ch[0]; u->conv_in.Cin = 64;
     u->conv_in.w = L.dalloc<bf16>((size_t)ch[0] * 64 * 9);
     if (w && u->conv_in.w)
-      permute_taps_pad_kernel<<<ew_grid((int64_t)ch[0] * 64 * 9), 256>>>(w, u->conv_in.w, ch[0], cfg.in_channels, 9, ch[0], 64);
+    {
+      if (L.f16()) permute_taps_pad_kernel<true><<<ew_grid((int64_t)ch[0] * 64 * 9), 256>>>(w, u->conv_in.w, ch[0], cfg.in_channels, 9, ch[0], 64);
+      else permute_taps_pad_kernel<false><<<ew_grid((int64_t)ch[0] * 64 * 9), 256>>>(w, u->conv_in.w, ch[0], cfg.in_channels, 9, ch[0], 64);
+    }
     u->conv_in.b = L.vec("conv_in.bias", ch[0]);
     auto mat = [&](const char* nm, int N, int K) {
       const float* s = L.get(nm, {N, K});
@@ -888,7 +926,10 @@ extern "C" int b2v_unet3d_finalize(b2v_unet3d* u) {
     u->conv_out.Cout = 64; u->conv_out.Cin = ch[0];
     u->conv_out.w = L.dalloc<bf16>((size_t)64 * ch[0] * 9);
     if (w && u->conv_out.w)
-      permute_taps_pad_kernel<<<ew_grid((int64_t)64 * ch[0] * 9), 256>>>(w, u->conv_out.w, cfg.out_channels, ch[0], 9, 64, ch[0]);
+    {
+      if (L.f16()) permute_taps_pad_kernel<true><<<ew_grid((int64_t)64 * ch[0] * 9), 256>>>(w, u->conv_out.w, cfg.out_channels, ch[0], 9, 64, ch[0]);
+      else permute_taps_pad_kernel<false><<<ew_grid((int64_t)64 * ch[0] * 9), 256>>>(w, u->conv_out.w, cfg.out_channels, ch[0], 9, 64, ch[0]);
+    }
     u->conv_out.b = L.vec("conv_out.bias", cfg.out_channels);
   }
   cudaError_t e = cudaDeviceSynchronize();

@@ -141,8 +141,8 @@ extern "C" int b2v_op_upsample2x(const void* x_dev, void* y_dev, int N, int H, i
 }
 
 extern "C" int b2v_op_latent_rows(const void* x_dev, int io_dtype, void* rows_dev, int B, int C, int F, int64_t hw, int Cpad,
-                                  void* stream) {
+                                  int act_dtype, void* stream) {
   B2V_CHECK(x_dev && rows_dev && B > 0 && C > 0 && F > 0 && hw > 0, "latent_rows: bad argument");
   B2V_TRY(b2v_device_check());
-  return ncfhw_to_rows(x_dev, io_dtype, rows_dev, B, C, F, hw, Cpad, (cudaStream_t)stream);
+  return ncfhw_to_rows(x_dev, io_dtype, rows_dev, act_dtype, B, C, F, hw, Cpad, (cudaStream_t)stream);
 }

@@ -228,6 +228,15 @@ def spotcheck_ddim(z_list, eps_list, znext_list, a_t, a_prev, C_, F, hw):
 
 
 # ---- building-block ops (tests) --------------------------------------------------------------------------------
+def act_tag(t):
+    """Activation dtype tag of a 2-byte operand tensor: bf16 (default arithmetic) or fp16 (the reference's)."""
+    if t.dtype == torch.float16:
+        return F16
+    if t.dtype == torch.bfloat16:
+        return BF16
+    raise TypeError("activation tensors are bfloat16 or float16, got %s" % t.dtype)
+
+
 def gemm(a, w, bias=None, rowbias=None, rows_per_group=0, residual=None, taps=1, tap_row_stride=0, rows_per_batch=0,
          flags=0, out=None):
     lib = _lib.load()
@@ -237,9 +246,9 @@ def gemm(a, w, bias=None, rowbias=None, rows_per_group=0, residual=None, taps=1,
     assert w.shape[1] == taps * Kc
     n_out = N // 2 if flags & _lib.EPI_GEGLU else N
     if out is None:
-        out = torch.empty((M, n_out), dtype=torch.bfloat16, device=a.device)
+        out = torch.empty((M, n_out), dtype=a.dtype, device=a.device)
     check(lib.b2v_op_gemm(ptr(a), ptr(w), ptr(bias), ptr(rowbias), int(rows_per_group), ptr(residual), ptr(out), M, N,
-                          Kc, taps, int(tap_row_stride), int(rows_per_batch), int(flags), stream()))
+                          Kc, taps, int(tap_row_stride), int(rows_per_batch), int(flags), act_tag(a), stream()))
     return out
 
 
@@ -250,11 +259,11 @@ def conv3x3(x, w, bias=None, rowbias=None, rows_per_group=0, residual=None, stri
     N, H, W, Cin = x.shape
     Cout = w.shape[0]
     P, Q = (H - 1) // stride + 1, (W - 1) // stride + 1
-    out = torch.empty((N, P, Q, Cout), dtype=torch.bfloat16, device=x.device)
+    out = torch.empty((N, P, Q, Cout), dtype=x.dtype, device=x.device)
     sb = lib.b2v_op_conv3x3_scratch_bytes(N, H, W, Cin, stride, mode)
     scratch = torch.empty(max(sb, 1), dtype=torch.uint8, device=x.device)
     check(lib.b2v_op_conv3x3(ptr(x), ptr(w), ptr(bias), ptr(rowbias), int(rows_per_group), ptr(residual), ptr(out), N,
-                             H, W, Cin, Cout, stride, mode, ptr(scratch), stream()))
+                             H, W, Cin, Cout, stride, mode, ptr(scratch), act_tag(x), stream()))
     return out
 
 
@@ -263,11 +272,11 @@ def group_norm(x, gamma, beta, n_items, groups, eps, silu, x2=None):
     _cuda(x)
     rows, C1 = x.shape
     C2 = x2.shape[1] if x2 is not None else 0
-    y = torch.empty((rows, C1 + C2), dtype=torch.bfloat16, device=x.device)
+    y = torch.empty((rows, C1 + C2), dtype=x.dtype, device=x.device)
     stats = torch.empty(lib.b2v_op_group_norm_scratch_bytes(n_items, rows // n_items, groups) + 256, dtype=torch.uint8,
                         device=x.device)
     check(lib.b2v_op_group_norm(ptr(x), C1, ptr(x2), C2, ptr(gamma), ptr(beta), ptr(y), n_items, rows // n_items,
-                                groups, float(eps), int(silu), ptr(stats), stream()))
+                                groups, float(eps), int(silu), ptr(stats), act_tag(x), stream()))
     return y
 
 
@@ -276,7 +285,7 @@ def layer_norm(x, gamma, beta, eps=1e-5):
     _cuda(x)
     rows, Cc = x.shape
     y = torch.empty_like(x)
-    check(lib.b2v_op_layer_norm(ptr(x), ptr(gamma), ptr(beta), ptr(y), rows, Cc, float(eps), stream()))
+    check(lib.b2v_op_layer_norm(ptr(x), ptr(gamma), ptr(beta), ptr(y), rows, Cc, float(eps), act_tag(x), stream()))
     return y
 
 
@@ -285,9 +294,9 @@ def attention(q, k, v, heads, kv_group=1, scale=0.125):
     lib = _lib.load()
     nb, Sq, D = q.shape
     Skv = k.shape[1]
-    out = torch.empty((nb, Sq, D), dtype=torch.bfloat16, device=q.device)
+    out = torch.empty((nb, Sq, D), dtype=q.dtype, device=q.device)
     check(lib.b2v_op_attention(ptr(q), q.stride(1), ptr(k), ptr(v), k.stride(1), ptr(out), D, nb, heads, Sq, Skv,
-                               kv_group, float(scale), stream()))
+                               kv_group, float(scale), act_tag(q), stream()))
     return out
 
 
@@ -295,9 +304,9 @@ def temporal_attention(qkv, B, F, HW, heads, scale=0.125):
     """qkv: [B*F*HW, 3*heads*64] fused rows in (b,f,p) order -> [B*F*HW, heads*64]."""
     lib = _lib.load()
     D = heads * 64
-    out = torch.empty((qkv.shape[0], D), dtype=torch.bfloat16, device=qkv.device)
+    out = torch.empty((qkv.shape[0], D), dtype=qkv.dtype, device=qkv.device)
     check(lib.b2v_op_temporal_attention(ptr(qkv), qkv.shape[1], 0, D, 2 * D, ptr(out), D, B, F, HW, heads,
-                                        float(scale), stream()))
+                                        float(scale), act_tag(qkv), stream()))
     return out
 
 
@@ -331,11 +340,11 @@ def upsample2x(x):
     return y
 
 
-def latent_rows(x, cpad=64):
-    """[B,C,F,h,w] (fp32/fp16/bf16) -> channels-last bf16 rows [B*F*h*w, cpad], channels >= C zero."""
+def latent_rows(x, cpad=64, act_dtype=torch.bfloat16):
+    """[B,C,F,h,w] (fp32/fp16/bf16) -> channels-last rows [B*F*h*w, cpad] of act_dtype, channels >= C zero."""
     lib = _lib.load()
     _cuda(x)
     B, Cc, F, h, w = x.shape
-    y = torch.empty((B * F * h * w, cpad), dtype=torch.bfloat16, device=x.device)
-    check(lib.b2v_op_latent_rows(ptr(x), dtype_tag(x), ptr(y), B, Cc, F, h * w, cpad, stream()))
+    y = torch.empty((B * F * h * w, cpad), dtype=act_dtype, device=x.device)
+    check(lib.b2v_op_latent_rows(ptr(x), dtype_tag(x), ptr(y), B, Cc, F, h * w, cpad, act_tag(y), stream()))
     return y

@@ -167,49 +167,68 @@ class SyntheticTextEncoder:
         return (out.to(self.device, self.dtype),)
 
 
+def unet_arith_dtype(dtype, unet_dtype=None):
+    """Arithmetic dtype of the UNet for a pipeline whose latents are `dtype`: fp16 latents -> fp16 arithmetic (the
+    reference's ``torch_dtype=torch.float16``), anything else -> bf16, unless stated explicitly."""
+    if unet_dtype is not None:
+        return unet_dtype
+    return torch.float16 if dtype == torch.float16 else torch.bfloat16
+
+
 class VideoPipeline:
-    def __init__(self, unet, scheduler, text_dim=1024, dtype=torch.bfloat16, vae=None):
+    def __init__(self, unet, scheduler, text_dim=1024, dtype=torch.bfloat16, vae=None, tokenizer=None,
+                 text_encoder=None):
         self.unet, self.scheduler, self.vae = unet, scheduler, vae
         self.device = unet.device
         self.dtype = dtype
-        self.tokenizer = SyntheticTokenizer()
-        self.text_encoder = SyntheticTextEncoder(text_dim, dtype, self.device)
+        self.tokenizer = tokenizer if tokenizer is not None else SyntheticTokenizer()
+        self.text_encoder = text_encoder if text_encoder is not None else SyntheticTextEncoder(text_dim, dtype, self.device)
+        self.synthetic_text = text_encoder is None
 
     def to(self, *a, **k):
         return self
 
     @classmethod
     def from_random(cls, model_id="cerspense/zeroscope_v2_XL", device="cuda", seed=1234, dtype=torch.bfloat16,
-                    config=None):
+                    config=None, unet_dtype=None):
         cfg = dict(config or KNOWN_MODELS.get(model_id) or ZEROSCOPE_CONFIG)
-        unet = UNet3DConditionModel(cfg, device=device)
+        unet = UNet3DConditionModel(cfg, device=device, dtype=unet_arith_dtype(dtype, unet_dtype))
         unet.load_state_dict(random_state_dict(unet.config.__dict__, unet.device, seed))
         return cls(unet, DDIMScheduler.from_pipeline_config(), text_dim=cfg["cross_attention_dim"], dtype=dtype)
 
     @classmethod
-    def from_pretrained(cls, path, device="cuda", dtype=torch.bfloat16, torch_dtype=None, **_):
+    def from_pretrained(cls, path, device="cuda", dtype=torch.bfloat16, torch_dtype=None, tokenizer=None,
+                        text_encoder=None, allow_synthetic_text=False, unet_dtype=None, **_):
         """The reference's ``TextToVideoSDPipeline.from_pretrained(model_id, torch_dtype=...)`` (chunk_only.py:44-56) for
         a LOCAL diffusers-layout directory: unet (+ vae when present) weights and the scheduler config are read from
-        disk; tokenizer / text encoder stay the synthetic stand-ins unless the caller attaches real ones (the CLIP text
-        tower is outside the accelerated path)."""
+        disk. The CLIP text tower is outside the accelerated path: pass the real ``tokenizer=`` and
+        ``text_encoder=`` (e.g. transformers' CLIPTokenizer / CLIPTextModel loaded from the same folder). Real UNet
+        weights driven by the synthetic stand-in embeddings would silently ignore the prompt, so that combination has
+        to be asked for with ``allow_synthetic_text=True`` (benchmarks, tests)."""
         from . import checkpoint
         from .vae import AutoencoderKL
         if not os.path.isdir(path):
             raise FileNotFoundError("%r is not a local directory (no network: pass a downloaded checkpoint folder)" % (path,))
+        if (tokenizer is None or text_encoder is None) and not allow_synthetic_text:
+            raise ValueError("from_pretrained(%r): no tokenizer= / text_encoder= given. The CLIP text tower is not part of "
+                             "libb2v; with the synthetic stand-in the prompt would be ignored. Pass the real modules, or "
+                             "allow_synthetic_text=True to run on seeded random embeddings on purpose." % (path,))
+        dtype = torch_dtype or dtype
         sd, cfg = checkpoint.read_component(path, "unet")
         ucfg = dict(ZEROSCOPE_CONFIG)
         ucfg.update(checkpoint.unet_config(cfg))
-        unet = UNet3DConditionModel(ucfg, device=device).load_state_dict(sd)
+        unet = UNet3DConditionModel(ucfg, device=device, dtype=unet_arith_dtype(dtype, unet_dtype)).load_state_dict(sd)
         sched = DDIMScheduler(**{**dict(DDIMScheduler.from_pipeline_config().config.__dict__),
                                  **checkpoint.scheduler_config(path)})
         vae = None
         if os.path.isdir(os.path.join(path, "vae")):
             vsd, vcfg = checkpoint.read_component(path, "vae")
             vae = AutoencoderKL(checkpoint.vae_config(vcfg), device=device).load_state_dict(vsd)
-        return cls(unet, sched, text_dim=ucfg["cross_attention_dim"], dtype=torch_dtype or dtype, vae=vae)
+        return cls(unet, sched, text_dim=ucfg["cross_attention_dim"], dtype=dtype, vae=vae, tokenizer=tokenizer,
+                   text_encoder=text_encoder)
 
     @classmethod
-    def from_state_dict(cls, state_dict, config=None, device="cuda", dtype=torch.bfloat16):
+    def from_state_dict(cls, state_dict, config=None, device="cuda", dtype=torch.bfloat16, unet_dtype=None):
         cfg = dict(config or ZEROSCOPE_CONFIG)
-        unet = UNet3DConditionModel(cfg, device=device).load_state_dict(state_dict)
+        unet = UNet3DConditionModel(cfg, device=device, dtype=unet_arith_dtype(dtype, unet_dtype)).load_state_dict(state_dict)
         return cls(unet, DDIMScheduler.from_pipeline_config(), text_dim=cfg["cross_attention_dim"], dtype=dtype)

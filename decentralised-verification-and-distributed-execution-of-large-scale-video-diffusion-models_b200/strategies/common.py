@@ -44,25 +44,50 @@ def add_common_args(p, num_frames=32, out_csv="benchmarks.csv", chunking=True):
     p.add_argument("--emu_bw_mbps", type=float, default=0, help="throttle bandwidth in Mbps (0 = no throttle)")
     p.add_argument("--emu_rtt_ms", type=float, default=0, help="one-way latency in ms (0 = none)")
     p.add_argument("--emu_jitter_ms", type=float, default=0, help="jitter stddev in ms")
-    # additions that do not exist in the reference (defaults keep its behaviour)
+    # additions that do not exist in the reference. Defaults keep its behaviour: fp16 latents and fp16 UNet arithmetic
+    # (torch_dtype=torch.float16, chunk_only.py:44-47), so the fp16-accumulator blend of chunk_only.py:136-150 is
+    # reproduced bit for bit without flags. Deviations from the reference at default flags, on purpose: (1) frames are
+    # decoded (out.mp4, temp_instab / flow_err CSV columns) only when a VAE with real weights is there — a local
+    # checkpoint folder as --model_id — or when --decode is given; (2) weights are seeded random values unless
+    # --model_id is such a folder (there is no network to fetch the hub model).
     p.add_argument("--seed", type=int, default=1234, help="seed of the random-init weights (no checkpoint download)")
-    p.add_argument("--dtype", default="bf16", choices=["bf16", "fp16", "fp32"], help="I/O dtype of the latents")
+    p.add_argument("--dtype", default="fp16", choices=["bf16", "fp16", "fp32"],
+                   help="dtype of the latents (base noise, windows, blend accumulator); fp16 = the reference")
+    p.add_argument("--unet_dtype", default=None, choices=["bf16", "fp16"],
+                   help="arithmetic dtype inside the UNet (default: fp16 when --dtype fp16, else bf16)")
     p.add_argument("--exchange", default="p2p", choices=["p2p", "nccl"],
                    help="end-of-denoise window exchange: p2p = blend kernel reads the peers' windows over NVLink "
                         "(fused exchange + blend), nccl = all_gather then blend")
+    p.add_argument("--synthetic_text", action="store_true",
+                   help="with a checkpoint folder that has no tokenizer/ + text_encoder/: run on seeded random prompt "
+                        "embeddings instead of failing (the prompt is then ignored)")
     p.add_argument("--halo_sync", action="store_true",
                    help="per-step halo exchange (not in the reference): after every DDIM step adjacent windows swap "
                         "their overlapping frames over NVLink and adopt the same crossfade, so windows evolve as one "
                         "video; needs a plan where at most two windows cover a frame")
-    p.add_argument("--decode", action="store_true",
-                   help="decode the blended latents to frames on rank 0 (b2v.vae, random-init SD VAE decoder) and write "
-                        "the mp4 + boundary metrics like the reference; off by default because the frames of a "
-                        "random-init model are noise and the steps/s metric excludes the decode")
+    p.add_argument("--decode", dest="decode", action="store_true", default=None,
+                   help="decode the blended latents to frames on rank 0 (b2v.vae) and write the mp4 + boundary metrics "
+                        "like the reference (chunk_only.py:152-208). Default: on when --model_id is a checkpoint folder "
+                        "with a VAE, off for random-init weights (their frames are noise and the steps/s metric "
+                        "excludes the decode; the CSV columns temp_instab / flow_err then stay empty)")
+    p.add_argument("--no_decode", dest="decode", action="store_false", help="never decode")
     return p
 
 
 def torch_dtype(name):
     return {"bf16": torch.bfloat16, "fp16": torch.float16, "fp32": torch.float32}[name]
+
+
+def load_text_tower(path, device, dtype):
+    """The CLIP tokenizer / text encoder of a local diffusers-layout checkpoint through ``transformers`` (library code,
+    outside the accelerated path: SURVEY.md §8a U11). Returns (None, None) when the folder has no text tower."""
+    tdir, edir = os.path.join(path, "tokenizer"), os.path.join(path, "text_encoder")
+    if not (os.path.isdir(tdir) and os.path.isdir(edir)):
+        return None, None
+    from transformers import CLIPTextModel, CLIPTokenizer
+    tok = CLIPTokenizer.from_pretrained(tdir)
+    enc = CLIPTextModel.from_pretrained(edir, torch_dtype=dtype if dtype != torch.float32 else None).to(device).eval()
+    return tok, enc
 
 
 def init_distributed(device="cuda"):
@@ -199,13 +224,19 @@ class WindowedDiffuser:
         self.dtype = torch_dtype(getattr(cfg, "dtype", "bf16"))
         if pipe is None:
             from ..pipeline import VideoPipeline
+            udt = torch_dtype(cfg.unet_dtype) if getattr(cfg, "unet_dtype", None) else None
             if os.path.isdir(cfg.model_id):  # a downloaded diffusers-layout checkpoint (chunk_only.py:44-56)
                 LOG.info("rank %d: loading %s on %s", self.rank, cfg.model_id, self.device)
-                pipe = VideoPipeline.from_pretrained(cfg.model_id, device=self.device, dtype=self.dtype)
+                tok, enc = load_text_tower(cfg.model_id, self.device, self.dtype)
+                pipe = VideoPipeline.from_pretrained(cfg.model_id, device=self.device, dtype=self.dtype,
+                                                     unet_dtype=udt, tokenizer=tok, text_encoder=enc,
+                                                     allow_synthetic_text=bool(getattr(cfg, "synthetic_text", False)))
+                if getattr(cfg, "decode", None) is None:
+                    cfg.decode = pipe.vae is not None
             else:                            # no network here: the named architecture with seeded random weights
                 LOG.info("rank %d: building random-init %s on %s", self.rank, cfg.model_id, self.device)
                 pipe = VideoPipeline.from_random(cfg.model_id, device=self.device, seed=getattr(cfg, "seed", 1234),
-                                                 dtype=self.dtype)
+                                                 dtype=self.dtype, unet_dtype=udt)
         if getattr(cfg, "decode", False) and getattr(pipe, "vae", None) is None and self.rank == 0:
             from ..vae import AutoencoderKL
             pipe.vae = AutoencoderKL.from_random(device=self.device, seed=getattr(cfg, "seed", 1234) + 1)

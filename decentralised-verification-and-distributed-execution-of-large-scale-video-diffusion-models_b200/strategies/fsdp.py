@@ -29,11 +29,10 @@ class FSDPBenchmark(WindowedDiffuser):
 
 def parse_args(argv=None):
     p = add_common_args(argparse.ArgumentParser(), num_frames=25, chunking=False)
-    p.add_argument("--out", default=None, help="legacy alias of --out_csv")
-    cfg = p.parse_args(argv)
-    if cfg.out:
-        cfg.out_csv = cfg.out
-    return cfg
+    # fsdp.py:278: a dead legacy flag in the reference (default fsdp_results.npy); the CSV always goes to --out_csv
+    p.add_argument("--out", default="fsdp_results.npy", help="legacy flag, parsed and ignored like the reference does")
+    p.set_defaults(prompt="a rocket flying off into space, hd, detailed")  # fsdp.py's own default prompt
+    return p.parse_args(argv)
 
 
 def main(argv=None):

@@ -33,7 +33,12 @@ ZEROSCOPE_CONFIG = dict(in_channels=4, out_channels=4, block_out_channels=(320, 
 
 
 class UNet3DConditionModel:
-    def __init__(self, config=None, device="cuda"):
+    def __init__(self, config=None, device="cuda", dtype=torch.bfloat16):
+        """dtype: element type of the activations and GEMM operands INSIDE the network — torch.bfloat16 (default) or
+        torch.float16 (the reference's ``torch_dtype=torch.float16``, chunk_only.py:44-47). Accumulation is fp32 either
+        way; I/O tensors of a call may be fp32/fp16/bf16 independently."""
+        if dtype not in (torch.bfloat16, torch.float16):
+            raise ValueError("UNet3DConditionModel arithmetic dtype must be bfloat16 or float16, got %s" % dtype)
         cfg = dict(ZEROSCOPE_CONFIG)
         if config:
             cfg.update({k: v for k, v in dict(config).items() if k in cfg})
@@ -44,7 +49,7 @@ class UNet3DConditionModel:
         if dev.index is None:
             dev = torch.device("cuda", torch.cuda.current_device())
         self.device = dev
-        self.dtype = torch.bfloat16  # arithmetic type of the kernels; I/O tensors may be fp32/fp16/bf16
+        self.dtype = dtype  # arithmetic type of the kernels; I/O tensors may be fp32/fp16/bf16
         lib = _lib.load()
         c = _lib.UNet3DConfigC()
         c.in_channels, c.out_channels = cfg["in_channels"], cfg["out_channels"]
@@ -57,6 +62,7 @@ class UNet3DConditionModel:
         c.norm_eps = cfg["norm_eps"]
         c.transformer_in_heads = cfg["transformer_in_heads"]
         c.text_len = cfg["text_len"]
+        c.act_dtype = _lib.F16 if dtype == torch.float16 else _lib.BF16
         h = C.c_void_p()
         with torch.cuda.device(self.device):
             check(lib.b2v_unet3d_create(C.byref(c), C.byref(h)))
@@ -72,8 +78,8 @@ class UNet3DConditionModel:
         with torch.cuda.device(self.device):
             for name, t in state_dict.items():
                 t = t.detach()
-                if t.dtype not in ops._DT:
-                    t = t.float()
+                if t.dtype != torch.float32:
+                    t = t.float()  # the library keeps fp32 masters until finalize: hand them over as fp32 (a plain copy)
                 t = t.contiguous()
                 shape = (C.c_int64 * t.ndim)(*t.shape)
                 check(self._lib.b2v_unet3d_load_tensor(self._h, name.encode(), C.c_void_p(t.data_ptr()),
@@ -83,12 +89,12 @@ class UNet3DConditionModel:
         return self
 
     @classmethod
-    def from_module(cls, module, device="cuda"):
+    def from_module(cls, module, device="cuda", dtype=torch.bfloat16):
         """Build from an object exposing ``cfg``/``config`` and ``state_dict()`` (the oracle restatement or a real
         diffusers model)."""
         cfg = getattr(module, "cfg", None)
         cfg = cfg.to_dict() if hasattr(cfg, "to_dict") else dict(getattr(module, "config", {}))
-        return cls(cfg, device=device).load_state_dict(module.state_dict())
+        return cls(cfg, device=device, dtype=dtype).load_state_dict(module.state_dict())
 
     def param_count(self):
         return int(self._lib.b2v_unet3d_param_count(self._h))

@@ -166,6 +166,9 @@ typedef struct b2v_unet3d_config {
   float norm_eps;             /* 1e-5 */
   int transformer_in_heads;   /* 8 */
   int text_len;               /* 77 */
+  int act_dtype;              /* element type of activations and GEMM operands inside the network: B2V_BF16 (also when 0)
+                                 or B2V_F16 — the reference's own arithmetic (chunk_only.py:44-47 torch_dtype=float16,
+                                 miner.py:83-86). Same tensor-core rate; fp16 carries 3 more mantissa bits. */
 } b2v_unet3d_config;
 
 typedef struct b2v_unet3d b2v_unet3d;
@@ -192,27 +195,28 @@ double b2v_unet3d_flops(const b2v_unet3d* h, int B, int F, int H, int W);
 
 /* ------------------------------------------------------------------------------------------------
  * Building-block ops (used by the UNet; exported so tests/ can check each kernel against the oracle).
- * Activations are channels-last bf16: [rows, C] with rows = (b, f, y, x) flattened.
+ * Activations are channels-last 2-byte rows: [rows, C] with rows = (b, f, y, x) flattened. `act_dtype` (B2V_BF16 or
+ * B2V_F16) names the element type of every activation / weight operand of the call; accumulation is always fp32.
  * ------------------------------------------------------------------------------------------------ */
 
 /* epilogue flags for b2v_op_gemm */
 #define B2V_EPI_GEGLU 1      /* W rows are [value | gate] interleaved per 128-column tile pair; out has N/2 columns */
 #define B2V_EPI_GELU 2
 
-/* out[M,N] = A[M,K] · W[N,K]^T (+bias[N]) (+rowbias[row/rows_per_group, N]) (+residual[M,N]); bf16 in/out,
+/* out[M,N] = A[M,K] · W[N,K]^T (+bias[N]) (+rowbias[row/rows_per_group, N]) (+residual[M,N]); act_dtype in/out,
  * fp32 accumulate on tcgen05. taps/tap_row_stride: 1 tap = plain GEMM; 3 taps = temporal (3,1,1) conv
  * where tap t reads row r+(t-1)*tap_row_stride inside a group of rows_per_batch rows, zero outside
  * (K = taps*Kc, W laid out [N][tap][Kc]). */
 int b2v_op_gemm(const void* a_dev, const void* w_dev, const float* bias_dev, const float* rowbias_dev,
                 int64_t rows_per_group, const void* residual_dev, void* out_dev, int64_t M, int N, int Kc,
-                int taps, int64_t tap_row_stride, int64_t rows_per_batch, int flags, void* stream);
+                int taps, int64_t tap_row_stride, int64_t rows_per_batch, int flags, int act_dtype, void* stream);
 
-/* 3x3 convolution, padding 1, stride 1 or 2, NHWC bf16, weights [Cout][3][3][Cin] bf16, implicit GEMM
+/* 3x3 convolution, padding 1, stride 1 or 2, NHWC, weights [Cout][3][3][Cin], implicit GEMM
  * (TMA im2col -> tcgen05). mode 0 = TMA im2col, 1 = explicit im2col matrix in `scratch_dev` then GEMM. */
 size_t b2v_op_conv3x3_scratch_bytes(int N, int H, int W, int Cin, int stride, int mode);
 int b2v_op_conv3x3(const void* x_dev, const void* w_dev, const float* bias_dev, const float* rowbias_dev,
                    int64_t rows_per_group, const void* residual_dev, void* out_dev, int N, int H, int W,
-                   int Cin, int Cout, int stride, int mode, void* scratch_dev, void* stream);
+                   int Cin, int Cout, int stride, int mode, void* scratch_dev, int act_dtype, void* stream);
 
 /* GroupNorm (+SiLU) over channels-last rows: stats per (batch item, group) over rows_per_item rows x
  * C/groups channels, then y = (x-mean)*rstd*gamma+beta (silu optional). x may be the channel concat of
@@ -221,19 +225,19 @@ int b2v_op_conv3x3(const void* x_dev, const void* w_dev, const float* bias_dev, 
 size_t b2v_op_group_norm_scratch_bytes(int64_t n_items, int64_t rows_per_item, int groups);
 int b2v_op_group_norm(const void* x_dev, int C1, const void* x2_dev, int C2, const float* gamma_dev,
                       const float* beta_dev, void* y_dev, int64_t n_items, int64_t rows_per_item,
-                      int groups, float eps, int silu, void* scratch_dev, void* stream);
+                      int groups, float eps, int silu, void* scratch_dev, int act_dtype, void* stream);
 int b2v_op_layer_norm(const void* x_dev, const float* gamma_dev, const float* beta_dev, void* y_dev,
-                      int64_t rows, int C, float eps, void* stream);
+                      int64_t rows, int C, float eps, int act_dtype, void* stream);
 
-/* softmax(Q K^T * scale) V, head_dim 64, bf16. q: [nb, Sq, ldq] rows, head h at column h*64;
+/* softmax(Q K^T * scale) V, head_dim 64. q: [nb, Sq, ldq] rows, head h at column h*64;
  * k/v: [nb / kv_group, Skv, ldk]; out [nb, Sq, ldo]. (tcgen05 flash attention.) */
 int b2v_op_attention(const void* q_dev, int64_t ldq, const void* k_dev, const void* v_dev, int64_t ldkv,
                      void* out_dev, int64_t ldo, int nb, int heads, int Sq, int Skv, int kv_group,
-                     float scale, void* stream);
+                     float scale, int act_dtype, void* stream);
 /* attention over the frame axis: tokens [B, F, HW, *], sequence = F (<= 32), head_dim 64. */
 int b2v_op_temporal_attention(const void* qkv_dev, int64_t ld, int q_off, int k_off, int v_off,
                               void* out_dev, int64_t ldo, int B, int F, int64_t HW, int heads,
-                              float scale, void* stream);
+                              float scale, int act_dtype, void* stream);
 
 /* ------------------------------------------------------------------------------------------------
  * Frame decode after the loop  ([UPSTREAM diffusers] pipe.vae.decode(z / 0.18215).sample and the uint8 frame
@@ -250,10 +254,10 @@ int b2v_op_softmax_rows(void* x_dev, int64_t rows, int cols, int64_t ld, float s
 int b2v_op_frames_u8(const void* rows_dev, int64_t ld, int64_t n_px, uint8_t* out_dev, void* stream);
 /* Nearest-neighbour x2 (Upsample2D, F.interpolate(scale_factor=2, mode="nearest")): [N,H,W,C] -> [N,2H,2W,C] bf16. */
 int b2v_op_upsample2x(const void* x_dev, void* y_dev, int N, int H, int W, int C, void* stream);
-/* Latents [B,C,F,h,w] of `io_dtype` -> channels-last bf16 rows [(b,f,y,x), Cpad], channels >= C zero: the layout
- * the tensor-core conv_in / post_quant_conv read. */
+/* Latents [B,C,F,h,w] of `io_dtype` -> channels-last rows [(b,f,y,x), Cpad] of act_dtype, channels >= C zero: the
+ * layout the tensor-core conv_in / post_quant_conv read. */
 int b2v_op_latent_rows(const void* x_dev, int io_dtype, void* rows_dev, int B, int C, int F, int64_t hw, int Cpad,
-                       void* stream);
+                       int act_dtype, void* stream);
 
 #ifdef __cplusplus
 }

@@ -344,8 +344,9 @@ class UNet3DConditionModel(nn.Module):
 
 def random_init_(model: nn.Module, seed: int = 1234, round_bf16: bool = False) -> nn.Module:
     """SURVEY §8c random-init protocol: overwrite EVERY parameter (including the zero-initialised temp_convs.*.conv4)
-    with seeded normal values scaled by fan-in; norm weights around 1. Optionally round to bf16-representable values
-    so that the oracle and the bf16 kernels multiply identical weights."""
+    with seeded normal values scaled by fan-in; norm weights around 1. Optionally round to values that are exactly
+    representable in bf16 AND in fp16 (bf16 rounding, magnitudes below fp16's smallest normal 2^-14 flushed to zero) so
+    that the oracle and the kernels — in either operand precision — multiply identical weights."""
     g = torch.Generator().manual_seed(seed)
     with torch.no_grad():
         for name, p in model.named_parameters():
@@ -359,6 +360,7 @@ def random_init_(model: nn.Module, seed: int = 1234, round_bf16: bool = False) -
                 v = torch.randn(p.shape, generator=g) / math.sqrt(fan_in)
             if round_bf16:
                 v = v.to(torch.bfloat16).to(torch.float32)
+                v = torch.where(v.abs() < 2.0 ** -14, torch.zeros_like(v), v)
             p.copy_(v)
     return model
 

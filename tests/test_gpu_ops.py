@@ -1,6 +1,8 @@
 """-m gpu: every building-block kernel of libb2v, called through the C-ABI, against a plain torch fp32 reference of the
-same op (floating-point kernels; tolerance written at each assert). bf16 inputs are shared by both sides, so the error
-budget is fp32-accumulate + one bf16 output rounding (2^-8 relative) unless stated."""
+same op (floating-point kernels; tolerance written at each assert). Every test runs in both activation dtypes of the
+library: bf16 (default) and fp16 (the reference's torch_dtype, chunk_only.py:44-47). The 2-byte inputs are shared by
+both sides, so the error budget is fp32-accumulate + one output rounding (bf16: 2^-8 relative; fp16: 2^-11, gated 4x
+tighter) unless stated. The largest cases are the ZeroscopeXL shapes the benchmark runs (72 x 128 latent: 9216 tokens)."""
 import math
 
 import pytest
@@ -14,8 +16,31 @@ def rel_l2(a, b):
     return float((a - b).norm() / b.norm().clamp_min(1e-12))
 
 
-def bf(x):
-    return x.to(torch.bfloat16)
+@pytest.fixture(params=[torch.bfloat16, torch.float16], ids=["bf16", "fp16"])
+def act(request):
+    return request.param
+
+
+class _Cast:
+    """A(x): cast to the activation dtype of the running test (set by the autouse fixture below)."""
+    dtype = torch.bfloat16
+
+    def __call__(self, x):
+        return x.to(self.dtype)
+
+
+A = _Cast()
+
+
+@pytest.fixture(autouse=True)
+def _set_cast(act):
+    A.dtype = act
+    yield
+
+
+def tol(act, bf16_tol):
+    """Gate of a check whose error is dominated by the output rounding: fp16 has 3 more mantissa bits than bf16."""
+    return bf16_tol if act == torch.bfloat16 else bf16_tol / 4
 
 
 def pack_geglu(w, b):
@@ -30,41 +55,41 @@ def pack_geglu(w, b):
 
 @pytest.mark.parametrize("M,N,K", [(128, 64, 64), (256, 128, 128), (1000, 320, 192), (4096, 256, 320),
                                    (300, 640, 1280), (77 * 2, 2560, 1024), (20000, 1280, 640)])
-def test_gemm_plain(cuda, M, N, K):
+def test_gemm_plain(cuda, act, M, N, K):
     from b2v import ops
     g = torch.Generator(device="cuda").manual_seed(M + N + K)
-    a = bf(torch.randn(M, K, device=cuda, generator=g))
-    w = bf(torch.randn(N, K, device=cuda, generator=g) / math.sqrt(K))
+    a = A(torch.randn(M, K, device=cuda, generator=g))
+    w = A(torch.randn(N, K, device=cuda, generator=g) / math.sqrt(K))
     bias = torch.randn(N, device=cuda, generator=g)
     out = ops.gemm(a, w, bias=bias)
     ref = a.float() @ w.float().t() + bias
     assert out.shape == (M, N)
-    assert rel_l2(out, ref) < 4e-3, rel_l2(out, ref)
+    assert rel_l2(out, ref) < tol(act, 4e-3), rel_l2(out, ref)
     assert float((out.float() - ref).abs().max()) < 0.05 * float(ref.abs().max())
 
 
-def test_gemm_residual_rowbias(cuda):
+def test_gemm_residual_rowbias(cuda, act):
     from b2v import ops
     g = torch.Generator(device="cuda").manual_seed(7)
     B, rows_per_group, N, K = 3, 200, 320, 256
     M = B * rows_per_group
-    a = bf(torch.randn(M, K, device=cuda, generator=g))
-    w = bf(torch.randn(N, K, device=cuda, generator=g) / math.sqrt(K))
+    a = A(torch.randn(M, K, device=cuda, generator=g))
+    w = A(torch.randn(N, K, device=cuda, generator=g) / math.sqrt(K))
     bias = torch.randn(N, device=cuda, generator=g)
     rowbias = torch.randn(B, N, device=cuda, generator=g)
-    res = bf(torch.randn(M, N, device=cuda, generator=g))
+    res = A(torch.randn(M, N, device=cuda, generator=g))
     out = ops.gemm(a, w, bias=bias, rowbias=rowbias, rows_per_group=rows_per_group, residual=res,
                    rows_per_batch=rows_per_group)
     ref = a.float() @ w.float().t() + bias + rowbias.repeat_interleave(rows_per_group, 0) + res.float()
-    assert rel_l2(out, ref) < 4e-3, rel_l2(out, ref)
+    assert rel_l2(out, ref) < tol(act, 4e-3), rel_l2(out, ref)
 
 
 @pytest.mark.parametrize("M,dim", [(256, 64), (1000, 320), (640, 1280)])
-def test_gemm_geglu(cuda, M, dim):
+def test_gemm_geglu(cuda, act, M, dim):
     from b2v import ops, _lib
     g = torch.Generator(device="cuda").manual_seed(dim)
-    a = bf(torch.randn(M, dim, device=cuda, generator=g))
-    w = bf(torch.randn(8 * dim, dim, device=cuda, generator=g) / math.sqrt(dim))
+    a = A(torch.randn(M, dim, device=cuda, generator=g))
+    w = A(torch.randn(8 * dim, dim, device=cuda, generator=g) / math.sqrt(dim))
     b = torch.randn(8 * dim, device=cuda, generator=g)
     wp, bp = pack_geglu(w, b)
     out = ops.gemm(a, wp, bias=bp, flags=_lib.EPI_GEGLU)
@@ -72,64 +97,65 @@ def test_gemm_geglu(cuda, M, dim):
     h, gate = proj.chunk(2, dim=-1)
     ref = h * torch.nn.functional.gelu(gate)
     assert out.shape == (M, 4 * dim)
-    assert rel_l2(out, ref) < 5e-3, rel_l2(out, ref)
+    assert rel_l2(out, ref) < tol(act, 5e-3), rel_l2(out, ref)
 
 
 @pytest.mark.parametrize("B,F,HW,C", [(1, 4, 128, 64), (2, 5, 100, 128), (2, 8, 256, 320), (1, 16, 45, 1280)])
-def test_gemm_temporal_taps(cuda, B, F, HW, C):
+def test_gemm_temporal_taps(cuda, act, B, F, HW, C):
     """TemporalConvLayer Conv3d (3,1,1), zero padded in time, as a 3-tap GEMM over row strides."""
     from b2v import ops
     g = torch.Generator(device="cuda").manual_seed(B * 100 + F)
-    x = bf(torch.randn(B, F, HW, C, device=cuda, generator=g))
-    w3 = bf(torch.randn(C, C, 3, device=cuda, generator=g) / math.sqrt(3 * C))  # [Cout][Cin][tap]
+    x = A(torch.randn(B, F, HW, C, device=cuda, generator=g))
+    w3 = A(torch.randn(C, C, 3, device=cuda, generator=g) / math.sqrt(3 * C))  # [Cout][Cin][tap]
     bias = torch.randn(C, device=cuda, generator=g)
     wk = w3.permute(0, 2, 1).contiguous().reshape(C, 3 * C)  # [Cout][tap][Cin]
     out = ops.gemm(x.reshape(-1, C), wk, bias=bias, taps=3, tap_row_stride=HW, rows_per_batch=F * HW)
     xr = x.float().permute(0, 3, 1, 2).reshape(B, C, F, HW, 1)
     ref = torch.nn.functional.conv3d(xr, w3.float().reshape(C, C, 3, 1, 1), bias, padding=(1, 0, 0))
     ref = ref.reshape(B, C, F, HW).permute(0, 2, 3, 1).reshape(-1, C)
-    assert rel_l2(out, ref) < 4e-3, rel_l2(out, ref)
+    assert rel_l2(out, ref) < tol(act, 4e-3), rel_l2(out, ref)
 
 
 @pytest.mark.parametrize("mode", [1, 0], ids=["explicit", "tmaim2col"])
 @pytest.mark.parametrize("N,H,W,Cin,Cout,stride", [(2, 16, 16, 64, 64, 1), (3, 20, 36, 128, 320, 1),
                                                    (2, 16, 24, 64, 128, 2), (1, 8, 8, 640, 1280, 1),
-                                                   (2, 40, 72, 320, 320, 1), (2, 10, 18, 320, 320, 2)])
-def test_conv3x3(cuda, mode, N, H, W, Cin, Cout, stride):
+                                                   (2, 40, 72, 320, 320, 1), (2, 10, 18, 320, 320, 2),
+                                                   (2, 72, 128, 320, 320, 1), (1, 72, 128, 960, 320, 1)])
+def test_conv3x3(cuda, act, mode, N, H, W, Cin, Cout, stride):
     from b2v import ops
     g = torch.Generator(device="cuda").manual_seed(H * W + Cin)
-    x = bf(torch.randn(N, H, W, Cin, device=cuda, generator=g))
-    w = bf(torch.randn(Cout, 3, 3, Cin, device=cuda, generator=g) / math.sqrt(9 * Cin))
+    x = A(torch.randn(N, H, W, Cin, device=cuda, generator=g))
+    w = A(torch.randn(Cout, 3, 3, Cin, device=cuda, generator=g) / math.sqrt(9 * Cin))
     bias = torch.randn(Cout, device=cuda, generator=g)
     out = ops.conv3x3(x, w, bias=bias, stride=stride, mode=mode)
     ref = torch.nn.functional.conv2d(x.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2), bias,
                                      stride=stride, padding=1).permute(0, 2, 3, 1)
     assert out.shape == ref.shape
-    assert rel_l2(out, ref) < 4e-3, (mode, rel_l2(out, ref))
+    assert rel_l2(out, ref) < tol(act, 4e-3), (mode, rel_l2(out, ref))
 
 
-def test_conv3x3_rowbias_residual(cuda):
+def test_conv3x3_rowbias_residual(cuda, act):
     from b2v import ops
     g = torch.Generator(device="cuda").manual_seed(3)
     B, F, H, W, Cin, Cout = 2, 3, 16, 16, 64, 128
-    x = bf(torch.randn(B * F, H, W, Cin, device=cuda, generator=g))
-    w = bf(torch.randn(Cout, 3, 3, Cin, device=cuda, generator=g) / math.sqrt(9 * Cin))
+    x = A(torch.randn(B * F, H, W, Cin, device=cuda, generator=g))
+    w = A(torch.randn(Cout, 3, 3, Cin, device=cuda, generator=g) / math.sqrt(9 * Cin))
     bias = torch.randn(Cout, device=cuda, generator=g)
     rowbias = torch.randn(B, Cout, device=cuda, generator=g)
-    res = bf(torch.randn(B * F, H, W, Cout, device=cuda, generator=g))
+    res = A(torch.randn(B * F, H, W, Cout, device=cuda, generator=g))
     out = ops.conv3x3(x, w, bias=bias, rowbias=rowbias, rows_per_group=F * H * W, residual=res)
     ref = torch.nn.functional.conv2d(x.float().permute(0, 3, 1, 2), w.float().permute(0, 3, 1, 2), bias,
                                      padding=1).permute(0, 2, 3, 1)
     ref = ref + rowbias.repeat_interleave(F, 0)[:, None, None, :] + res.float()
-    assert rel_l2(out, ref) < 4e-3, rel_l2(out, ref)
+    assert rel_l2(out, ref) < tol(act, 4e-3), rel_l2(out, ref)
 
 
 @pytest.mark.parametrize("items,rows,C,silu,eps", [(4, 256, 64, 1, 1e-5), (6, 1024, 320, 1, 1e-5),
                                                    (2, 2880, 640, 0, 1e-6), (3, 45, 1280, 1, 1e-5)])
-def test_group_norm(cuda, items, rows, C, silu, eps):
+def test_group_norm(cuda, act, items, rows, C, silu, eps):
     from b2v import ops
     g = torch.Generator(device="cuda").manual_seed(C)
-    x = bf(torch.randn(items * rows, C, device=cuda, generator=g) * 2 + 0.5)
+    x = A(torch.randn(items * rows, C, device=cuda, generator=g) * 2 + 0.5)
     gamma = 1 + 0.1 * torch.randn(C, device=cuda, generator=g)
     beta = 0.1 * torch.randn(C, device=cuda, generator=g)
     y = ops.group_norm(x, gamma, beta, items, 32, eps, silu)
@@ -139,16 +165,17 @@ def test_group_norm(cuda, items, rows, C, silu, eps):
         ref = torch.nn.functional.silu(ref)
     ref = ref.permute(0, 2, 1).reshape(-1, C)
     # tolerance: one bf16 rounding of an O(1) value
-    assert float((y.float() - ref).abs().max()) < 0.03
-    assert rel_l2(y, ref) < 4e-3
+    # one output rounding of an O(1..8) value + tanh.approx (2^-11 relative) inside the fused SiLU
+    assert float((y.float() - ref).abs().max()) < (0.03 if act == torch.bfloat16 else 0.012)
+    assert rel_l2(y, ref) < tol(act, 4e-3)
 
 
-def test_group_norm_concat(cuda):
+def test_group_norm_concat(cuda, act):
     from b2v import ops
     g = torch.Generator(device="cuda").manual_seed(11)
     items, rows, C1, C2 = 4, 180, 1280, 640
-    x1 = bf(torch.randn(items * rows, C1, device=cuda, generator=g))
-    x2 = bf(torch.randn(items * rows, C2, device=cuda, generator=g) * 3)
+    x1 = A(torch.randn(items * rows, C1, device=cuda, generator=g))
+    x2 = A(torch.randn(items * rows, C2, device=cuda, generator=g) * 3)
     C = C1 + C2
     gamma = 1 + 0.1 * torch.randn(C, device=cuda, generator=g)
     beta = 0.1 * torch.randn(C, device=cuda, generator=g)
@@ -156,49 +183,52 @@ def test_group_norm_concat(cuda):
     xr = torch.cat([x1, x2], 1).float().reshape(items, rows, C).permute(0, 2, 1)
     ref = torch.nn.functional.silu(torch.nn.functional.group_norm(xr, 32, gamma, beta, 1e-5))
     ref = ref.permute(0, 2, 1).reshape(-1, C)
-    assert rel_l2(y, ref) < 4e-3
+    assert rel_l2(y, ref) < tol(act, 4e-3)
 
 
 @pytest.mark.parametrize("rows,C", [(1000, 64), (4096, 320), (333, 512), (512, 1280)])
-def test_layer_norm(cuda, rows, C):
+def test_layer_norm(cuda, act, rows, C):
     from b2v import ops
     g = torch.Generator(device="cuda").manual_seed(C)
-    x = bf(torch.randn(rows, C, device=cuda, generator=g) * 3 + 1)
+    x = A(torch.randn(rows, C, device=cuda, generator=g) * 3 + 1)
     gamma = 1 + 0.1 * torch.randn(C, device=cuda, generator=g)
     beta = 0.1 * torch.randn(C, device=cuda, generator=g)
     y = ops.layer_norm(x, gamma, beta)
     ref = torch.nn.functional.layer_norm(x.float(), (C,), gamma, beta, 1e-5)
-    assert rel_l2(y, ref) < 4e-3
+    assert rel_l2(y, ref) < tol(act, 4e-3)
 
 
 @pytest.mark.parametrize("nb,heads,Sq,Skv,kv_group", [(2, 1, 128, 128, 1), (3, 2, 256, 256, 1), (4, 5, 1000, 1000, 1),
-                                                      (6, 2, 300, 77, 3), (2, 20, 180, 180, 1), (1, 5, 2880, 2880, 1)])
-def test_attention(cuda, nb, heads, Sq, Skv, kv_group):
+                                                      (6, 2, 300, 77, 3), (2, 20, 180, 180, 1), (1, 5, 2880, 2880, 1),
+                                                      (2, 5, 9216, 9216, 1), (2, 5, 9216, 77, 2)])
+def test_attention(cuda, act, nb, heads, Sq, Skv, kv_group):
     from b2v import ops
     g = torch.Generator(device="cuda").manual_seed(Sq + Skv)
     D = heads * 64
-    q = bf(torch.randn(nb, Sq, D, device=cuda, generator=g))
-    k = bf(torch.randn(nb // kv_group, Skv, D, device=cuda, generator=g))
-    v = bf(torch.randn(nb // kv_group, Skv, D, device=cuda, generator=g))
+    q = A(torch.randn(nb, Sq, D, device=cuda, generator=g))
+    k = A(torch.randn(nb // kv_group, Skv, D, device=cuda, generator=g))
+    v = A(torch.randn(nb // kv_group, Skv, D, device=cuda, generator=g))
     out = ops.attention(q, k, v, heads, kv_group=kv_group)
     qh = q.float().reshape(nb, Sq, heads, 64).transpose(1, 2)
     kh = k.float().reshape(-1, Skv, heads, 64).transpose(1, 2).repeat_interleave(kv_group, 0)
     vh = v.float().reshape(-1, Skv, heads, 64).transpose(1, 2).repeat_interleave(kv_group, 0)
     ref = torch.softmax(qh @ kh.transpose(-1, -2) * 0.125, -1) @ vh
     ref = ref.transpose(1, 2).reshape(nb, Sq, D)
-    # P is rounded to bf16 before the PV product: 2^-8 relative per probability
-    assert rel_l2(out, ref) < 1e-2, rel_l2(out, ref)
+    # P is rounded to the activation dtype before the PV product: 2^-8 (bf16) / 2^-11 (fp16) relative per probability
+    err = rel_l2(out, ref)
+    print("attention", (nb, heads, Sq, Skv), act, "rel-l2 %.3e" % err)
+    assert err < tol(act, 1e-2), err
 
 
 @pytest.mark.parametrize("B,F,HW,heads", [(1, 4, 64, 1), (2, 8, 100, 5), (2, 16, 45, 20), (1, 24, 33, 8), (1, 1, 16, 2)])
-def test_temporal_attention(cuda, B, F, HW, heads):
+def test_temporal_attention(cuda, act, B, F, HW, heads):
     from b2v import ops
     g = torch.Generator(device="cuda").manual_seed(F * HW)
     D = heads * 64
-    qkv = bf(torch.randn(B * F * HW, 3 * D, device=cuda, generator=g))
+    qkv = A(torch.randn(B * F * HW, 3 * D, device=cuda, generator=g))
     out = ops.temporal_attention(qkv, B, F, HW, heads)
     t = qkv.float().reshape(B, F, HW, 3, heads, 64).permute(3, 0, 2, 4, 1, 5)  # [3][B][HW][heads][F][64]
     q, k, v = t[0], t[1], t[2]
     ref = torch.softmax(q @ k.transpose(-1, -2) * 0.125, -1) @ v  # [B][HW][heads][F][64]
     ref = ref.permute(0, 3, 1, 2, 4).reshape(B * F * HW, D)
-    assert rel_l2(out, ref) < 4e-3, rel_l2(out, ref)
+    assert rel_l2(out, ref) < tol(act, 4e-3), rel_l2(out, ref)

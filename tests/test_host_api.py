@@ -103,14 +103,20 @@ def test_cli_flags_and_defaults():
         fsdp_chunked_coherent.parse_args(["--mode", "bogus"])
     s = fsdp_chunked.parse_args([])
     assert (s.num_frames, s.mode, s.context_weight) == (25, "split", 0.35)
-    f = fsdp.parse_args(["--out", "legacy.csv"])
-    assert f.num_frames == 25 and f.out_csv == "legacy.csv" and not hasattr(f, "guidance_scale")
+    # fsdp.py:278: --out is a dead legacy flag of the reference (the CSV always goes to --out_csv); fsdp.py has its own
+    # default prompt
+    f = fsdp.parse_args(["--out", "legacy.npy"])
+    assert f.num_frames == 25 and f.out_csv == "benchmarks.csv" and f.out == "legacy.npy" and not hasattr(f, "guidance_scale")
+    assert f.prompt == "a rocket flying off into space, hd, detailed" and c.prompt == "a rocket in space, 4k"
     with pytest.raises(SystemExit):
         fsdp.parse_args(["--overlap", "2"])
-    # additions of this build are off by default: the reference's behaviour is what runs without flags
-    assert (c.halo_sync, c.decode, c.exchange) == (False, False, "p2p")
-    on = chunk_only.parse_args(["--halo_sync", "--decode", "--exchange", "nccl"])
-    assert (on.halo_sync, on.decode, on.exchange) == (True, True, "nccl")
+    # additions of this build: the defaults are the reference's arithmetic (fp16 latents, fp16 UNet: chunk_only.py:44-47).
+    # decode = None means "decode iff the checkpoint folder brings a VAE" (random-init runs write no mp4: stated
+    # deviation, strategies/common.py add_common_args)
+    assert (c.halo_sync, c.decode, c.exchange, c.dtype, c.unet_dtype) == (False, None, "p2p", "fp16", None)
+    on = chunk_only.parse_args(["--halo_sync", "--decode", "--exchange", "nccl", "--dtype", "bf16"])
+    assert (on.halo_sync, on.decode, on.exchange, on.dtype) == (True, True, "nccl", "bf16")
+    assert chunk_only.parse_args(["--no_decode"]).decode is False
     # the experiment driver's command line (full_experiments_ZeroscopeXL.sh:25) parses
     chunk_only.parse_args("--emu_bw_mbps 500 --emu_rtt_ms 3.01 --emu_jitter_ms 3.53 --model_id cerspense/zeroscope_v2_XL "
                           "--out_csv ZeroscopeXL/wifi_results.csv".split())
