@@ -29,39 +29,55 @@ __device__ __forceinline__ float ex2(float x) {
 // flash attention, head_dim 64, q tile 128, kv tile 128, 2 CTAs / SM (the co-resident CTA's MMAs run under this
 // CTA's softmax and vice versa)
 //   warp 0: TMA producer   warp 1: MMA issuer   warps 2-5: softmax (thread = query row)
-// smem: Q 16K | K 2x16K | V 2x16K | P 32K      TMEM: S cols [0,128)   O cols [128,192) (accumulates over kv tiles)
+// smem: Q 16K | K 3x16K | V 3x16K
+// TMEM: S cols [0,128) fp32 | O cols [128,192) fp32 (accumulates over kv tiles) | P cols [192,256) packed 16-bit pairs
 // S(j+1) is computed while softmax(j) runs: the softmax warps release the S columns right after loading them.
 // Softmax is single pass: the S row (128 fp32) is held in registers; the exponent uses a *stale* running maximum
 // that is only refreshed (and O rescaled in TMEM) when the true maximum has moved by more than 2^8 — the final
 // O / l is exact either way, and O never round-trips through registers in the steady state.
+// P never touches shared memory: the softmax warps write the rounded probabilities back to TMEM (tcgen05.st) and the
+// P V MMA takes its A operand from there — no st.shared, no MEMBAR + proxy fence, no operand fetch from shared
+// memory for P (measured with the FMA-pipe exponentials below: 4.49 -> 4.01 ms on the L0 shape,
+// profiles/r02_attn_ab.md).
 // ------------------------------------------------------------------------------------------------
 constexpr int AT_THREADS = 192;
 constexpr int AT_TILE = 16384;  // 128 rows x 64 bf16
-constexpr int AT_SMEM = AT_TILE * (1 + 2 + 2 + 2) + 128;  // 2 CTAs/SM: 2 x (this + 1 KiB system) <= 227 KiB
+constexpr int AT_STAGES = 3;    // K / V ring depth
+constexpr int AT_SMEM = AT_TILE * (1 + 2 * AT_STAGES) + 128;  // 2 CTAs/SM: 2 x (this + 1 KiB system) <= 228 KiB
 constexpr int AT_TMEM_COLS = 256;
 constexpr float AT_RESCALE_LOG2 = 8.0f;
+// exp2 on the FMA pipe for a share of the scores. The MUFU does 4 ex2 / clk / sub-partition (8.0 cycles per warp
+// instruction, tools/ubench_pipes.cu) and one per score makes it the busiest pipe at head_dim 64 (70 %); ex2 on packed
+// 16-bit pairs is no way out (ex2.approx.ftz.bf16x2 / f16x2 compile to two MUFU.EX2 + PRMT on sm_100a). Round-to-nearest
+// split x = n + f by the 1.5 * 2^23 trick, degree-3 minimax 2^f on [-0.5, 0.5] (max relative error 7.5e-5: below half
+// an ulp of the bf16 / fp16 P), n added into the exponent field; all of it on packed fp32 pairs (FFMA2).
+constexpr float AT_MAGIC = 12582912.0f;
+constexpr float AT_C0 = 0.9999280572f, AT_C1 = 0.6932609677f, AT_C2 = 0.2426111251f, AT_C3 = 0.0551716685f;
+constexpr int AT_DEFAULT_POLY = 2;
 
 struct AttnParams {
   __nv_bfloat16* out;
   int64_t ldo;
   int Sq, Skv, kv_group, nkv;
-  float scale_log2;  // scale * log2(e)
+  float scale_log2;      // scale * log2(e)
+  float inv_scale_log2;  // 1 / scale_log2
 };
 
-template <bool F16>
+// POLY = column pairs out of every 8 whose exponentials are computed on the FMA pipe (0 = all on the MUFU)
+template <bool F16, int POLY>
 __global__ void __launch_bounds__(AT_THREADS, 2)
 attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUtensorMap tmK,
             const __grid_constant__ CUtensorMap tmV, const AttnParams p) {
   extern __shared__ __align__(1024) uint8_t smem[];
   uint8_t* sQ = smem;
   uint8_t* sK = smem + AT_TILE;
-  uint8_t* sV = smem + 3 * AT_TILE;
-  uint8_t* sP = smem + 5 * AT_TILE;
-  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + 7 * AT_TILE);
-  const uint32_t q_full = smem_u32(bars + 0), k_full0 = smem_u32(bars + 1), v_full0 = smem_u32(bars + 3),
-                 kv_empty0 = smem_u32(bars + 5), s_full = smem_u32(bars + 7), p_full = smem_u32(bars + 8),
-                 o_full = smem_u32(bars + 9), s_free = smem_u32(bars + 10);
-  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 11);
+  uint8_t* sV = smem + (1 + AT_STAGES) * AT_TILE;
+  uint64_t* bars = reinterpret_cast<uint64_t*>(smem + (1 + 2 * AT_STAGES) * AT_TILE);
+  const uint32_t q_full = smem_u32(bars + 0), s_full = smem_u32(bars + 1), p_full = smem_u32(bars + 2),
+                 o_full = smem_u32(bars + 3), s_free = smem_u32(bars + 4), k_full0 = smem_u32(bars + 5),
+                 v_full0 = smem_u32(bars + 5 + AT_STAGES), kv_empty0 = smem_u32(bars + 5 + 2 * AT_STAGES);
+  uint32_t* tmem_slot = reinterpret_cast<uint32_t*>(bars + 5 + 3 * AT_STAGES);
+  static_assert((5 + 3 * AT_STAGES) * 8 + 4 <= 128, "barrier block");
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   const int q0 = blockIdx.x * 128, h = blockIdx.y, b = blockIdx.z;
@@ -74,7 +90,7 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
     }
     prefetch_tmap(&tmQ); prefetch_tmap(&tmK); prefetch_tmap(&tmV);
     mbar_init(q_full, 1);
-    for (int i = 0; i < 2; ++i) { mbar_init(k_full0 + 8 * i, 1); mbar_init(v_full0 + 8 * i, 1); mbar_init(kv_empty0 + 8 * i, 1); }
+    for (int i = 0; i < AT_STAGES; ++i) { mbar_init(k_full0 + 8 * i, 1); mbar_init(v_full0 + 8 * i, 1); mbar_init(kv_empty0 + 8 * i, 1); }
     mbar_init(s_full, 1);
     mbar_init(p_full, 4);
     mbar_init(o_full, 1);
@@ -86,7 +102,7 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
-  const uint32_t tS = tmem_base, tO = tmem_base + 128;
+  const uint32_t tS = tmem_base, tO = tmem_base + 128, tP = tmem_base + 192;
   pdl_wait();
 
   if (warp == 0) {
@@ -94,66 +110,70 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       mbar_expect_tx(q_full, AT_TILE);
       tma_load_3d(smem_u32(sQ), &tmQ, q_full, h * 64, q0, b);
       const int bk = b / p.kv_group;
+      int st = 0, ph = 0;
       for (int j = 0; j < nkv; ++j) {
-        const int st = j & 1;
-        mbar_wait(kv_empty0 + 8 * st, ((j >> 1) & 1) ^ 1);
+        mbar_wait(kv_empty0 + 8 * st, ph ^ 1);
         mbar_expect_tx(k_full0 + 8 * st, AT_TILE);
         tma_load_3d(smem_u32(sK + st * AT_TILE), &tmK, k_full0 + 8 * st, h * 64, j * 128, bk);
         mbar_expect_tx(v_full0 + 8 * st, AT_TILE);
         tma_load_3d(smem_u32(sV + st * AT_TILE), &tmV, v_full0 + 8 * st, h * 64, j * 128, bk);
+        if (++st == AT_STAGES) { st = 0; ph ^= 1; }
       }
     }
   } else if (warp == 1) {
     constexpr uint32_t idesc_qk = umma_idesc_16(128, 128, F16, F16);
     constexpr uint32_t idesc_pv = umma_idesc_16(128, 64, F16, F16) | (1u << 16);  // B (=V) is MN-major
-    auto issue_qk = [&](int j) {
-      const int st = j & 1;
-      mbar_wait(k_full0 + 8 * st, (j >> 1) & 1);
+    int qst = 0, qph = 0;  // ring position of the next S = Q K^T
+    auto issue_qk = [&]() {
+      mbar_wait(k_full0 + 8 * qst, qph);
       tc_fence_after();
       if (elect_one()) {
-        const uint64_t a = umma_desc_sw128(smem_u32(sQ)), bd = umma_desc_sw128(smem_u32(sK + st * AT_TILE));
+        const uint64_t a = umma_desc_sw128(smem_u32(sQ)), bd = umma_desc_sw128(smem_u32(sK + qst * AT_TILE));
 #pragma unroll
         for (int k = 0; k < 4; ++k) umma_bf16_ss(tS, a + 2 * k, bd + 2 * k, idesc_qk, k != 0);
         umma_commit(s_full);
       }
       __syncwarp();
+      if (++qst == AT_STAGES) { qst = 0; qph ^= 1; }
     };
     mbar_wait(q_full, 0);
-    issue_qk(0);
+    issue_qk();
+    int st = 0, ph = 0;
     for (int j = 0; j < nkv; ++j) {
-      const int st = j & 1;
       // S(j+1) = Q K(j+1)^T is issued as soon as the softmax warps have pulled S(j) into registers, so it runs on the
       // tensor core UNDER softmax(j) and the softmax warps never wait for a score tile in the steady state
       if (j + 1 < nkv) {
         mbar_wait(s_free, j & 1);
         tc_fence_after();
-        issue_qk(j + 1);
+        issue_qk();
       }
-      mbar_wait(p_full, j & 1);   // P(j) is in smem, O has been rescaled if it had to be
-      mbar_wait(v_full0 + 8 * st, (j >> 1) & 1);
+      mbar_wait(p_full, j & 1);   // P(j) is in TMEM, O has been rescaled if it had to be
+      mbar_wait(v_full0 + 8 * st, ph);
       tc_fence_after();
       if (elect_one()) {
 #pragma unroll
         for (int k = 0; k < 8; ++k) {
-          // A = P: two 64-wide K blocks of 16 KiB; B = V: 16 kv rows (2 KiB) per k-step, MN-major
-          const uint64_t a = umma_desc_sw128(smem_u32(sP + (k >> 2) * AT_TILE)) + 2 * (k & 3);
+          // A = P from TMEM: 128 rows (lanes) x 16 kv per step = 8 columns of packed pairs; B = V: 16 kv rows (2 KiB)
+          // per k-step, MN-major
           const uint64_t bd = umma_desc_sw128(smem_u32(sV + st * AT_TILE + k * 2048));
-          umma_bf16_ss(tO, a, bd, idesc_pv, (j | k) != 0);
+          umma_bf16_ts(tO, tP + 8 * k, bd, idesc_pv, (j | k) != 0);
         }
         umma_commit(o_full);
         umma_commit(kv_empty0 + 8 * st);
       }
       __syncwarp();
+      if (++st == AT_STAGES) { st = 0; ph ^= 1; }
     }
   } else {
     const int quarter = warp & 3;
     const int row = quarter * 32 + lane;
     const uint32_t lane_off = (uint32_t)(quarter * 32) << 16;
     const float sl2 = p.scale_log2;
-    float m_used = -INFINITY;  // maximum the exponents are taken against (raw score units)
+    // reference the exponents are taken against, in log2 units and ALWAYS an integer (ceil of the scaled row maximum when
+    // it was last refreshed): MAGIC - mb is then exact in fp32, which the FMA-pipe exp2 needs, and rescales of O are
+    // exact powers of two
+    float mb = -INFINITY;
     float l = 0.f;
-    uint8_t* prow = sP + row * 128;
-    const int sw = row & 7;
     for (int j = 0; j < nkv; ++j) {
       mbar_wait(s_full, j & 1);
       tc_fence_after();
@@ -170,7 +190,7 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       if (kv_left < 128) {
 #pragma unroll
         for (int i = 0; i < 128; ++i)
-          if (i >= kv_left) sv[i] = 0xff800000u;  // -inf: exp2 -> 0, never the maximum
+          if (i >= kv_left) sv[i] = 0xff800000u;  // -inf: exp2 -> 0 (2^-125 on the FMA pipe), never the maximum
       }
       float mx0 = -INFINITY, mx1 = -INFINITY, mx2 = -INFINITY, mx3 = -INFINITY;
 #pragma unroll
@@ -181,27 +201,43 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
         mx3 = max3(mx3, __uint_as_float(sv[i + 6]), __uint_as_float(sv[i + 7]));
       }
       const float mx = fmaxf(fmaxf(mx0, mx1), fmaxf(mx2, mx3));
-      // refresh the reference maximum only when it is stale by more than 2^AT_RESCALE_LOG2 (always on the first tile)
-      const bool stale = (mx - m_used) * sl2 > AT_RESCALE_LOG2;
+      // refresh the reference only when it is stale by more than 2^AT_RESCALE_LOG2 (always on the first tile)
+      const float mxs = mx * sl2;
+      const bool stale = mxs - mb > AT_RESCALE_LOG2;
       float alpha = 1.0f;
       if (stale) {
-        alpha = ex2((m_used - mx) * sl2);  // m_used = -inf -> 0
-        m_used = mx;
+        const float nb = ceilf(mxs);
+        alpha = ex2(mb - nb);  // mb = -inf -> 0
+        mb = nb;
       }
-      const float mb = m_used * sl2;
-      // exponent = s * scale*log2e - m*scale*log2e: two columns per FFMA2 / FADD2 (half the issue slots of scalar fp32).
-      // Moving a share of the exponentials to an FMA-pipe polynomial (Cody-Waite + degree 3, as FlashAttention-4 does) was
-      // measured and rejected: 25 / 37.5 / 50 % of the columns cost +4 / +6.5 / +8.5 % (profiles/r01b_attn_ab.log) — FFMA2
-      // does not double the fp32 rate on this part, so the polynomial is no cheaper than the MUFU it replaces.
+      // exponent = s * scale*log2e - mb: two columns per FFMA2 (half the issue slots of scalar fp32)
       const uint64_t sl2_2 = pack2(sl2, sl2), nmb2 = pack2(-mb, -mb);
+      const uint64_t mg2 = pack2(AT_MAGIC - mb, AT_MAGIC - mb), neg1 = pack2(-1.f, -1.f);
+      const uint64_t c0 = pack2(AT_C0, AT_C0), c1 = pack2(AT_C1, AT_C1), c2 = pack2(AT_C2, AT_C2), c3 = pack2(AT_C3, AT_C3);
+      const float lo = (mb - 125.0f) * p.inv_scale_log2;  // scores below it would leave the exponent field: clamp
       uint64_t sumA = 0ull, sumB = 0ull;  // (0.f, 0.f)
       uint32_t pk[64];
 #pragma unroll
       for (int i = 0; i < 64; ++i) {
-        const uint64_t x2 = fma2(pack2u(sv[2 * i], sv[2 * i + 1]), sl2_2, nmb2);
-        float x0, x1;
-        unpack2(x2, x0, x1);
-        const float e0 = ex2(x0), e1 = ex2(x1);
+        float e0, e1;
+        if (POLY > 0 && ((i & 7) * POLY) % 8 < POLY) {
+          const uint64_t s2 = pack2(fmaxf(__uint_as_float(sv[2 * i]), lo), fmaxf(__uint_as_float(sv[2 * i + 1]), lo));
+          const uint64_t t2 = fma2(s2, sl2_2, mg2);   // MAGIC + n, n = round(x)
+          const uint64_t nm = fma2(t2, neg1, mg2);    // -mb - n (exact)
+          const uint64_t fr = fma2(s2, sl2_2, nm);    // f = x - n in [-0.5, 0.5]
+          const uint64_t pl = fma2(fma2(fma2(c3, fr, c2), fr, c1), fr, c0);
+          uint32_t tb0, tb1, pb0, pb1;
+          unpack2u(t2, tb0, tb1);
+          unpack2u(pl, pb0, pb1);
+          e0 = __uint_as_float(pb0 + (tb0 << 23));   // 2^f * 2^n: n sits in the low mantissa bits of MAGIC + n
+          e1 = __uint_as_float(pb1 + (tb1 << 23));
+        } else {
+          const uint64_t x2 = fma2(pack2u(sv[2 * i], sv[2 * i + 1]), sl2_2, nmb2);
+          float x0, x1;
+          unpack2(x2, x0, x1);
+          e0 = ex2(x0);
+          e1 = ex2(x1);
+        }
         if (i & 1) sumB = add2(sumB, pack2(e0, e1));
         else sumA = add2(sumA, pack2(e0, e1));
         pk[i] = pack_act2<F16>(e0, e1);
@@ -210,7 +246,7 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
       unpack2(add2(sumA, sumB), s0, s1);
       l = l * alpha + (s0 + s1);
       if (j > 0) {
-        mbar_wait(o_full, (j - 1) & 1);  // PV(j-1) retired: sP may be overwritten, O may be touched
+        mbar_wait(o_full, (j - 1) & 1);  // PV(j-1) retired: P may be overwritten, O may be touched
         tc_fence_after();
         if (__any_sync(0xffffffffu, stale)) {
           // rescale this row of the O accumulator in TMEM (rare after the first few kv tiles)
@@ -224,16 +260,14 @@ attn_kernel(const __grid_constant__ CUtensorMap tmQ, const __grid_constant__ CUt
             tmem_st16(tO + lane_off + c, ov);
             tmem_st16(tO + lane_off + c + 16, ov + 16);
           }
-          tmem_wait_st();
         }
       }
-      // 16 x 16-byte chunks of the row (8 bf16 each) into the two 128B-swizzled K-major P tiles
-#pragma unroll
-      for (int q = 0; q < 16; ++q) {
-        const uint4 u = make_uint4(pk[4 * q], pk[4 * q + 1], pk[4 * q + 2], pk[4 * q + 3]);
-        *reinterpret_cast<uint4*>(prow + (q >> 3) * AT_TILE + (((q & 7) ^ sw) << 4)) = u;
-      }
-      fence_proxy_async_smem();  // generic-proxy smem writes -> visible to the tensor core (async proxy)
+      // P(j): 64 columns of packed pairs, row = lane
+      tmem_st16(tP + lane_off, pk);
+      tmem_st16(tP + lane_off + 16, pk + 16);
+      tmem_st16(tP + lane_off + 32, pk + 32);
+      tmem_st16(tP + lane_off + 48, pk + 48);
+      tmem_wait_st();
       tc_fence_before();
       __syncwarp();
       if (lane == 0) mbar_arrive(p_full);
@@ -436,12 +470,29 @@ int attention(const AttnArgs& a, cudaStream_t s) {
   B2V_CHECK(a.ldq % 8 == 0 && a.ldkv % 8 == 0 && a.ldo % 8 == 0, "attention: leading dims must be multiples of 8");
   B2V_CHECK(a.heads <= 65535 && a.nb <= 65535, "attention: grid too large");
   B2V_CHECK(act_ok(a.adt), "attention: activation dtype must be bf16 or fp16");
+  // B2V_ATTN_POLY = 0..3 picks the share of FMA-pipe exponentials for A/B runs (tools/attn_ab.py); the default is the
+  // fastest measured (profiles/r02_attn_ab.md)
+  using Kern = void (*)(CUtensorMap, CUtensorMap, CUtensorMap, AttnParams);
+  struct Variant { Kern bf16, f16; };
+  static const Variant variants[] = {
+#define B2V_AV(P) {attn_kernel<false, P>, attn_kernel<true, P>}
+      B2V_AV(0), B2V_AV(1), B2V_AV(2), B2V_AV(3),
+#undef B2V_AV
+  };
+  constexpr int n_variants = (int)(sizeof(variants) / sizeof(variants[0]));
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
+  static int variant = AT_DEFAULT_POLY;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(attn_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);
-    if (attr_err == cudaSuccess)
-      attr_err = cudaFuncSetAttribute(attn_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);
+    if (const char* e = getenv("B2V_ATTN_POLY")) {
+      const int v = atoi(e);
+      if (v >= 0 && v < n_variants) variant = v;
+    }
+    for (int i = 0; i < n_variants && attr_err == cudaSuccess; ++i) {
+      attr_err = cudaFuncSetAttribute(variants[i].bf16, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);
+      if (attr_err == cudaSuccess)
+        attr_err = cudaFuncSetAttribute(variants[i].f16, cudaFuncAttributeMaxDynamicSharedMemorySize, AT_SMEM);
+    }
   });
   if (attr_err != cudaSuccess) return fail(B2V_ERR_CUDA, "attention smem attr: %s", cudaGetErrorString(attr_err));
   CUtensorMap tmQ, tmK, tmV;
@@ -463,9 +514,10 @@ int attention(const AttnArgs& a, cudaStream_t s) {
   p.Sq = a.Sq; p.Skv = a.Skv; p.kv_group = a.kv_group;
   p.nkv = (a.Skv + 127) / 128;
   p.scale_log2 = a.scale * 1.4426950408889634f;
+  p.inv_scale_log2 = 1.0f / p.scale_log2;
   dim3 grid((unsigned)((a.Sq + 127) / 128), (unsigned)a.heads, (unsigned)a.nb);
-  if (a.adt == B2V_F16) B2V_CUDA_OK(launch_pdl(attn_kernel<true>, grid, dim3(AT_THREADS), AT_SMEM, s, tmQ, tmK, tmV, p));
-  else B2V_CUDA_OK(launch_pdl(attn_kernel<false>, grid, dim3(AT_THREADS), AT_SMEM, s, tmQ, tmK, tmV, p));
+  const Kern kern = a.adt == B2V_F16 ? variants[variant].f16 : variants[variant].bf16;
+  B2V_CUDA_OK(launch_pdl(kern, grid, dim3(AT_THREADS), AT_SMEM, s, tmQ, tmK, tmV, p));
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;

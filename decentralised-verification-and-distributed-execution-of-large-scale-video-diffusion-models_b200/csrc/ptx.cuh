@@ -281,6 +281,16 @@ __device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t smem_addr) {
   d |= (uint64_t)2 << 61;                        // SWIZZLE_128B
   return d;
 }
+// K-major operand tile WITHOUT swizzle: core matrices of 8 rows x 16 bytes stored contiguously (128 B); `lbo` = byte
+// distance between core matrices adjacent in K, `sbo` = between core matrices adjacent in M / N
+__device__ __forceinline__ uint64_t umma_desc_nosw(uint32_t smem_addr, uint32_t lbo, uint32_t sbo) {
+  uint64_t d = 0;
+  d |= (uint64_t)((smem_addr >> 4) & 0x3FFFu);
+  d |= (uint64_t)((lbo >> 4) & 0x3FFFu) << 16;
+  d |= (uint64_t)((sbo >> 4) & 0x3FFFu) << 32;
+  d |= (uint64_t)1 << 46;
+  return d;
+}
 // instruction descriptor of kind::f16: fp32 accumulator (bits [4,6) = 1), A format bits [7,10) and B format bits
 // [10,13) (0 = fp16, 1 = bf16), both operands K-major, M x N tile
 __host__ __device__ constexpr uint32_t umma_idesc_16(int M, int N, bool a_f16, bool b_f16) {
@@ -302,6 +312,9 @@ __device__ __forceinline__ uint64_t pack2u(uint32_t a, uint32_t b) {
 }
 __device__ __forceinline__ void unpack2(uint64_t r, float& a, float& b) {
   asm("mov.b64 {%0, %1}, %2;" : "=f"(a), "=f"(b) : "l"(r));
+}
+__device__ __forceinline__ void unpack2u(uint64_t r, uint32_t& a, uint32_t& b) {
+  asm("mov.b64 {%0, %1}, %2;" : "=r"(a), "=r"(b) : "l"(r));
 }
 __device__ __forceinline__ uint64_t fma2(uint64_t a, uint64_t b, uint64_t c) {
   uint64_t d;
