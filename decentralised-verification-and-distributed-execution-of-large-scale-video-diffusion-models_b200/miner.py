@@ -67,6 +67,99 @@ class Trajectory:
                 "latents": zs, "noise_preds": es, "alphas": list(self.alphas), "leaf_data": leaf_b64}
 
 
+    def reveal(self, indices) -> Dict[int, Optional[Tuple[str, str, List[str]]]]:
+        """Only the requested leaves, in the wire form of ``open_leaves`` / ``forward_reveal_leaves`` (miner.py:813-888):
+        {i: (z_b64, eps_b64, [sibling_b64, ...]) or None}. As in the reference ``i`` is looked up among the KEYS of
+        leaf_data, i.e. the committed timesteps. Only the requested leaf images are base64-encoded (on the device) and
+        cross PCIe: k of n leaves cost k/n of ``wire()`` — at ZeroscopeXL 9.4 MB of text per leaf instead of 472 MB for
+        a 50-step trajectory."""
+        import base64
+        indices = [int(i) for i in indices]
+        pos = {int(t): k for k, t in enumerate(self.timesteps)}
+        hit = [i for i in dict.fromkeys(indices) if i in pos]
+        out: Dict[int, Optional[Tuple[str, str, List[str]]]] = {i: None for i in indices}
+        if not hit:
+            return out
+        digests = self.digests
+        if digests is None:
+            digests = ops.sha256_leaves(self.latents, self.noise_preds, prefixes=self.timesteps)
+            self.digests = digests
+        _, paths = ops.merkle_build(digests)
+        plist = proof._paths_as_lists(paths, len(self.timesteps))
+        zs = leaves_b64([self.latents[pos[i]] for i in hit])
+        es = leaves_b64([self.noise_preds[pos[i]] for i in hit])
+        for k, i in enumerate(hit):
+            out[i] = (zs[k], es[k], [base64.b64encode(pp).decode("ascii") for pp in plist[pos[i]]])
+        return out
+
+
+class LeafStore:
+    """The miner's ``_leaf_data_by_request`` (miner.py:131, 636): committed trajectories parked per
+    ``(caller_hotkey, request_id)`` until the validator asks for leaves, DEVICE-resident (a 50-step XL trajectory is
+    177 MB of HBM; the reference keeps the same bytes on the host) and deleted after one reveal like the reference does
+    (miner.py:420, 841, 877)."""
+
+    def __init__(self):
+        self._leaf_data_by_request: Dict[Tuple[str, str], Trajectory] = {}
+
+    def put(self, caller_hotkey, request_id, trajectory: Trajectory):
+        self._leaf_data_by_request[(caller_hotkey, request_id)] = trajectory   # miner.py:636
+
+    def __len__(self):
+        return len(self._leaf_data_by_request)
+
+    def open_leaves(self, indices, request_id=None, caller_hotkey=None):
+        """miner.py:813-842 (the RPC): only the requested leaves; unknown request -> every index maps to None."""
+        indices = [int(i) for i in indices]
+        if caller_hotkey is None:
+            caller_hotkey = "unknown"
+        if request_id is None:
+            return {i: None for i in indices}
+        key = (caller_hotkey, request_id)
+        traj = self._leaf_data_by_request.get(key)
+        if not traj:
+            return {i: None for i in indices}
+        result = traj.reveal(indices)
+        del self._leaf_data_by_request[key]
+        return result
+
+    def forward_reveal_leaves(self, synapse):
+        """miner.py:844-888: ``synapse`` is a RevealLeavesSynapse (protocol.py:74-95: indices, request_id,
+        caller_hotkey, leaves) or anything with those attributes; never raises."""
+        try:
+            indices = [int(i) for i in synapse.indices]
+            key = (synapse.caller_hotkey, synapse.request_id)
+            traj = self._leaf_data_by_request.get(key)
+            if not traj:
+                synapse.leaves = {i: None for i in indices}
+                return synapse
+            result = traj.reveal(indices)
+            del self._leaf_data_by_request[key]
+            synapse.leaves = result
+            return synapse
+        except Exception:
+            synapse.leaves = {i: None for i in synapse.indices}
+            return synapse
+
+    def spot_check_all(self, caller_hotkey, request_id):
+        """The spot-check fast path of ``forward`` (miner.py:352-456: seed 0, empty challenge): the indices are lost in
+        serialisation there, so the reference returns EVERY leaf of the request as ``proof['leaf_data']``. Same here
+        (this is the expensive form; validators that can should send RevealLeavesSynapse)."""
+        empty = {"merkle_root": "", "signature": "", "seed": 0, "challenge": "", "leaf_data": {}}
+        if caller_hotkey is None:
+            return empty
+        key = (caller_hotkey, request_id)
+        traj = self._leaf_data_by_request.get(key)
+        if not traj:
+            return empty
+        try:
+            result = traj.reveal(traj.timesteps)
+            del self._leaf_data_by_request[key]
+            return dict(empty, leaf_data=result)
+        except Exception:
+            return empty
+
+
 def decode_final_frames(pipe, z, reference_view=True):
     """InferNet/neurons/miner.py:593-600: the final latents [B,C,T,h,w] -> ``pipe.vae.decode(flat / scaling).sample``
     over all B*T frames at once -> numpy [T,H,W,3] in the decoder's [-1,1] range (the array ``export_to_video`` gets).

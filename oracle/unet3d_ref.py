@@ -73,6 +73,11 @@ class TimestepEmbedding(nn.Module):
 # attention blocks
 # ---------------------------------------------------------------------------------------------------------------
 class Attention(nn.Module):
+    # bench.py's CPU arm sets this: the same attention through F.scaled_dot_product_attention (what diffusers'
+    # default AttnProcessor2_0 calls) — the materialised [b, heads, s, s] score tensor below is 54 GB at the
+    # ZeroscopeXL 16-frame window. Tests keep the explicit softmax.
+    use_sdpa = False
+
     def __init__(self, query_dim, heads, dim_head, cross_attention_dim=None):
         super().__init__()
         inner = heads * dim_head
@@ -90,8 +95,11 @@ class Attention(nn.Module):
         q = self.to_q(x).view(b, s, self.heads, -1).transpose(1, 2)
         k = self.to_k(ctx).view(b, ctx.shape[1], self.heads, -1).transpose(1, 2)
         v = self.to_v(ctx).view(b, ctx.shape[1], self.heads, -1).transpose(1, 2)
-        w = torch.softmax((q @ k.transpose(-1, -2)) * self.scale, dim=-1)
-        o = (w @ v).transpose(1, 2).reshape(b, s, -1)
+        if Attention.use_sdpa:
+            o = F.scaled_dot_product_attention(q, k, v, scale=self.scale).transpose(1, 2).reshape(b, s, -1)
+        else:
+            w = torch.softmax((q @ k.transpose(-1, -2)) * self.scale, dim=-1)
+            o = (w @ v).transpose(1, 2).reshape(b, s, -1)
         return self.to_out[0](o)
 
 

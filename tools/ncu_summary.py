@@ -17,6 +17,7 @@ KEYS = [
     ("sm__pipe_alu_cycles_active.avg.pct_of_peak_sustained_active", "alu pipe %"),
     ("sm__pipe_fma_cycles_active.avg.pct_of_peak_sustained_active", "fma pipe %"),
     ("sm__inst_executed_pipe_xu.avg.pct_of_peak_sustained_active", "xu (MUFU) %"),
+    ("smsp__issue_active.avg.pct_of_peak_sustained_active", "issue active %"),
     ("sm__warps_active.avg.pct_of_peak_sustained_active", "occupancy %"),
     ("launch__registers_per_thread", "regs"),
     ("launch__grid_size", "grid"),

@@ -44,3 +44,11 @@ if what in ("norm", "all"):
     g, b = torch.ones(320, device=dev), torch.zeros(320, device=dev)
     t(lambda: ops.group_norm(x, g, b, 32, 32, 1e-5, True), "group_norm+silu L0 (items=32)")
     t(lambda: ops.layer_norm(x, g, b), "layer_norm L0")
+if what in ("sha", "all"):
+    # the commitment of one 50-step ZeroscopeXL trajectory: 50 leaves of be16(t) || z fp16 || eps fp16 (3 538 946 B each)
+    elems = 4 * 24 * 72 * 128
+    zs = torch.randn(50, elems, device=dev).half()
+    es = torch.randn(50, elems, device=dev).half()
+    zl, el = [zs[i] for i in range(50)], [es[i] for i in range(50)]
+    t(lambda: ops.sha256_leaves(zl, el, prefixes=list(range(50)), mode=1), "sha256 chain kernel, 50 XL leaves")
+    t(lambda: ops.sha256_leaves(zl[:1], el[:1], prefixes=[981], mode=3), "sha256 warp kernel, 1 XL leaf")
