@@ -19,6 +19,50 @@ extern "C" int b2v_op_gemm(const void* a_dev, const void* w_dev, const float* bi
   return gemm_tiled(g, (cudaStream_t)stream);
 }
 
+extern "C" int b2v_gn_stats_ok(int64_t M, int N, int64_t rows_per_batch, int groups) {
+  return gn_stats_ok(M, N, rows_per_batch, groups) ? 1 : 0;
+}
+
+extern "C" int b2v_op_gemm_gnstats(const void* a_dev, const void* w_dev, const float* bias_dev, const float* rowbias_dev,
+                                   int64_t rows_per_group, const void* residual_dev, void* out_dev, int64_t M, int N,
+                                   int Kc, int taps, int64_t tap_row_stride, int64_t rows_per_batch, int act_dtype,
+                                   float* gn_stats_dev, int gn_groups, void* stream) {
+  B2V_CHECK(a_dev && w_dev && out_dev && gn_stats_dev, "null argument");
+  B2V_TRY(b2v_device_check());
+  B2V_CHECK(gn_stats_ok(M, N, rows_per_batch, gn_groups), "this GEMM shape does not emit GroupNorm statistics (b2v_gn_stats_ok)");
+  GemmArgs g;
+  g.adt = act_dtype;
+  g.a = a_dev; g.w = w_dev; g.bias = bias_dev; g.rowbias = rowbias_dev; g.rows_per_group = rows_per_group;
+  g.residual = residual_dev; g.out = out_dev; g.M = M; g.N = N; g.Kc = Kc; g.taps = taps;
+  g.tap_row_stride = tap_row_stride; g.rows_per_batch = rows_per_batch;
+  g.gn_stats = gn_stats_dev; g.gn_groups = gn_groups;
+  return gemm_tiled(g, (cudaStream_t)stream);
+}
+
+extern "C" int b2v_op_conv3x3_gnstats(const void* x_dev, const void* w_dev, const float* bias_dev,
+                                      const float* rowbias_dev, int64_t rows_per_group, const void* residual_dev,
+                                      void* out_dev, int N, int H, int W, int Cin, int Cout, int act_dtype,
+                                      float* gn_stats_dev, int gn_groups, void* stream) {
+  B2V_CHECK(x_dev && w_dev && out_dev && gn_stats_dev, "null argument");
+  B2V_TRY(b2v_device_check());
+  B2V_CHECK(gn_stats_ok((int64_t)N * H * W, Cout, 0, gn_groups), "this conv shape does not emit GroupNorm statistics");
+  ConvArgs c;
+  c.adt = act_dtype;
+  c.x = x_dev; c.w = w_dev; c.bias = bias_dev; c.rowbias = rowbias_dev; c.rows_per_group = rows_per_group;
+  c.residual = residual_dev; c.out = out_dev; c.N = N; c.H = H; c.W = W; c.Cin = Cin; c.Cout = Cout; c.stride = 1;
+  c.gn_stats = gn_stats_dev; c.gn_groups = gn_groups;
+  return conv3x3_im2col(c, (cudaStream_t)stream);
+}
+
+extern "C" int b2v_op_group_norm_pre(const void* x_dev, int C, const float* gamma_dev, const float* beta_dev, void* y_dev,
+                                     int64_t n_items, int64_t rows_per_item, int groups, float eps, int silu,
+                                     void* scratch_dev, const float* pre_dev, int act_dtype, void* stream) {
+  B2V_CHECK(x_dev && gamma_dev && beta_dev && y_dev && scratch_dev && pre_dev, "null argument");
+  B2V_TRY(b2v_device_check());
+  return group_norm(act_dtype, x_dev, C, nullptr, 0, gamma_dev, beta_dev, y_dev, n_items, rows_per_item, groups, eps, silu,
+                    scratch_dev, (cudaStream_t)stream, pre_dev);
+}
+
 extern "C" size_t b2v_op_conv3x3_scratch_bytes(int N, int H, int W, int Cin, int stride, int mode) {
   if (mode == 0) return 0;
   const int64_t P = (H - 1) / stride + 1, Q = (W - 1) / stride + 1;

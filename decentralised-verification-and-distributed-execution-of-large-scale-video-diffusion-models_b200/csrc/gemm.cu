@@ -86,6 +86,9 @@ struct GemmParams {
   void* out_raw;
   int nc_dtype, nc_cout, nc_F;
   int64_t nc_HW;
+  // GroupNorm statistics of the output (GNG > 0 instantiations): [M/32][gn_groups]{sum, sumsq}
+  float* gn_stats;
+  int gn_groups;
 };
 
 constexpr int EPI_PLAIN = 0, EPI_GEGLU_T = 1, EPI_NCFHW = 2;
@@ -134,7 +137,11 @@ __device__ __forceinline__ uint64_t gelu_fast2(uint64_t x2) {
 // GEMMs were bound by the LSU/L2 request rate of the latter). With RES the residual panel ARRIVES in the same buffer by
 // TMA load and is updated in place; when a tile is one panel wide (all but BN = 256) two buffers alternate so the
 // residual of the NEXT tile is already in flight while this one is processed.
-template <int BN, int MODE, bool GEGLU, bool RES, int CG, bool F16>
+// GNG > 0 (BN = 160 only): the 80 columns of this warp are GNG whole GroupNorm groups of the OUTPUT tensor. Every lane
+// accumulates {sum, sum of squares} of its row per group while the values pass through its registers, the warp folds the
+// 32 rows with a fixed-order shuffle tree (deterministic) and writes 2 GNG floats per 32-row block: the consumer's
+// GroupNorm needs no statistics pass over the activation (norm.cu: group_norm with `pre`).
+template <int BN, int MODE, bool GEGLU, bool RES, int CG, bool F16, int GNG>
 __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtensorMap* tmO, const CUtensorMap* tmR,
                                               uint8_t* stage0, uint32_t rbar0, uint32_t tmem_base, uint32_t tfull0,
                                               uint32_t tempty0, int warp, int lane, int num_tiles) {
@@ -184,6 +191,9 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
       rb = p.rowbias + (gclamped / p.rows_per_group) * (int64_t)p.N + wcol0;
     }
     const uint32_t tacc = tmem_base + acc * Cfg::ACC_STRIDE + ((uint32_t)(quarter * 32) << 16);
+    float gsum[GNG > 0 ? GNG : 1], gsq[GNG > 0 ? GNG : 1];
+#pragma unroll
+    for (int i = 0; i < (GNG > 0 ? GNG : 1); ++i) gsum[i] = gsq[i] = 0.f;
     uint32_t v[2][16];
     uint32_t g[GEGLU ? 2 : 1][16];
     // bias (+ time-embedding row bias) of a chunk is fetched ONE CHUNK AHEAD, together with the chunk's TMEM load: the
@@ -309,6 +319,15 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
         o.w = pack_act2<F16>(f[8 * j + 6], f[8 * j + 7]);
         sts128(dst, o);
       }
+      if constexpr (GNG > 0) {
+        constexpr int CPG = (OUT_COLS / 2) / GNG;  // channels per group
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int gi = (c + j) / CPG;  // compile-time: the chunk loop is fully unrolled
+          gsum[gi] += f[j];
+          gsq[gi] = fmaf(f[j], f[j], gsq[gi]);
+        }
+      }
       if (k == CH_PER_PANEL - 1) {
         // ---- panel complete: ONE TMA store of 32 rows x PANEL_COLS (rows outside the tensor / slab are clipped) ----
         fence_proxy_async_smem();
@@ -327,6 +346,40 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
       else mbar_arrive(tempty0 + 8 * acc);
     }
     if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    if constexpr (GNG > 0) {
+      // fold the 32 rows: reduce-scatter over the lane bits 4, 3, ... (a fixed tree), then all-reduce over the rest.
+      // Afterwards lane l holds value index l >> SH (even index = sum, odd = sum of squares of group index / 2).
+      constexpr int NV = 2 * GNG;
+      float rv[NV];
+#pragma unroll
+      for (int i = 0; i < GNG; ++i) { rv[2 * i] = gsum[i]; rv[2 * i + 1] = gsq[i]; }
+      int n = NV;
+#pragma unroll
+      for (int off = 16; off >= 1; off >>= 1) {
+        if (n > 1) {
+          n >>= 1;
+          const bool up = (lane & off) != 0;
+#pragma unroll
+          for (int i = 0; i < NV / 2; ++i) {
+            if (i < n) {
+              const float send = up ? rv[i] : rv[i + n];
+              const float keep = up ? rv[i + n] : rv[i];
+              rv[i] = keep + __shfl_xor_sync(0xffffffffu, send, off);
+            }
+          }
+        } else {
+          rv[0] += __shfl_xor_sync(0xffffffffu, rv[0], off);
+        }
+      }
+      constexpr int SH = NV == 16 ? 1 : (NV == 8 ? 2 : 3);
+      if ((lane & ((1 << SH) - 1)) == 0) {
+        constexpr int CPG = (OUT_COLS / 2) / GNG;
+        const int idx = lane >> SH;
+        const int64_t grow = (MODE == 0 ? (int64_t)slab * p.rows_per_batch : 0) + row0;  // first row of this warp
+        const int g0 = wcol0 / CPG;
+        p.gn_stats[(((grow >> 5) * p.gn_groups) + g0 + (idx >> 1)) * 2 + (idx & 1)] = rv[0];
+      }
+    }
   }
   if (lane == 0) bulk_wait0();  // this warp's TMA stores have drained before its shared memory goes away
 }
@@ -372,7 +425,7 @@ __device__ __forceinline__ void epilogue_loop_ncfhw(const GemmParams& p, uint32_
 }
 
 // MODE 0: A through a 3-D tiled tensor map (channels, rows, slabs); MODE 1: A through a 4-D im2col map.
-template <int BN, int MODE, int EPI, bool RES, int CG, bool F16>
+template <int BN, int MODE, int EPI, bool RES, int CG, bool F16, int GNG = 0>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR, const GemmParams p) {
@@ -511,7 +564,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if constexpr (EPI == EPI_NCFHW)
       epilogue_loop_ncfhw<Cfg::ACC_STRIDE>(p, tmem_base, tfull0, tempty0, warp, lane, num_tiles);
     else
-      epilogue_loop<BN, MODE, EPI == EPI_GEGLU_T, RES, CG, F16>(p, &tmO, &tmR,
+      epilogue_loop<BN, MODE, EPI == EPI_GEGLU_T, RES, CG, F16, GNG>(p, &tmO, &tmR,
                                                                 sEpi + (warp - 2) * Cfg::NBUF * Cfg::PANEL_BYTES,
                                                                 rbar0 + 16 * (warp - 2), tmem_base, tfull0, tempty0,
                                                                 warp, lane, num_tiles);
@@ -527,7 +580,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   }
 }
 
-template <int BN, int MODE, int EPI, bool RES, int CG, bool F16>
+template <int BN, int MODE, int EPI, bool RES, int CG, bool F16, int GNG = 0>
 int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int64_t out_rows_per_slab,
                 int64_t out_slabs, cudaStream_t s) {
   using Cfg = TileCfg<BN, EPI == EPI_GEGLU_T, RES, CG>;
@@ -543,14 +596,14 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(gemm_kernel<BN, MODE, EPI, RES, CG, F16>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    attr_err = cudaFuncSetAttribute(gemm_kernel<BN, MODE, EPI, RES, CG, F16, GNG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     Cfg::SMEM_BYTES);
   });
   if (attr_err != cudaSuccess) return fail(B2V_ERR_CUDA, "gemm smem attr: %s", cudaGetErrorString(attr_err));
   const int units = p.num_m_units * p.num_n_tiles;
   if (CG == 1) {
     const int grid = units < sm_count() ? units : sm_count();
-    B2V_CUDA_OK(launch_pdl(gemm_kernel<BN, MODE, EPI, RES, CG, F16>, dim3((unsigned)grid), dim3(NUM_THREADS), Cfg::SMEM_BYTES, s,
+    B2V_CUDA_OK(launch_pdl(gemm_kernel<BN, MODE, EPI, RES, CG, F16, GNG>, dim3((unsigned)grid), dim3(NUM_THREADS), Cfg::SMEM_BYTES, s,
                            tmA, tmB, tmO, tmR, p));
   } else {
     // one CTA pair (cluster of 2 = the two SMs of a TPC) per work unit, persistent over the units
@@ -567,18 +620,18 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
     attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
     cfg.attrs = attr;
     cfg.numAttrs = 2;
-    B2V_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_kernel<BN, MODE, EPI, RES, CG, F16>, tmA, tmB, tmO, tmR, p));
+    B2V_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_kernel<BN, MODE, EPI, RES, CG, F16, GNG>, tmA, tmB, tmO, tmR, p));
   }
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;
 }
 
-template <int BN, int MODE, int CG, bool F16>
+template <int BN, int MODE, int CG, bool F16, int GNG = 0>
 int launch_plain(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int64_t orows, int64_t oslabs,
                  cudaStream_t s) {
-  if (p.residual) return launch_gemm<BN, MODE, EPI_PLAIN, true, CG, F16>(tmA, tmB, p, orows, oslabs, s);
-  return launch_gemm<BN, MODE, EPI_PLAIN, false, CG, F16>(tmA, tmB, p, orows, oslabs, s);
+  if (p.residual) return launch_gemm<BN, MODE, EPI_PLAIN, true, CG, F16, GNG>(tmA, tmB, p, orows, oslabs, s);
+  return launch_gemm<BN, MODE, EPI_PLAIN, false, CG, F16, GNG>(tmA, tmB, p, orows, oslabs, s);
 }
 
 template <int MODE, int CG, bool F16>
@@ -590,7 +643,17 @@ int dispatch_gemm_t(int bn, bool geglu, const CUtensorMap& tmA, const CUtensorMa
   }
   switch (bn) {
     case 256: return launch_plain<256, MODE, CG, F16>(tmA, tmB, p, orows, oslabs, s);
-    case 160: return launch_plain<160, MODE, CG, F16>(tmA, tmB, p, orows, oslabs, s);
+    case 160:
+      if constexpr (CG == 2) {  // statistics-emitting epilogues exist for CTA pairs only (gn_stats_ok)
+        if (p.gn_stats) {
+          const int cpg = p.N / p.gn_groups;
+          if (cpg == 10) return launch_plain<160, MODE, CG, F16, 8>(tmA, tmB, p, orows, oslabs, s);
+          if (cpg == 20) return launch_plain<160, MODE, CG, F16, 4>(tmA, tmB, p, orows, oslabs, s);
+          if (cpg == 40) return launch_plain<160, MODE, CG, F16, 2>(tmA, tmB, p, orows, oslabs, s);
+          return fail(B2V_ERR_ARG, "gn_stats: %d channels per group unsupported", cpg);
+        }
+      }
+      return launch_plain<160, MODE, CG, F16>(tmA, tmB, p, orows, oslabs, s);
     case 128: return launch_plain<128, MODE, CG, F16>(tmA, tmB, p, orows, oslabs, s);
     case 64: return launch_plain<64, MODE, CG, F16>(tmA, tmB, p, orows, oslabs, s);
   }
@@ -653,6 +716,23 @@ int pick_bn(int N, bool geglu, int64_t m_units, int cg) {
   return (N % 64 == 0) ? 64 : 0;
 }
 
+// The epilogue emits GroupNorm statistics when a warp's 80 output columns are whole groups (N a multiple of 160, 10 / 20
+// / 40 channels per group), the tile is 160 wide by the cost model's own choice, the rows form whole CTA-pair units
+// (no clipped rows in any 32-row block) and there are at least two 128-row tiles per slab (CTA pairs).
+static bool gn_stats_shape_ok(int64_t M, int N, int64_t rpb, int groups, int bn, int cg) {
+  if (groups <= 0 || N % groups != 0) return false;
+  const int cpg = N / groups;
+  return bn == 160 && cg == 2 && N % 160 == 0 && (cpg == 10 || cpg == 20 || cpg == 40) && rpb % (BM * 2) == 0 && M % rpb == 0;
+}
+bool gn_stats_ok(int64_t M, int N, int64_t rows_per_batch, int groups) {
+  const int64_t rpb = rows_per_batch > 0 ? rows_per_batch : M;
+  if (M <= 0 || M % rpb != 0) return false;
+  const int64_t slabs = M / rpb, m_tiles_per_slab = (rpb + BM - 1) / BM;
+  const int cg = pick_cg(m_tiles_per_slab);
+  const int bn = pick_bn(N, false, slabs * ((m_tiles_per_slab + cg - 1) / cg), cg);
+  return gn_stats_shape_ok(M, N, rpb, groups, bn, cg);
+}
+
 static bool trace_on() {
   static int on = -1;
   if (on < 0) on = getenv("B2V_TRACE") != nullptr;
@@ -703,6 +783,10 @@ int gemm_tiled(const GemmArgs& g, cudaStream_t s) {
   p.out = g.out;
   p.ldo = g.ldo > 0 ? g.ldo : (geglu ? g.N / 2 : g.N);
   p.gelu = (g.flags & B2V_EPI_GELU) ? 1 : 0;
+  if (g.gn_stats && !geglu && !p.gelu && gn_stats_shape_ok(g.M, g.N, rpb, g.gn_groups, bn, cg)) {
+    p.gn_stats = g.gn_stats;
+    p.gn_groups = g.gn_groups;
+  }
   if (cg == 2) return dispatch_gemm<0, 2>(g.adt, bn, geglu, tmA, tmB, p, rpb, slabs, s);
   return dispatch_gemm<0, 1>(g.adt, bn, geglu, tmA, tmB, p, rpb, slabs, s);
 }
@@ -747,6 +831,10 @@ int conv3x3_im2col(const ConvArgs& c, cudaStream_t s) {
   p.out = c.out;
   p.ldo = c.Cout;
   p.gelu = 0;
+  if (c.gn_stats && !c.ncfhw_out && gn_stats_shape_ok(p.M, c.Cout, p.M, c.gn_groups, bn, cg)) {
+    p.gn_stats = c.gn_stats;
+    p.gn_groups = c.gn_groups;
+  }
   if (c.ncfhw_out) {
     B2V_CHECK(c.Cout == 64 && c.ncfhw_cout >= 1 && c.ncfhw_cout <= 16 && c.stride == 1 && c.N % c.ncfhw_F == 0 &&
                   dtype_size(c.ncfhw_dtype) != 0,

@@ -123,6 +123,38 @@ __device__ __forceinline__ void gn_fold_item(const float* __restrict__ partial, 
   __syncthreads();
 }
 
+// Statistics that arrive from the producing GEMM's epilogue come as one {sum, sumsq} per 32-row block and group. When an
+// item has more of them than an apply CTA should fold by itself (temporal norms: F*H*W / 32 blocks per batch element),
+// this kernel folds them once per item — fixed order, fp64 — into ONE partial per (item, group): grid = (groups, items),
+// a warp-strided sum per thread, then a fixed-order tree over the CTA.
+__global__ void __launch_bounds__(256)
+gn_prefold_kernel(const float* __restrict__ pre, int splits, int groups, float* __restrict__ out /*[item][group][2]*/) {
+  __shared__ double2 sh[256];
+  pdl_wait();
+  const int g = blockIdx.x, item = blockIdx.y;
+  double a = 0.0, q = 0.0;
+  for (int sp = threadIdx.x; sp < splits; sp += 256) {
+    const float2 v = __ldg(reinterpret_cast<const float2*>(pre + ((((int64_t)item * splits + sp) * groups + g) << 1)));
+    a += (double)v.x;
+    q += (double)v.y;
+  }
+  sh[threadIdx.x] = make_double2(a, q);
+  __syncthreads();
+  for (int w = 128; w >= 1; w >>= 1) {
+    if (threadIdx.x < w) {
+      const double2 o = sh[threadIdx.x + w];
+      sh[threadIdx.x].x += o.x;
+      sh[threadIdx.x].y += o.y;
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    float* dst = out + (((int64_t)item * groups + g) << 1);
+    dst[0] = (float)sh[0].x;  // the apply pass re-reads them as float partials (splits = 1)
+    dst[1] = (float)sh[0].y;
+  }
+}
+
 __device__ __forceinline__ float tanh_approx(float x) {
   float y;
   asm("tanh.approx.f32 %0, %1;" : "=f"(y) : "f"(x));
@@ -141,12 +173,12 @@ template <bool F16>
 __global__ void __launch_bounds__(GN_MAX_THREADS)
 gn_apply_kernel(const __nv_bfloat16* __restrict__ x1, int C1, const __nv_bfloat16* __restrict__ x2, int C2,
                 const float* __restrict__ gamma, const float* __restrict__ beta, __nv_bfloat16* __restrict__ y,
-                int64_t rows_per_item, int groups, int rpp, int silu, const float* __restrict__ partial, double cnt,
-                float eps) {
+                int64_t rows_per_item, int groups, int rpp, int silu, const float* __restrict__ partial, int splits,
+                double cnt, float eps) {
   __shared__ float2 stats[64];  // {mean, rstd} of this CTA's item, per group
   __shared__ double2 fold_scratch[(GN_MAX_THREADS / 32) * 64];
   pdl_wait();
-  gn_fold_item(partial, blockIdx.y, gridDim.x, groups, cnt, eps, fold_scratch, stats);
+  gn_fold_item(partial, blockIdx.y, splits, groups, cnt, eps, fold_scratch, stats);
   const int C = C1 + C2;
   const int vecs = C >> 3;
   const int cpg = C / groups;
@@ -370,10 +402,12 @@ size_t group_norm_scratch_bytes(int64_t n_items, int64_t rows_per_item, int grou
   return ((partial + 255) & ~(size_t)255) + sizeof(float2) * (size_t)n_items * groups;
 }
 
+constexpr int GN_DIRECT_FOLD_MAX = 512;  // 32-row blocks per item an apply CTA folds by itself (128 KiB out of L2)
+
 template <bool F16>
 static int group_norm_t(const void* x1, int C1, const void* x2, int C2, const float* gamma, const float* beta, void* y,
                         int64_t n_items, int64_t rows_per_item, int groups, float eps, int silu, void* scratch,
-                        cudaStream_t s) {
+                        const float* pre, cudaStream_t s) {
   const int C = C1 + C2;
   B2V_CHECK(C % 8 == 0 && C1 % 8 == 0 && C % groups == 0 && (C / groups) % 2 == 0, "group_norm: C=%d (C1=%d) groups=%d unsupported", C, C1, groups);
   B2V_CHECK(C <= GN_MAX_THREADS * 8, "group_norm: C=%d too wide (max %d)", C, GN_MAX_THREADS * 8);
@@ -389,12 +423,29 @@ static int group_norm_t(const void* x1, int C1, const void* x2, int C2, const fl
   B2V_CHECK(pbytes + 256 + sizeof(float2) * (size_t)n_items * groups <= group_norm_scratch_bytes(n_items, rows_per_item, groups) + 256,
             "group_norm: scratch too small for %d splits", splits);
   dim3 grid((unsigned)splits, (unsigned)n_items);
-  B2V_CUDA_OK(launch_pdl(gn_stats_kernel<F16>, grid, dim3(threads), shb, s, (const __nv_bfloat16*)x1, C1,
-                         (const __nv_bfloat16*)x2, C2, rows_per_item, groups, rpp, partial));
-  count_launch();
+  const float* fold_src = partial;
+  int fold_splits = splits;
+  if (pre) {
+    // statistics emitted by the producing GEMM (one partial per 32-row block): no pass over the activation
+    B2V_CHECK(C2 == 0 && rows_per_item % 32 == 0, "group_norm: precomputed statistics need whole 32-row blocks, no concat");
+    const int64_t blocks = rows_per_item / 32;
+    if (blocks <= GN_DIRECT_FOLD_MAX) {
+      fold_src = pre;
+      fold_splits = (int)blocks;
+    } else {
+      B2V_CUDA_OK(launch_pdl(gn_prefold_kernel, dim3((unsigned)groups, (unsigned)n_items), dim3(256), 0, s, pre,
+                             (int)blocks, groups, partial));
+      count_launch();
+      fold_splits = 1;
+    }
+  } else {
+    B2V_CUDA_OK(launch_pdl(gn_stats_kernel<F16>, grid, dim3(threads), shb, s, (const __nv_bfloat16*)x1, C1,
+                           (const __nv_bfloat16*)x2, C2, rows_per_item, groups, rpp, partial));
+    count_launch();
+  }
   B2V_CUDA_OK(launch_pdl(gn_apply_kernel<F16>, grid, dim3(threads), 0, s, (const __nv_bfloat16*)x1, C1,
                          (const __nv_bfloat16*)x2, C2, gamma, beta, (__nv_bfloat16*)y, rows_per_item, groups, rpp, silu,
-                         (const float*)partial, (double)rows_per_item * (double)(C / groups), eps));
+                         fold_src, fold_splits, (double)rows_per_item * (double)(C / groups), eps));
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;
@@ -402,9 +453,9 @@ static int group_norm_t(const void* x1, int C1, const void* x2, int C2, const fl
 
 int group_norm(int adt, const void* x1, int C1, const void* x2, int C2, const float* gamma, const float* beta, void* y,
                int64_t n_items, int64_t rows_per_item, int groups, float eps, int silu, void* scratch,
-               cudaStream_t s) {
+               cudaStream_t s, const float* pre) {
   B2V_DISPATCH_ACT(adt, F16, return group_norm_t<F16>(x1, C1, x2, C2, gamma, beta, y, n_items, rows_per_item, groups, eps,
-                                                      silu, scratch, s));
+                                                      silu, scratch, pre, s));
   return 0;
 }
 

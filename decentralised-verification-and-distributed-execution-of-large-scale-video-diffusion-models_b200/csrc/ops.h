@@ -11,7 +11,9 @@ namespace b2v {
 // adt = element type of the activations (B2V_BF16 or B2V_F16); upsample / concat / im2col move 2-byte elements blindly
 int group_norm(int adt, const void* x1, int C1, const void* x2, int C2, const float* gamma, const float* beta, void* y,
                int64_t n_items, int64_t rows_per_item, int groups, float eps, int silu, void* scratch,
-               cudaStream_t s);
+               cudaStream_t s, const float* pre = nullptr);
+// pre: {sum, sumsq} per 32-row block and group, [n_items * rows_per_item / 32][groups][2] fp32, as emitted by the GEMM
+// epilogue that produced x1 (GemmArgs::gn_stats): the statistics pass is skipped (x2 must be null)
 size_t group_norm_scratch_bytes(int64_t n_items, int64_t rows_per_item, int groups);
 int layer_norm(int adt, const void* x, const float* gamma, const float* beta, void* y, int64_t rows, int C, float eps,
                cudaStream_t s);

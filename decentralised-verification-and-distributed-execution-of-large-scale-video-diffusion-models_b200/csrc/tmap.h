@@ -36,7 +36,14 @@ struct GemmArgs {
   int64_t tap_row_stride = 0;
   int64_t rows_per_batch = 0;  // 0 -> M
   int flags = 0;
+  // GroupNorm statistics of the OUTPUT, emitted by the epilogue (see gn_stats_ok): per 32-row block and group the fp32
+  // {sum, sum of squares} of the values just produced, [M/32][gn_groups][2]. Ignored (left untouched) when the shape
+  // does not qualify — ask gn_stats_ok first.
+  float* gn_stats = nullptr;
+  int gn_groups = 32;
 };
+// true when gemm_tiled / conv3x3_im2col called with these sizes will fill GemmArgs::gn_stats / ConvArgs::gn_stats
+bool gn_stats_ok(int64_t M, int N, int64_t rows_per_batch, int groups);
 
 struct ConvArgs {
   int adt = B2V_BF16;       // element type of x / w / residual / out: B2V_BF16 or B2V_F16
@@ -52,6 +59,8 @@ struct ConvArgs {
   // (N = B*F images; the weight is zero-padded to Cout = 64 rows)
   void* ncfhw_out = nullptr;
   int ncfhw_dtype = 0, ncfhw_cout = 0, ncfhw_F = 1;
+  float* gn_stats = nullptr;  // as GemmArgs::gn_stats, M = N*P*Q rows
+  int gn_groups = 32;
 };
 
 int pick_bn(int N, bool geglu, int64_t m_units = 0, int cg = 1);

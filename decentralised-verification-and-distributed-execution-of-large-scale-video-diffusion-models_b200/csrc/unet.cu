@@ -13,6 +13,7 @@
 #include <memory>
 #include <mutex>
 #include <string>
+#include <unordered_map>
 #include <vector>
 
 #include "common.cuh"
@@ -415,18 +416,37 @@ struct Ctx {
     if (!p && status == 0) status = fail(B2V_ERR_WORKSPACE, "workspace too small");
     return p;
   }
-  void free(void* p) { arena.release(p); }
+  // GroupNorm statistics emitted by the epilogue of the GEMM / conv that produced an activation (gemm.cu GNG epilogues):
+  // activation pointer -> [rows/32][groups][2] fp32 in the arena. Consumed (and released) by the first GroupNorm over that
+  // activation, or released with the activation. B2V_GN_FUSE=0 turns the fusion off (A/B).
+  std::unordered_map<const void*, float*> gstats;
+  float* want_stats(const void* out, int64_t M, int N, int64_t rows_per_batch) {
+    static int on = -1;
+    if (on < 0) { const char* e = getenv("B2V_GN_FUSE"); on = (e && atoi(e) == 0) ? 0 : 1; }
+    if (!on || !gn_stats_ok(M, N, rows_per_batch, u->cfg.norm_num_groups)) return nullptr;
+    float* st = (float*)bytes(sizeof(float) * 2 * (size_t)(M / 32) * u->cfg.norm_num_groups);
+    if (st) gstats[out] = st;
+    return st;
+  }
+  void drop_stats(const void* p) {
+    auto it = gstats.find(p);
+    if (it != gstats.end()) { arena.release(it->second); gstats.erase(it); }
+  }
+  void free(void* p) { drop_stats(p); arena.release(p); }
   void run(int st) { if (status == 0 && st != 0) status = st; }
   bool live() const { return status == 0 && !arena.dry(); }
 };
 
 struct Act { bf16* p; int64_t rows; int C; int H, W; };  // rows = B*F*H*W
 
+// feeds_gn: the output goes (first) into a GroupNorm without concat — ask the epilogue for its statistics
 void gemm(Ctx& c, const bf16* a, int64_t M, const Lin& l, const bf16* residual, bf16* out, int flags = 0,
-          int64_t lda = 0) {
+          int64_t lda = 0, bool feeds_gn = false) {
   c.flops += 2.0 * (double)M * l.N * l.K;
+  float* st = feeds_gn ? c.want_stats(out, M, l.N, M) : nullptr;
   if (!c.live()) return;
   GemmArgs g;
+  g.gn_stats = st; g.gn_groups = c.u->cfg.norm_num_groups;
   g.adt = c.u->adt;
   g.a = a; g.lda = lda; g.w = l.w; g.bias = l.b; g.residual = residual; g.out = out;
   g.M = M; g.N = l.N; g.Kc = l.K; g.taps = 1; g.rows_per_batch = M; g.flags = flags;
@@ -436,16 +456,24 @@ void gemm(Ctx& c, const bf16* a, int64_t M, const Lin& l, const bf16* residual, 
 void gn(Ctx& c, const bf16* x1, int C1, const bf16* x2, int C2, const Norm& n, bf16* y, int64_t items, int64_t rows_per,
         float eps, int silu) {
   void* stats = c.bytes(group_norm_scratch_bytes(items, rows_per, c.u->cfg.norm_num_groups));
-  if (c.live()) c.run(group_norm(c.u->adt, x1, C1, x2, C2, n.g, n.b, y, items, rows_per, c.u->cfg.norm_num_groups, eps, silu, stats, c.s));
+  const float* pre = nullptr;
+  if (!x2 && rows_per % 32 == 0) {
+    auto it = c.gstats.find(x1);
+    if (it != c.gstats.end()) pre = it->second;
+  }
+  if (c.live()) c.run(group_norm(c.u->adt, x1, C1, x2, C2, n.g, n.b, y, items, rows_per, c.u->cfg.norm_num_groups, eps, silu, stats, c.s, pre));
   c.free(stats);
+  c.drop_stats(x1);  // one GroupNorm per activation reads them (the skip copies are normalised as part of a concat)
 }
 
 void conv(Ctx& c, const bf16* x, int N, int H, int W, const Conv& w, int stride, const float* rowbias,
-          int64_t rows_per_group, const bf16* residual, bf16* out, int real_cin = 0) {
+          int64_t rows_per_group, const bf16* residual, bf16* out, int real_cin = 0, bool feeds_gn = false) {
   const int P = (H - 1) / stride + 1, Q = (W - 1) / stride + 1;
   c.flops += 2.0 * (double)N * P * Q * w.Cout * 9.0 * (real_cin ? real_cin : w.Cin);  // algorithmic: padding not counted
+  float* st = feeds_gn ? c.want_stats(out, (int64_t)N * P * Q, w.Cout, 0) : nullptr;
   if (!c.live()) return;
   ConvArgs a;
+  a.gn_stats = st; a.gn_groups = c.u->cfg.norm_num_groups;
   a.adt = c.u->adt;
   a.x = x; a.w = w.w; a.bias = w.b; a.rowbias = rowbias; a.rows_per_group = rows_per_group; a.residual = residual;
   a.out = out; a.N = N; a.H = H; a.W = W; a.Cin = w.Cin; a.Cout = w.Cout; a.stride = stride;
@@ -460,7 +488,7 @@ Act resnet(Ctx& c, const ResnetW& r, const Act& xa, const bf16* xb, int Cb) {
   bf16* h1 = c.act(M, Cin);
   gn(c, xa.p, xa.C, xb, Cb, r.n1, h1, N, (int64_t)H * W, c.u->cfg.norm_eps, 1);
   bf16* h2 = c.act(M, r.Cout);
-  conv(c, h1, N, H, W, r.c1, 1, r.rowbias, (int64_t)c.F * H * W, nullptr, h2);
+  conv(c, h1, N, H, W, r.c1, 1, r.rowbias, (int64_t)c.F * H * W, nullptr, h2, 0, true);
   c.free(h1);
   bf16* h3 = c.act(M, r.Cout);
   gn(c, h2, r.Cout, nullptr, 0, r.n2, h3, N, (int64_t)H * W, c.u->cfg.norm_eps, 1);
@@ -481,7 +509,7 @@ Act resnet(Ctx& c, const ResnetW& r, const Act& xa, const bf16* xb, int Cb) {
     res = sc;
   }
   bf16* out = c.act(M, r.Cout);
-  conv(c, h3, N, H, W, r.c2, 1, nullptr, 0, res, out);
+  conv(c, h3, N, H, W, r.c2, 1, nullptr, 0, res, out, 0, true);
   c.free(h3);
   if (sc) c.free(sc);
   return Act{out, M, r.Cout, H, W};
@@ -497,8 +525,10 @@ Act temp_conv(Ctx& c, const TempConvW& t, const Act& x) {
     gn(c, cur, t.C, nullptr, 0, t.n[i], n, c.B, (int64_t)c.F * HW, 1e-5f, 1);
     bf16* o = c.act(M, t.C);
     c.flops += 2.0 * (double)M * t.C * 3.0 * t.C;
+    float* st = c.want_stats(o, M, t.C, (int64_t)c.F * HW);
     if (c.live()) {
       GemmArgs g;
+      g.gn_stats = st; g.gn_groups = c.u->cfg.norm_num_groups;
       g.adt = c.u->adt;
       g.a = n; g.w = t.c[i].w; g.bias = t.c[i].b; g.residual = (i == 3) ? x.p : nullptr; g.out = o;
       g.M = M; g.N = t.C; g.Kc = t.C; g.taps = 3; g.tap_row_stride = HW; g.rows_per_batch = (int64_t)c.F * HW;
@@ -579,7 +609,7 @@ Act spatial(Ctx& c, const SpatialW& a, const Act& x) {
   }
   feed_forward(c, b, h, M);
   bf16* out = c.act(M, C);
-  gemm(c, h, M, a.proj_out, x.p, out);
+  gemm(c, h, M, a.proj_out, x.p, out, 0, 0, true);
   c.free(h);
   return Act{out, M, C, x.H, x.W};
 }
@@ -613,7 +643,7 @@ Act temporal(Ctx& c, const TemporalW& a, const Act& x) {
   }
   feed_forward(c, b, h, M);
   bf16* out = c.act(M, C);
-  gemm(c, h, M, a.proj_out, x.p, out);
+  gemm(c, h, M, a.proj_out, x.p, out, 0, 0, true);
   c.free(h);
   return Act{out, M, C, x.H, x.W};
 }
@@ -652,7 +682,7 @@ int forward_impl(b2v_unet3d* u, Ctx& c, int io_dtype, int H, int W) {
   {
     bf16* xin = c.act((int64_t)N * H * W, u->conv_in.Cin);
     if (c.live()) c.run(ncfhw_to_rows(sample, io_dtype, xin, u->adt, B, cfg.in_channels, F, (int64_t)H * W, u->conv_in.Cin, c.s));
-    conv(c, xin, N, H, W, u->conv_in, 1, nullptr, 0, nullptr, x.p, cfg.in_channels);
+    conv(c, xin, N, H, W, u->conv_in, 1, nullptr, 0, nullptr, x.p, cfg.in_channels, true);
     c.free(xin);
   }
   {
@@ -683,7 +713,7 @@ int forward_impl(b2v_unet3d* u, Ctx& c, int io_dtype, int H, int W) {
     if (L.has_sampler) {
       const int P = (x.H - 1) / 2 + 1, Q = (x.W - 1) / 2 + 1;
       Act y{c.act((int64_t)N * P * Q, x.C), (int64_t)N * P * Q, x.C, P, Q};
-      conv(c, x.p, N, x.H, x.W, L.sampler, 2, nullptr, 0, nullptr, y.p);
+      conv(c, x.p, N, x.H, x.W, L.sampler, 2, nullptr, 0, nullptr, y.p, 0, true);
       x = y;
       skips.push_back(x);
     }

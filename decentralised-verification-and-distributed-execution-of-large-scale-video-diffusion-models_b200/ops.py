@@ -252,6 +252,50 @@ def gemm(a, w, bias=None, rowbias=None, rows_per_group=0, residual=None, taps=1,
     return out
 
 
+def gn_stats_ok(M, N, rows_per_batch=0, groups=32):
+    return bool(_lib.load().b2v_gn_stats_ok(int(M), int(N), int(rows_per_batch), int(groups)))
+
+
+def gemm_gnstats(a, w, bias=None, rowbias=None, rows_per_group=0, residual=None, taps=1, tap_row_stride=0,
+                 rows_per_batch=0, groups=32):
+    """gemm() whose epilogue also emits the GroupNorm statistics of its output: (out, stats[M/32, groups, 2] fp32)."""
+    lib = _lib.load()
+    _cuda(a); _cuda(w)
+    M, Kc = a.shape
+    N = w.shape[0]
+    out = torch.empty((M, N), dtype=a.dtype, device=a.device)
+    stats = torch.zeros((M // 32, groups, 2), dtype=torch.float32, device=a.device)
+    check(lib.b2v_op_gemm_gnstats(ptr(a), ptr(w), ptr(bias), ptr(rowbias), int(rows_per_group), ptr(residual), ptr(out), M,
+                                  N, Kc, taps, int(tap_row_stride), int(rows_per_batch), act_tag(a), ptr(stats), groups,
+                                  stream()))
+    return out, stats
+
+
+def conv3x3_gnstats(x, w, bias=None, rowbias=None, rows_per_group=0, residual=None, groups=32):
+    lib = _lib.load()
+    _cuda(x); _cuda(w)
+    N, H, W, Cin = x.shape
+    Cout = w.shape[0]
+    out = torch.empty((N, H, W, Cout), dtype=x.dtype, device=x.device)
+    stats = torch.zeros((N * H * W // 32, groups, 2), dtype=torch.float32, device=x.device)
+    check(lib.b2v_op_conv3x3_gnstats(ptr(x), ptr(w), ptr(bias), ptr(rowbias), int(rows_per_group), ptr(residual), ptr(out),
+                                     N, H, W, Cin, Cout, act_tag(x), ptr(stats), groups, stream()))
+    return out, stats
+
+
+def group_norm_pre(x, gamma, beta, n_items, groups, eps, silu, pre):
+    """group_norm() fed with statistics emitted by the producing GEMM (gemm_gnstats / conv3x3_gnstats)."""
+    lib = _lib.load()
+    _cuda(x)
+    rows, C = x.shape
+    y = torch.empty((rows, C), dtype=x.dtype, device=x.device)
+    scratch = torch.empty(lib.b2v_op_group_norm_scratch_bytes(n_items, rows // n_items, groups) + 256, dtype=torch.uint8,
+                          device=x.device)
+    check(lib.b2v_op_group_norm_pre(ptr(x), C, ptr(gamma), ptr(beta), ptr(y), n_items, rows // n_items, groups, float(eps),
+                                    int(silu), ptr(scratch), ptr(pre), act_tag(x), stream()))
+    return y
+
+
 def conv3x3(x, w, bias=None, rowbias=None, rows_per_group=0, residual=None, stride=1, mode=0):
     """x: [N,H,W,Cin] bf16; w: [Cout,3,3,Cin] bf16 -> [N,P,Q,Cout]."""
     lib = _lib.load()

@@ -65,6 +65,11 @@ def add_common_args(p, num_frames=32, out_csv="benchmarks.csv", chunking=True):
                    help="per-step halo exchange (not in the reference): after every DDIM step adjacent windows swap "
                         "their overlapping frames over NVLink and adopt the same crossfade, so windows evolve as one "
                         "video; needs a plan where at most two windows cover a frame")
+    p.add_argument("--pre_steps", type=int, default=0,
+                   help="legacy coordinator's full-latent pre-denoise (legacy/Latent Chunking/precond_overlap/"
+                        "run_worker.py:161-176, its default there is 3; 0 = the strategies' behaviour): the whole video "
+                        "goes through the first N timesteps on every rank (replicated, bit-identical), then the windows "
+                        "are cut from that latent and run the complete schedule, as the legacy workers do")
     p.add_argument("--decode", dest="decode", action="store_true", default=None,
                    help="decode the blended latents to frames on rank 0 (b2v.vae) and write the mp4 + boundary metrics "
                         "like the reference (chunk_only.py:152-208). Default: on when --model_id is a checkpoint folder "
@@ -127,17 +132,19 @@ class CudaDenoiser:
         self.unet_forwards = 0
         self.launches0 = ops.launch_count()
 
-    def __call__(self, lat):
+    def __call__(self, lat, first=0, last=None, use_ctx=True):
+        """``first`` / ``last`` restrict the loop to ``timesteps[first:last]`` (the full-latent pre-denoise)."""
         sched, unet = self.pipe.scheduler, self.pipe.unet
         n_dup = 2 if self.gs is not None else 1
-        x = ops.make_unet_input(lat, n_dup, ctx=self.ctx, ctx_w=self.ctx_w)
+        ctx, ctx_w = (self.ctx, self.ctx_w) if use_ctx else (None, 0.0)
+        x = ops.make_unet_input(lat, n_dup, ctx=ctx, ctx_w=ctx_w)
         eps2 = torch.empty_like(x)
-        for i, t in enumerate(sched.host_timesteps()):
+        for i, t in list(enumerate(sched.host_timesteps()))[first:last]:
             unet.forward_into(x, t, self.emb, eps2)
             self.unet_forwards += 1
             if self.on_step is not None:
                 self.on_step(i, t, lat, eps2)
-            lat, x = sched.fused_cfg_step(lat, eps2, t, self.gs, ctx=self.ctx, ctx_w=self.ctx_w, n_dup=n_dup, xnext=x)
+            lat, x = sched.fused_cfg_step(lat, eps2, t, self.gs, ctx=ctx, ctx_w=ctx_w, n_dup=n_dup, xnext=x)
         return lat
 
 
@@ -292,7 +299,20 @@ class WindowedDiffuser:
         return cuda_blend(windows, T, ov)
 
     # ---- the run ------------------------------------------------------------------------------------------
+    def pre_denoise(self, base):
+        """--pre_steps N (N4, second half): the full latent through the first N timesteps before it is cut into windows.
+        Every rank does the same work on the same values (same seed, same kernels: bit-identical, no broadcast)."""
+        n = int(getattr(self.cfg, "pre_steps", 0) or 0)
+        if n <= 0 or self._denoise_fn is not None:
+            return base
+        if getattr(self, "_cuda_denoiser", None) is None:
+            self._cuda_denoiser = CudaDenoiser(self.pipe, self.uncond_emb, self.cond_emb, self.guidance_scale,
+                                               ctx=self.ctx, context_weight=self.context_weight if self.use_ctx else 0.0)
+        with torch.no_grad():
+            return self._cuda_denoiser(base.clone(), 0, n, use_ctx=False)
+
     def denoise_my_windows(self, plan, base):
+        base = self.pre_denoise(base)
         if getattr(self.cfg, "halo_sync", False) and self._denoise_fn is None:
             return self.denoise_my_windows_lockstep(plan, base)
         out = []

@@ -229,6 +229,25 @@ int b2v_op_group_norm(const void* x_dev, int C1, const void* x2_dev, int C2, con
 int b2v_op_layer_norm(const void* x_dev, const float* gamma_dev, const float* beta_dev, void* y_dev,
                       int64_t rows, int C, float eps, int act_dtype, void* stream);
 
+/* GroupNorm statistics out of the PRODUCING GEMM / conv (ResnetBlock2D conv1 -> norm2, TemporalConvLayer conv_i ->
+ * norm_{i+1}, proj_out -> the next block's norm: the statistics pass over the activation disappears).
+ * b2v_op_gemm_gnstats / b2v_op_conv3x3_gnstats are b2v_op_gemm / b2v_op_conv3x3 (stride 1, TMA im2col) whose epilogue
+ * also writes gn_stats_dev[M/32][gn_groups][2] = fp32 {sum, sum of squares} of the output per 32-row block and group
+ * (fixed-order, bit-reproducible). Shapes qualify when b2v_gn_stats_ok() is 1 (N a multiple of 160 with 10 / 20 / 40
+ * channels per group, whole 256-row units); otherwise the calls fail with B2V_ERR_ARG.
+ * b2v_op_group_norm_pre is b2v_op_group_norm (no concat) fed with such statistics instead of its own first pass. */
+int b2v_gn_stats_ok(int64_t M, int N, int64_t rows_per_batch, int groups);
+int b2v_op_gemm_gnstats(const void* a_dev, const void* w_dev, const float* bias_dev, const float* rowbias_dev,
+                        int64_t rows_per_group, const void* residual_dev, void* out_dev, int64_t M, int N, int Kc,
+                        int taps, int64_t tap_row_stride, int64_t rows_per_batch, int act_dtype, float* gn_stats_dev,
+                        int gn_groups, void* stream);
+int b2v_op_conv3x3_gnstats(const void* x_dev, const void* w_dev, const float* bias_dev, const float* rowbias_dev,
+                           int64_t rows_per_group, const void* residual_dev, void* out_dev, int N, int H, int W,
+                           int Cin, int Cout, int act_dtype, float* gn_stats_dev, int gn_groups, void* stream);
+int b2v_op_group_norm_pre(const void* x_dev, int C, const float* gamma_dev, const float* beta_dev, void* y_dev,
+                          int64_t n_items, int64_t rows_per_item, int groups, float eps, int silu, void* scratch_dev,
+                          const float* pre_dev, int act_dtype, void* stream);
+
 /* softmax(Q K^T * scale) V, head_dim 64. q: [nb, Sq, ldq] rows, head h at column h*64;
  * k/v: [nb / kv_group, Skv, ldk]; out [nb, Sq, ldo]. (tcgen05 flash attention.) */
 int b2v_op_attention(const void* q_dev, int64_t ldq, const void* k_dev, const void* v_dev, int64_t ldkv,

@@ -98,10 +98,12 @@ def context_mean(base):
     return base.mean(dim=2, keepdim=True)
 
 
-def denoise(unet, sched, lat, uncond_emb, cond_emb, guidance_scale, ctx=None, context_weight=0.35, record=None):
-    """One chunk through every timestep with classifier-free guidance. `record(step, t, lat_in, eps, lat_out)`."""
+def denoise(unet, sched, lat, uncond_emb, cond_emb, guidance_scale, ctx=None, context_weight=0.35, record=None,
+            first=0, last=None):
+    """One chunk through every timestep (or timesteps[first:last]) with classifier-free guidance.
+    `record(step, t, lat_in, eps, lat_out)`."""
     emb = torch.cat([uncond_emb, cond_emb], 0)
-    for i, t in enumerate(sched.timesteps):
+    for i, t in list(enumerate(sched.timesteps))[first:last]:
         x = sched.scale_model_input(torch.cat([lat] * 2), t)
         if ctx is not None:
             x = x + context_weight * ctx.repeat(1, 1, lat.shape[2], 1, 1)
@@ -130,10 +132,16 @@ def denoise_miner(unet, sched, z, ehs):
 
 
 def run_strategy(unet, sched, base, uncond_emb, cond_emb, world, guidance_scale=7.5, chunk_size=0, overlap=4,
-                 coherent=False, context_weight=0.35, record=None):
+                 coherent=False, context_weight=0.35, record=None, pre_steps=0):
     """All ranks of chunk_only.py (coherent=False) or fsdp_chunked_coherent.py --mode hybrid_ctx (coherent=True),
-    sequentially. Returns dict(lat, chunks, ranges, cs, ov)."""
+    sequentially. Returns dict(lat, chunks, ranges, cs, ov).
+    pre_steps > 0: the legacy coordinator's full-latent pre-denoise (legacy/Latent Chunking/precond_overlap/
+    run_worker.py:161-176): the WHOLE video goes through the first pre_steps timesteps (guidance as given, no context),
+    then the windows are cut from that latent and — as the legacy workers do, run_worker.py:184 'pre_steps': 0, :44 —
+    run the complete schedule again from its first timestep."""
     T = base.shape[2]
+    if pre_steps > 0:
+        base = denoise(unet, sched, base.clone(), uncond_emb, cond_emb, guidance_scale, None, 0.0, None, 0, pre_steps)
     cs, ov, ranges = (plan_coherent if coherent else plan_chunk_only)(T, world, chunk_size, overlap)
     ctx = context_mean(base) if coherent else None
     gathered = []

@@ -232,3 +232,69 @@ def test_temporal_attention(cuda, act, B, F, HW, heads):
     ref = torch.softmax(q @ k.transpose(-1, -2) * 0.125, -1) @ v  # [B][HW][heads][F][64]
     ref = ref.permute(0, 3, 1, 2, 4).reshape(B * F * HW, D)
     assert rel_l2(out, ref) < tol(act, 4e-3), rel_l2(out, ref)
+
+
+# ---- GroupNorm statistics out of the producing GEMM's epilogue -------------------------------------
+def _ref_block_stats(out_f32, groups):
+    M, N = out_f32.shape
+    v = out_f32.reshape(M // 32, 32, groups, N // groups).double()
+    return torch.stack([v.sum(dim=(1, 3)), (v * v).sum(dim=(1, 3))], dim=-1)
+
+
+@pytest.mark.parametrize("adt", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("M,N,K,taps,res,items", [(1024, 320, 320, 1, False, 4), (2048, 640, 320, 1, True, 2),
+                                                   (1536, 320, 64, 3, True, 2), (36864, 320, 128, 1, False, 2),
+                                                   (2304, 1280, 128, 1, False, 1)])
+def test_gemm_emits_group_norm_stats(cuda, adt, M, N, K, taps, res, items):
+    """gemm_gnstats: same output bits as gemm(); statistics = {sum, sumsq} per 32-row block and group of the fp32 results
+    (before rounding); group_norm_pre on them == the two-pass group_norm within rounding of the statistics, and both
+    within the op gate of torch fp32. (36864 rows / 2 items = 576 blocks per item: the pre-fold kernel path.)"""
+    from b2v import ops
+    g = torch.Generator(device=cuda).manual_seed(M + N + taps)
+    rpb = M // items if taps == 3 else 0
+    if not ops.gn_stats_ok(M, N, rpb, 32):
+        pytest.skip("the cost model does not pick the 160-wide tile for this shape")
+    a = torch.randn(M, K, device=cuda, generator=g).to(adt)
+    w = (torch.randn(N, taps * K, device=cuda, generator=g) / math.sqrt(taps * K)).to(adt)
+    bias = torch.randn(N, device=cuda, generator=g)
+    r = torch.randn(M, N, device=cuda, generator=g).to(adt) if res else None
+    kw = dict(bias=bias, residual=r, taps=taps, tap_row_stride=(M // items) // 4 if taps == 3 else 0, rows_per_batch=rpb)
+    plain = ops.gemm(a, w, **kw)
+    out, stats = ops.gemm_gnstats(a, w, groups=32, **kw)
+    assert torch.equal(out, plain)
+    want = _ref_block_stats(out.float(), 32)          # from the ROUNDED output: differs by the rounding noise only
+    err = (stats.double() - want).abs().max() / want.abs().max()
+    print("gn stats", adt, (M, N, K, taps, res), "max rel err vs stats of the rounded output %.3e" % float(err))
+    assert float(err) < (2e-3 if adt == torch.bfloat16 else 3e-4)
+    gam = 1 + 0.1 * torch.randn(N, device=cuda, generator=g)
+    bet = 0.1 * torch.randn(N, device=cuda, generator=g)
+    for silu in (0, 1):
+        two_pass = ops.group_norm(out, gam, bet, items, 32, 1e-5, silu)
+        fused = ops.group_norm_pre(out, gam, bet, items, 32, 1e-5, silu, stats)
+        ref = torch.nn.functional.group_norm(out.float().reshape(items, M // items, N).permute(0, 2, 1), 32, gam, bet, 1e-5)
+        ref = (torch.nn.functional.silu(ref) if silu else ref).permute(0, 2, 1).reshape(M, N)
+        gate = 1e-2 if adt == torch.bfloat16 else 2.5e-3
+        assert rel_l2(fused, ref) < gate and rel_l2(two_pass, ref) < gate
+        assert rel_l2(fused, two_pass) < gate / 2
+        assert torch.equal(fused, ops.group_norm_pre(out, gam, bet, items, 32, 1e-5, silu, stats))   # bit-reproducible
+
+
+@pytest.mark.parametrize("adt", [torch.bfloat16, torch.float16])
+def test_conv3x3_emits_group_norm_stats(cuda, adt):
+    from b2v import ops
+    g = torch.Generator(device=cuda).manual_seed(9)
+    Nimg, H, W, Cin, Cout = 2, 16, 32, 64, 320
+    assert ops.gn_stats_ok(Nimg * H * W, Cout, 0, 32)
+    x = torch.randn(Nimg, H, W, Cin, device=cuda, generator=g).to(adt)
+    w = (torch.randn(Cout, 3, 3, Cin, device=cuda, generator=g) / 24.0).to(adt)
+    bias = torch.randn(Cout, device=cuda, generator=g)
+    out, stats = ops.conv3x3_gnstats(x, w, bias=bias)
+    assert torch.equal(out, ops.conv3x3(x, w, bias=bias))
+    want = _ref_block_stats(out.float().reshape(-1, Cout), 32)
+    err = float((stats.double() - want).abs().max() / want.abs().max())
+    assert err < (2e-3 if adt == torch.bfloat16 else 3e-4), err
+    gam, bet = torch.ones(Cout, device=cuda), torch.zeros(Cout, device=cuda)
+    rows = out.reshape(-1, Cout)
+    a = ops.group_norm_pre(rows, gam, bet, Nimg, 32, 1e-5, 1, stats)
+    b = ops.group_norm(rows, gam, bet, Nimg, 32, 1e-5, 1)
+    assert rel_l2(a, b) < 5e-3

@@ -197,3 +197,36 @@ def test_windowed_diffuser_world1(cuda, tmp_path):
     assert res["world_size"] == 1 and res["num_frames"] == 8 and res["chunk_size"] == 8 and res["overlap"] == 2
     assert d.latents.shape == (1, 4, 8, 16, 16) and bool(torch.isfinite(d.latents).all())
     assert res["steps_per_s"] > 0
+
+
+def test_pre_steps_vs_oracle(cuda, tmp_path):
+    """--pre_steps N (second half; legacy/Latent Chunking/precond_overlap/run_worker.py:161-176): the full
+    latent through the first N timesteps (CFG, no context), then the windows — cut from THAT latent — through the
+    complete schedule, as the legacy workers do. Engine (fp16 UNet arithmetic) vs the fp32 oracle."""
+    from oracle import strategy_ref as S
+    from oracle import unet3d_ref as R
+    from oracle.ddim_ref import pipeline_scheduler
+    from b2v.pipeline import VideoPipeline
+    from b2v.scheduler import DDIMScheduler
+    from b2v.strategies.chunk_only import ChunkedVideoDiffuser
+    from b2v.strategies.common import base_noise
+    from b2v.unet import UNet3DConditionModel
+    ref = R.random_init_(R.UNet3DConditionModel(R.TINY), seed=1234, round_bf16=True).eval()
+    net = UNet3DConditionModel(R.TINY.to_dict(), device=cuda, dtype=torch.float16).load_state_dict(ref.state_dict())
+    pipe = VideoPipeline(net, DDIMScheduler.from_pipeline_config(), text_dim=128, dtype=torch.float32)
+    outs = {}
+    for n in (0, 2):
+        cfg = _cfg(out_csv=str(tmp_path / "p.csv"), pre_steps=n, guidance_scale=1.0)
+        d = ChunkedVideoDiffuser(cfg, pipe=pipe)
+        d()
+        outs[n] = d.latents.cpu()
+        base = base_noise(4, 8, 16, 16, torch.float32, torch.device("cpu"))
+        sch = pipeline_scheduler()
+        sch.set_timesteps(4)
+        want = S.run_strategy(ref, sch, base, d.uncond_emb.float().cpu(), d.cond_emb.float().cpu(), 1, 1.0, 0, 4,
+                              pre_steps=n)["lat"]
+        live = want.abs().amax(dim=(0, 1, 3, 4)) > 0   # reference quirk Q1: ramp-zero edge frames are exactly 0
+        rel = float((outs[n][:, :, live] - want[:, :, live]).norm() / want[:, :, live].norm())
+        print("pre_steps=%d rel-l2 vs oracle %.3e" % (n, rel))
+        assert rel <= 1e-2, (n, rel)
+    assert float((outs[0] - outs[2]).abs().max()) > 1e-2   # the pre-denoise really changes the result
