@@ -62,6 +62,9 @@ _SIGNATURES = {
     "b2v_op_conv3x3": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _i, _i, _i, _i, _i, _i, _i, _vp, _i, _vp]),
     "b2v_op_group_norm": (_i, [_vp, _i, _vp, _i, _vp, _vp, _vp, _i64, _i64, _i, _f, _i, _vp, _i, _vp]),
     "b2v_op_group_norm_scratch_bytes": (_sz, [_i64, _i64, _i]),
+    "b2v_row_stats_slots": (_i, [_i64, _i, _i64]),
+    "b2v_op_gemm_rowstats": (_i, [_vp, _vp, _vp, _vp, _vp, _i64, _i, _i, _i, _vp, _vp]),
+    "b2v_op_gemm_lnin": (_i, [_vp, _vp, _vp, _vp, _vp, _i, _f, _vp, _i64, _i, _i, _i, _i, _vp]),
     "b2v_gn_stats_ok": (_i, [_i64, _i, _i64, _i]),
     "b2v_op_gemm_gnstats": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _i64, _i, _i, _i, _i64, _i64, _i, _vp, _i, _vp]),
     "b2v_op_conv3x3_gnstats": (_i, [_vp, _vp, _vp, _vp, _i64, _vp, _vp, _i, _i, _i, _i, _i, _i, _vp, _i, _vp]),

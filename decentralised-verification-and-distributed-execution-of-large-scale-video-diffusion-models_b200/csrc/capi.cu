@@ -19,6 +19,34 @@ extern "C" int b2v_op_gemm(const void* a_dev, const void* w_dev, const float* bi
   return gemm_tiled(g, (cudaStream_t)stream);
 }
 
+extern "C" int b2v_row_stats_slots(int64_t M, int N, int64_t rows_per_batch) { return row_stats_slots(M, N, rows_per_batch); }
+
+extern "C" int b2v_op_gemm_rowstats(const void* a_dev, const void* w_dev, const float* bias_dev, const void* residual_dev,
+                                    void* out_dev, int64_t M, int N, int Kc, int act_dtype, float* row_stats_dev,
+                                    void* stream) {
+  B2V_CHECK(a_dev && w_dev && out_dev && row_stats_dev, "null argument");
+  B2V_TRY(b2v_device_check());
+  B2V_CHECK(row_stats_slots(M, N, 0) > 0, "this GEMM shape has no row-statistics epilogue");
+  GemmArgs g;
+  g.adt = act_dtype;
+  g.a = a_dev; g.w = w_dev; g.bias = bias_dev; g.residual = residual_dev; g.out = out_dev; g.M = M; g.N = N; g.Kc = Kc;
+  g.row_stats = row_stats_dev;
+  return gemm_tiled(g, (cudaStream_t)stream);
+}
+
+extern "C" int b2v_op_gemm_lnin(const void* a_raw_dev, const void* w_gamma_dev, const float* bias_folded_dev,
+                                const float* csum_dev, const float* ln_stats_dev, int ln_slots, float eps, void* out_dev,
+                                int64_t M, int N, int Kc, int flags, int act_dtype, void* stream) {
+  B2V_CHECK(a_raw_dev && w_gamma_dev && bias_folded_dev && csum_dev && ln_stats_dev && out_dev, "null argument");
+  B2V_TRY(b2v_device_check());
+  GemmArgs g;
+  g.adt = act_dtype;
+  g.a = a_raw_dev; g.w = w_gamma_dev; g.bias = bias_folded_dev; g.out = out_dev; g.M = M; g.N = N; g.Kc = Kc;
+  g.flags = flags;
+  g.ln_stats = ln_stats_dev; g.ln_csum = csum_dev; g.ln_slots = ln_slots; g.ln_eps = eps;
+  return gemm_tiled(g, (cudaStream_t)stream);
+}
+
 extern "C" int b2v_gn_stats_ok(int64_t M, int N, int64_t rows_per_batch, int groups) {
   return gn_stats_ok(M, N, rows_per_batch, groups) ? 1 : 0;
 }

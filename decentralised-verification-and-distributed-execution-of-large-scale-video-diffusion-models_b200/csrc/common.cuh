@@ -139,6 +139,11 @@ __device__ __forceinline__ uint16_t to_act(float x) {
   if constexpr (F16) return __half_as_ushort(__float2half_rn(x));
   else return __bfloat16_as_ushort(__float2bfloat16_rn(x));
 }
+template <bool F16>
+__device__ __forceinline__ float act_to_float(uint16_t v) {
+  if constexpr (F16) return __half2float(__ushort_as_half(v));
+  else return __bfloat162float(__ushort_as_bfloat16(v));
+}
 static inline bool act_ok(int adt) { return adt == B2V_BF16 || adt == B2V_F16; }
 // run `...` with a constexpr bool F16 selected by the activation dtype tag
 #define B2V_DISPATCH_ACT(adt, F16, ...)                                                    \

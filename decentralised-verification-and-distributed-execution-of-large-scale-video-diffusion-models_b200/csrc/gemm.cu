@@ -89,7 +89,17 @@ struct GemmParams {
   // GroupNorm statistics of the output (GNG > 0 instantiations): [M/32][gn_groups]{sum, sumsq}
   float* gn_stats;
   int gn_groups;
+  // LayerNorm fused across two GEMMs (FUSE_RSTAT / FUSE_LNIN instantiations):
+  //  producer: row_stats[M][2 * num_n_tiles]{sum, sumsq} of each output row over the columns of one epilogue warp
+  //  consumer: A is the RAW activation; ln_stats[M][ln_slots] are its row partials, ln_csum[N] = sum_k W'[n][k] with
+  //            W' = W diag(gamma) (what `w` holds), bias = b + W beta:  out = rstd (acc - mean csum) + bias
+  float* row_stats;
+  const float* ln_stats;
+  const float* ln_csum;
+  int ln_slots;
+  float ln_eps;
 };
+constexpr int FUSE_RSTAT = 16, FUSE_LNIN = 32;  // FUSE template argument: 0 | GNG (2, 4, 8) | FUSE_RSTAT | FUSE_LNIN
 
 constexpr int EPI_PLAIN = 0, EPI_GEGLU_T = 1, EPI_NCFHW = 2;
 
@@ -141,11 +151,13 @@ __device__ __forceinline__ uint64_t gelu_fast2(uint64_t x2) {
 // accumulates {sum, sum of squares} of its row per group while the values pass through its registers, the warp folds the
 // 32 rows with a fixed-order shuffle tree (deterministic) and writes 2 GNG floats per 32-row block: the consumer's
 // GroupNorm needs no statistics pass over the activation (norm.cu: group_norm with `pre`).
-template <int BN, int MODE, bool GEGLU, bool RES, int CG, bool F16, int GNG>
+template <int BN, int MODE, bool GEGLU, bool RES, int CG, bool F16, int FUSE>
 __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtensorMap* tmO, const CUtensorMap* tmR,
                                               uint8_t* stage0, uint32_t rbar0, uint32_t tmem_base, uint32_t tfull0,
                                               uint32_t tempty0, int warp, int lane, int num_tiles) {
   using Cfg = TileCfg<BN, GEGLU, RES, CG>;
+  constexpr int GNG = FUSE & 15;
+  constexpr bool RSTAT = FUSE == FUSE_RSTAT, LNIN = FUSE == FUSE_LNIN;
   constexpr int OUT_COLS = Cfg::OUT_COLS;
   constexpr int NCH = OUT_COLS / 32;  // 16-column chunks per group
   // work units: tile `u` of this CTA (CG = 1) or of this CTA pair (CG = 2: rank r owns rows [128 r, +128) of the unit)
@@ -191,6 +203,24 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
       rb = p.rowbias + (gclamped / p.rows_per_group) * (int64_t)p.N + wcol0;
     }
     const uint32_t tacc = tmem_base + acc * Cfg::ACC_STRIDE + ((uint32_t)(quarter * 32) << 16);
+    // this lane's output row (LayerNorm fusion: its statistics in, or its partial sums out)
+    const int64_t lrow = (MODE == 0 ? (int64_t)slab * p.rows_per_batch : 0) + row0 + lane;
+    float ln_rstd = 1.f, ln_nrm = 0.f;  // LNIN: out = rstd * acc + (bias' - rstd * mean * csum)
+    if constexpr (LNIN) {
+      const float2* st = reinterpret_cast<const float2*>(p.ln_stats) + (lrow < p.M ? lrow : p.M - 1) * p.ln_slots;
+      float sm = 0.f, sq = 0.f;
+      for (int i = 0; i < p.ln_slots; ++i) {  // fixed order
+        const float2 t = __ldg(st + i);
+        sm += t.x;
+        sq += t.y;
+      }
+      const float inv_k = 1.0f / (float)p.Kc;
+      const float mean = sm * inv_k;
+      const float var = fmaxf(fmaf(-mean, mean, sq * inv_k), 0.f);
+      ln_rstd = rsqrtf(var + p.ln_eps);
+      ln_nrm = -ln_rstd * mean;
+    }
+    float rsum = 0.f, rsq = 0.f;  // RSTAT
     float gsum[GNG > 0 ? GNG : 1], gsq[GNG > 0 ? GNG : 1];
 #pragma unroll
     for (int i = 0; i < (GNG > 0 ? GNG : 1); ++i) gsum[i] = gsq[i] = 0.f;
@@ -212,6 +242,11 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
         for (int j = 0; j < 4; ++j) {
           const float4 b = __ldg(b4 + j);
           bv[slot][4 * j] = b.x; bv[slot][4 * j + 1] = b.y; bv[slot][4 * j + 2] = b.z; bv[slot][4 * j + 3] = b.w;
+          if constexpr (LNIN) {
+            const float4 cs = __ldg(reinterpret_cast<const float4*>(p.ln_csum + wcol0 + c) + j);
+            bv[slot][4 * j] = fmaf(ln_nrm, cs.x, b.x); bv[slot][4 * j + 1] = fmaf(ln_nrm, cs.y, b.y);
+            bv[slot][4 * j + 2] = fmaf(ln_nrm, cs.z, b.z); bv[slot][4 * j + 3] = fmaf(ln_nrm, cs.w, b.w);
+          }
         }
         if constexpr (GEGLU) {
           const float4* g4 = reinterpret_cast<const float4*>(p.bias + wcol0 + BN / 2 + c);
@@ -219,6 +254,11 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
           for (int j = 0; j < 4; ++j) {
             const float4 b = __ldg(g4 + j);
             bg[slot][4 * j] = b.x; bg[slot][4 * j + 1] = b.y; bg[slot][4 * j + 2] = b.z; bg[slot][4 * j + 3] = b.w;
+            if constexpr (LNIN) {
+              const float4 cs = __ldg(reinterpret_cast<const float4*>(p.ln_csum + wcol0 + BN / 2 + c) + j);
+              bg[slot][4 * j] = fmaf(ln_nrm, cs.x, b.x); bg[slot][4 * j + 1] = fmaf(ln_nrm, cs.y, b.y);
+              bg[slot][4 * j + 2] = fmaf(ln_nrm, cs.z, b.z); bg[slot][4 * j + 3] = fmaf(ln_nrm, cs.w, b.w);
+            }
           }
         }
       } else {
@@ -267,7 +307,18 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
         for (int j = 0; j < 16; ++j) f[j] = __uint_as_float(v[cur][j]);
       }
       if constexpr (!GEGLU) {
-        if (p.bias) {
+        if constexpr (LNIN) {  // bias' and csum always exist on this path
+          const float4* b4 = reinterpret_cast<const float4*>(p.bias + wcol0 + c);
+          const float4* c4 = reinterpret_cast<const float4*>(p.ln_csum + wcol0 + c);
+#pragma unroll
+          for (int j = 0; j < 4; ++j) {
+            const float4 b = __ldg(b4 + j), cs = __ldg(c4 + j);
+            f[4 * j] = fmaf(f[4 * j], ln_rstd, fmaf(ln_nrm, cs.x, b.x));
+            f[4 * j + 1] = fmaf(f[4 * j + 1], ln_rstd, fmaf(ln_nrm, cs.y, b.y));
+            f[4 * j + 2] = fmaf(f[4 * j + 2], ln_rstd, fmaf(ln_nrm, cs.z, b.z));
+            f[4 * j + 3] = fmaf(f[4 * j + 3], ln_rstd, fmaf(ln_nrm, cs.w, b.w));
+          }
+        } else if (p.bias) {
           const float4* b4 = reinterpret_cast<const float4*>(p.bias + wcol0 + c);
 #pragma unroll
           for (int j = 0; j < 4; ++j) {
@@ -290,8 +341,14 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
         for (int j = 0; j < 8; ++j) {
           uint64_t val2 = pack2u(v[cur][2 * j], v[cur][2 * j + 1]);
           uint64_t gate2 = pack2u(g[cur][2 * j], g[cur][2 * j + 1]);
-          val2 = add2(val2, pack2(bv[cur][2 * j], bv[cur][2 * j + 1]));
-          gate2 = add2(gate2, pack2(bg[cur][2 * j], bg[cur][2 * j + 1]));
+          if constexpr (LNIN) {
+            const uint64_t r2 = pack2(ln_rstd, ln_rstd);
+            val2 = fma2(val2, r2, pack2(bv[cur][2 * j], bv[cur][2 * j + 1]));
+            gate2 = fma2(gate2, r2, pack2(bg[cur][2 * j], bg[cur][2 * j + 1]));
+          } else {
+            val2 = add2(val2, pack2(bv[cur][2 * j], bv[cur][2 * j + 1]));
+            gate2 = add2(gate2, pack2(bg[cur][2 * j], bg[cur][2 * j + 1]));
+          }
           unpack2(mul2(val2, gelu_fast2(gate2)), f[2 * j], f[2 * j + 1]);
         }
       } else {
@@ -318,6 +375,10 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
         o.z = pack_act2<F16>(f[8 * j + 4], f[8 * j + 5]);
         o.w = pack_act2<F16>(f[8 * j + 6], f[8 * j + 7]);
         sts128(dst, o);
+      }
+      if constexpr (RSTAT) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) { rsum += f[j]; rsq = fmaf(f[j], f[j], rsq); }
       }
       if constexpr (GNG > 0) {
         constexpr int CPG = (OUT_COLS / 2) / GNG;  // channels per group
@@ -346,6 +407,11 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
       else mbar_arrive(tempty0 + 8 * acc);
     }
     if (++acc == 2) { acc = 0; acc_phase ^= 1; }
+    if constexpr (RSTAT) {
+      // this row's {sum, sumsq} over this warp's columns: slot (n_tile, column half) of the row's partial list
+      if (lrow < p.M)
+        reinterpret_cast<float2*>(p.row_stats)[lrow * (2 * p.num_n_tiles) + 2 * n_tile + group] = make_float2(rsum, rsq);
+    }
     if constexpr (GNG > 0) {
       // fold the 32 rows: reduce-scatter over the lane bits 4, 3, ... (a fixed tree), then all-reduce over the rest.
       // Afterwards lane l holds value index l >> SH (even index = sum, odd = sum of squares of group index / 2).
@@ -425,7 +491,7 @@ __device__ __forceinline__ void epilogue_loop_ncfhw(const GemmParams& p, uint32_
 }
 
 // MODE 0: A through a 3-D tiled tensor map (channels, rows, slabs); MODE 1: A through a 4-D im2col map.
-template <int BN, int MODE, int EPI, bool RES, int CG, bool F16, int GNG = 0>
+template <int BN, int MODE, int EPI, bool RES, int CG, bool F16, int FUSE = 0>
 __global__ void __launch_bounds__(NUM_THREADS, 1)
 gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUtensorMap tmB,
             const __grid_constant__ CUtensorMap tmO, const __grid_constant__ CUtensorMap tmR, const GemmParams p) {
@@ -564,7 +630,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
     if constexpr (EPI == EPI_NCFHW)
       epilogue_loop_ncfhw<Cfg::ACC_STRIDE>(p, tmem_base, tfull0, tempty0, warp, lane, num_tiles);
     else
-      epilogue_loop<BN, MODE, EPI == EPI_GEGLU_T, RES, CG, F16, GNG>(p, &tmO, &tmR,
+      epilogue_loop<BN, MODE, EPI == EPI_GEGLU_T, RES, CG, F16, FUSE>(p, &tmO, &tmR,
                                                                 sEpi + (warp - 2) * Cfg::NBUF * Cfg::PANEL_BYTES,
                                                                 rbar0 + 16 * (warp - 2), tmem_base, tfull0, tempty0,
                                                                 warp, lane, num_tiles);
@@ -580,7 +646,7 @@ gemm_kernel(const __grid_constant__ CUtensorMap tmA, const __grid_constant__ CUt
   }
 }
 
-template <int BN, int MODE, int EPI, bool RES, int CG, bool F16, int GNG = 0>
+template <int BN, int MODE, int EPI, bool RES, int CG, bool F16, int FUSE = 0>
 int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int64_t out_rows_per_slab,
                 int64_t out_slabs, cudaStream_t s) {
   using Cfg = TileCfg<BN, EPI == EPI_GEGLU_T, RES, CG>;
@@ -596,14 +662,14 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
   static std::once_flag once;
   static cudaError_t attr_err = cudaSuccess;
   std::call_once(once, [] {
-    attr_err = cudaFuncSetAttribute(gemm_kernel<BN, MODE, EPI, RES, CG, F16, GNG>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+    attr_err = cudaFuncSetAttribute(gemm_kernel<BN, MODE, EPI, RES, CG, F16, FUSE>, cudaFuncAttributeMaxDynamicSharedMemorySize,
                                     Cfg::SMEM_BYTES);
   });
   if (attr_err != cudaSuccess) return fail(B2V_ERR_CUDA, "gemm smem attr: %s", cudaGetErrorString(attr_err));
   const int units = p.num_m_units * p.num_n_tiles;
   if (CG == 1) {
     const int grid = units < sm_count() ? units : sm_count();
-    B2V_CUDA_OK(launch_pdl(gemm_kernel<BN, MODE, EPI, RES, CG, F16, GNG>, dim3((unsigned)grid), dim3(NUM_THREADS), Cfg::SMEM_BYTES, s,
+    B2V_CUDA_OK(launch_pdl(gemm_kernel<BN, MODE, EPI, RES, CG, F16, FUSE>, dim3((unsigned)grid), dim3(NUM_THREADS), Cfg::SMEM_BYTES, s,
                            tmA, tmB, tmO, tmR, p));
   } else {
     // one CTA pair (cluster of 2 = the two SMs of a TPC) per work unit, persistent over the units
@@ -620,26 +686,50 @@ int launch_gemm(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams
     attr[1].val.programmaticStreamSerializationAllowed = pdl_enabled() ? 1 : 0;
     cfg.attrs = attr;
     cfg.numAttrs = 2;
-    B2V_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_kernel<BN, MODE, EPI, RES, CG, F16, GNG>, tmA, tmB, tmO, tmR, p));
+    B2V_CUDA_OK(cudaLaunchKernelEx(&cfg, gemm_kernel<BN, MODE, EPI, RES, CG, F16, FUSE>, tmA, tmB, tmO, tmR, p));
   }
   count_launch();
   B2V_CUDA_OK(launch_check());
   return 0;
 }
 
-template <int BN, int MODE, int CG, bool F16, int GNG = 0>
+template <int BN, int MODE, int CG, bool F16, int FUSE = 0>
 int launch_plain(const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p, int64_t orows, int64_t oslabs,
                  cudaStream_t s) {
-  if (p.residual) return launch_gemm<BN, MODE, EPI_PLAIN, true, CG, F16, GNG>(tmA, tmB, p, orows, oslabs, s);
-  return launch_gemm<BN, MODE, EPI_PLAIN, false, CG, F16, GNG>(tmA, tmB, p, orows, oslabs, s);
+  if (p.residual) return launch_gemm<BN, MODE, EPI_PLAIN, true, CG, F16, FUSE>(tmA, tmB, p, orows, oslabs, s);
+  return launch_gemm<BN, MODE, EPI_PLAIN, false, CG, F16, FUSE>(tmA, tmB, p, orows, oslabs, s);
 }
 
 template <int MODE, int CG, bool F16>
 int dispatch_gemm_t(int bn, bool geglu, const CUtensorMap& tmA, const CUtensorMap& tmB, const GemmParams& p,
                     int64_t orows, int64_t oslabs, cudaStream_t s) {
   if (geglu) {
-    if (bn == 256) return launch_gemm<256, MODE, EPI_GEGLU_T, false, CG, F16>(tmA, tmB, p, orows, oslabs, s);
+    if (bn == 256) {
+      if constexpr (MODE == 0) {
+        if (p.ln_stats) return launch_gemm<256, MODE, EPI_GEGLU_T, false, CG, F16, FUSE_LNIN>(tmA, tmB, p, orows, oslabs, s);
+      }
+      return launch_gemm<256, MODE, EPI_GEGLU_T, false, CG, F16>(tmA, tmB, p, orows, oslabs, s);
+    }
     return fail(B2V_ERR_ARG, "GEGLU epilogue needs N %% 256 == 0");
+  }
+  if constexpr (MODE == 0) {  // LayerNorm fused across GEMMs: linear layers only
+    if (p.ln_stats) {
+      if (p.residual) return fail(B2V_ERR_ARG, "a GEMM that normalises its input takes no residual");
+      switch (bn) {
+        case 256: return launch_gemm<256, MODE, EPI_PLAIN, false, CG, F16, FUSE_LNIN>(tmA, tmB, p, orows, oslabs, s);
+        case 160: return launch_gemm<160, MODE, EPI_PLAIN, false, CG, F16, FUSE_LNIN>(tmA, tmB, p, orows, oslabs, s);
+        case 128: return launch_gemm<128, MODE, EPI_PLAIN, false, CG, F16, FUSE_LNIN>(tmA, tmB, p, orows, oslabs, s);
+      }
+      return fail(B2V_ERR_ARG, "no LayerNorm-input tile for N");
+    }
+    if (p.row_stats) {
+      switch (bn) {
+        case 256: return launch_plain<256, MODE, CG, F16, FUSE_RSTAT>(tmA, tmB, p, orows, oslabs, s);
+        case 160: return launch_plain<160, MODE, CG, F16, FUSE_RSTAT>(tmA, tmB, p, orows, oslabs, s);
+        case 128: return launch_plain<128, MODE, CG, F16, FUSE_RSTAT>(tmA, tmB, p, orows, oslabs, s);
+      }
+      return fail(B2V_ERR_ARG, "no row-statistics tile for N");
+    }
   }
   switch (bn) {
     case 256: return launch_plain<256, MODE, CG, F16>(tmA, tmB, p, orows, oslabs, s);
@@ -724,6 +814,16 @@ static bool gn_stats_shape_ok(int64_t M, int N, int64_t rpb, int groups, int bn,
   const int cpg = N / groups;
   return bn == 160 && cg == 2 && N % 160 == 0 && (cpg == 10 || cpg == 20 || cpg == 40) && rpb % (BM * 2) == 0 && M % rpb == 0;
 }
+// number of {sum, sumsq} partials per row a GEMM with GemmArgs::row_stats writes (2 per N tile: one per epilogue warp
+// column half); 0 when the shape has no row-statistics epilogue (64-wide tiles)
+int row_stats_slots(int64_t M, int N, int64_t rows_per_batch) {
+  const int64_t rpb = rows_per_batch > 0 ? rows_per_batch : M;
+  if (M <= 0 || M % rpb != 0) return 0;
+  const int64_t slabs = M / rpb, m_tiles_per_slab = (rpb + BM - 1) / BM;
+  const int cg = pick_cg(m_tiles_per_slab);
+  const int bn = pick_bn(N, false, slabs * ((m_tiles_per_slab + cg - 1) / cg), cg);
+  return (bn == 256 || bn == 160 || bn == 128) ? 2 * (N / bn) : 0;
+}
 bool gn_stats_ok(int64_t M, int N, int64_t rows_per_batch, int groups) {
   const int64_t rpb = rows_per_batch > 0 ? rows_per_batch : M;
   if (M <= 0 || M % rpb != 0) return false;
@@ -786,6 +886,16 @@ int gemm_tiled(const GemmArgs& g, cudaStream_t s) {
   if (g.gn_stats && !geglu && !p.gelu && gn_stats_shape_ok(g.M, g.N, rpb, g.gn_groups, bn, cg)) {
     p.gn_stats = g.gn_stats;
     p.gn_groups = g.gn_groups;
+  }
+  if (g.row_stats) {
+    B2V_CHECK(!geglu && !p.gelu && g.taps == 1 && !p.gn_stats && bn != 64, "row_stats: plain linear epilogues only");
+    p.row_stats = g.row_stats;
+  }
+  if (g.ln_stats) {
+    B2V_CHECK(g.ln_csum && g.bias && g.ln_slots > 0 && g.taps == 1 && !g.residual && !g.rowbias && !p.gelu && bn != 64 &&
+                  !p.row_stats && !p.gn_stats,
+              "ln_stats: needs csum + folded bias, a plain or GEGLU linear epilogue");
+    p.ln_stats = g.ln_stats; p.ln_csum = g.ln_csum; p.ln_slots = g.ln_slots; p.ln_eps = g.ln_eps;
   }
   if (cg == 2) return dispatch_gemm<0, 2>(g.adt, bn, geglu, tmA, tmB, p, rpb, slabs, s);
   return dispatch_gemm<0, 1>(g.adt, bn, geglu, tmA, tmB, p, rpb, slabs, s);

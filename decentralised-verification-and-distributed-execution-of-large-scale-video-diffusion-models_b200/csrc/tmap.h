@@ -41,7 +41,17 @@ struct GemmArgs {
   // does not qualify — ask gn_stats_ok first.
   float* gn_stats = nullptr;
   int gn_groups = 32;
+  // LayerNorm fused across two linear layers (see gemm.cu FUSE_RSTAT / FUSE_LNIN):
+  //  producer: row_stats[M][row_stats_slots()] {sum, sumsq} partials of every output row
+  //  consumer: `a` is the RAW activation, ln_stats its partials (ln_slots per row), `w` = W diag(gamma),
+  //            ln_csum[N] = row sums of that (rounded) w, `bias` = b + W beta:  out = rstd (acc - mean csum) + bias
+  float* row_stats = nullptr;
+  const float* ln_stats = nullptr;
+  const float* ln_csum = nullptr;
+  int ln_slots = 0;
+  float ln_eps = 1e-5f;
 };
+int row_stats_slots(int64_t M, int N, int64_t rows_per_batch);
 // true when gemm_tiled / conv3x3_im2col called with these sizes will fill GemmArgs::gn_stats / ConvArgs::gn_stats
 bool gn_stats_ok(int64_t M, int N, int64_t rows_per_batch, int groups);
 

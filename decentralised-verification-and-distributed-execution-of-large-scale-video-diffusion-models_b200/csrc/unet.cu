@@ -78,6 +78,53 @@ __global__ void pack_geglu_kernel(const float* __restrict__ w, const float* __re
   }
 }
 
+// LayerNorm folded into the linear layer that consumes it (gemm.cu FUSE_LNIN): one CTA per output row n of W [N][K]:
+//   w_out[n][k] = w[n][k] * gamma[k]            (fp32; rounded to the operand type by the packing kernels afterwards)
+//   csum[n]     = sum_k round(w_out[n][k])      (of the values the tensor core will actually multiply)
+//   bias_out[n] = bias_in[n] + sum_k w[n][k] * beta[k]
+// Fixed-order block reduction: the packed weights are bit-reproducible.
+template <bool F16>
+__global__ void __launch_bounds__(128)
+ln_fold_rows_kernel(const float* __restrict__ w, const float* __restrict__ gamma, const float* __restrict__ beta,
+                    const float* __restrict__ bias_in, float* __restrict__ w_out, float* __restrict__ csum,
+                    float* __restrict__ bias_out, int K) {
+  __shared__ float sh[2][128];
+  const int n = blockIdx.x;
+  float cs = 0.f, bs = 0.f;
+  for (int k = threadIdx.x; k < K; k += 128) {
+    const float wv = w[(int64_t)n * K + k];
+    const float ws = wv * gamma[k];
+    w_out[(int64_t)n * K + k] = ws;
+    cs += act_to_float<F16>(to_act<F16>(ws));
+    bs = fmaf(wv, beta[k], bs);
+  }
+  sh[0][threadIdx.x] = cs;
+  sh[1][threadIdx.x] = bs;
+  __syncthreads();
+  for (int o = 64; o >= 1; o >>= 1) {
+    if ((int)threadIdx.x < o) {
+      sh[0][threadIdx.x] += sh[0][threadIdx.x + o];
+      sh[1][threadIdx.x] += sh[1][threadIdx.x + o];
+    }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    csum[n] = sh[0][0];
+    bias_out[n] = (bias_in ? bias_in[n] : 0.f) + sh[1][0];
+  }
+}
+// a [2H] vector permuted like the rows of a packed GEGLU weight (pack_geglu_kernel)
+__global__ void pack_geglu_vec_kernel(const float* __restrict__ v, float* __restrict__ vo, int H) {
+  const int r = blockIdx.x * blockDim.x + threadIdx.x;
+  if (r >= 2 * H) return;
+  const int tile = r / 256, within = r % 256;
+  vo[r] = v[within < 128 ? tile * 128 + within : H + tile * 128 + (within - 128)];
+}
+__global__ void fill_kernel(float* __restrict__ p, float v, int n) {
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) p[i] = v;
+}
+
 inline int ew_grid(int64_t n) {
   int64_t g = (n + 255) / 256;
   if (g > 148 * 16) g = 148 * 16;
@@ -142,7 +189,11 @@ class Arena {
 // packed weights
 // ------------------------------------------------------------------------------------------------
 struct Norm { float* g = nullptr; float* b = nullptr; int C = 0; };
-struct Lin { bf16* w = nullptr; float* b = nullptr; int N = 0, K = 0; };  // w [N][K]
+struct Lin {  // w [N][K]
+  bf16* w = nullptr; float* b = nullptr; int N = 0, K = 0;
+  float* lnsum = nullptr;  // non-null: the LayerNorm in front of this layer is folded in (w = W diag(gamma), b = b + W beta,
+                           // lnsum[n] = sum_k w[n][k]): feed it the RAW hidden states + their row statistics
+};
 struct Conv { bf16* w = nullptr; float* b = nullptr; int Cout = 0, Cin = 0; };  // w [Cout][9][Cin]
 
 struct ResnetW {
@@ -203,6 +254,8 @@ struct b2v_unet3d {
   float* temb_scratch = nullptr;  // [kMaxB*temb] silu(emb) + sinusoid + hidden
   float* t_dev = nullptr;         // the timestep, read by the (replayed) sinusoid kernel
   std::vector<ResnetW*> all_resnets;
+  bool ln_fuse = true;            // LayerNorms folded into their consuming linear layers (B2V_LN_FUSE=0 at finalize: off)
+  float *ln_ones = nullptr, *ln_zeros = nullptr;  // unit LayerNorm affine for the (rare) shapes without a fused epilogue
 
   // CUDA-graph replay of the ~1100-launch forward: one executable graph per (shape, io dtype, workspace). The graph
   // reads / writes fixed staging buffers at the head of the workspace, so caller pointers may change between calls.
@@ -305,6 +358,56 @@ struct Loader {
     }
     return l;
   }
+  // ---- LayerNorm `ln` folded into the layer(s) that read its output ----
+  // rows [row0, row0+Neach) of the fp32 scratch (w_tmp [Ntot][K], cs_tmp / b_tmp [Ntot]) from checkpoint matrix `name`
+  void fold_rows(const std::string& name, bool has_bias, int Neach, int K, const Norm& ln, float* w_tmp, float* cs_tmp,
+                 float* b_tmp, int row0) {
+    const float* w = get(name + ".weight", {Neach, K});
+    const float* b = has_bias ? get(name + ".bias", {Neach}) : nullptr;
+    if (!w || !ln.g || !ln.b || !w_tmp) return;
+    if (f16()) ln_fold_rows_kernel<true><<<Neach, 128, 0, s>>>(w, ln.g, ln.b, b, w_tmp + (size_t)row0 * K, cs_tmp + row0, b_tmp + row0, K);
+    else ln_fold_rows_kernel<false><<<Neach, 128, 0, s>>>(w, ln.g, ln.b, b, w_tmp + (size_t)row0 * K, cs_tmp + row0, b_tmp + row0, K);
+  }
+  struct Tmp { float *w = nullptr, *cs = nullptr, *b = nullptr; };
+  Tmp tmp_alloc(int Ntot, int K) {
+    Tmp t;
+    if (cudaMalloc((void**)&t.w, sizeof(float) * (size_t)Ntot * K) != cudaSuccess ||
+        cudaMalloc((void**)&t.cs, sizeof(float) * Ntot) != cudaSuccess ||
+        cudaMalloc((void**)&t.b, sizeof(float) * Ntot) != cudaSuccess) { if (err.empty()) err = "cudaMalloc failed"; }
+    return t;
+  }
+  void tmp_free(Tmp& t) { cudaStreamSynchronize(s); cudaFree(t.w); cudaFree(t.cs); cudaFree(t.b); }
+  // plain linear layer(s) stacked row-wise, LayerNorm folded in
+  Lin lin_ln(const std::vector<std::string>& names, int Neach, int K, bool has_bias, const Norm& ln) {
+    Lin l; l.N = Neach * (int)names.size(); l.K = K;
+    Tmp t = tmp_alloc(l.N, K);
+    for (size_t i = 0; i < names.size(); ++i) fold_rows(names[i], has_bias, Neach, K, ln, t.w, t.cs, t.b, (int)i * Neach);
+    l.w = mat_bf16(t.w, (int64_t)l.N * K);
+    l.b = dalloc<float>((size_t)l.N);
+    l.lnsum = dalloc<float>((size_t)l.N);
+    if (l.b && l.lnsum && t.b && t.cs) {
+      cudaMemcpyAsync(l.b, t.b, sizeof(float) * l.N, cudaMemcpyDeviceToDevice, s);
+      cudaMemcpyAsync(l.lnsum, t.cs, sizeof(float) * l.N, cudaMemcpyDeviceToDevice, s);
+    }
+    tmp_free(t);
+    return l;
+  }
+  Lin geglu_ln(const std::string& p, int dim, const Norm& ln) {
+    const int H = 4 * dim;
+    Lin l; l.N = 2 * H; l.K = dim;
+    Tmp t = tmp_alloc(2 * H, dim);
+    fold_rows(p, true, 2 * H, dim, ln, t.w, t.cs, t.b, 0);
+    l.w = dalloc<bf16>((size_t)2 * H * dim);
+    l.b = dalloc<float>((size_t)2 * H);
+    l.lnsum = dalloc<float>((size_t)2 * H);
+    if (t.w && t.b && t.cs && l.w && l.b && l.lnsum) {
+      if (f16()) pack_geglu_kernel<true><<<ew_grid((int64_t)2 * H * dim), 256, 0, s>>>(t.w, t.b, l.w, l.b, H, dim);
+      else pack_geglu_kernel<false><<<ew_grid((int64_t)2 * H * dim), 256, 0, s>>>(t.w, t.b, l.w, l.b, H, dim);
+      pack_geglu_vec_kernel<<<(2 * H + 255) / 256, 256, 0, s>>>(t.cs, l.lnsum, H);
+    }
+    tmp_free(t);
+    return l;
+  }
   Conv conv3x3(const std::string& p, int Cout, int Cin) {
     Conv c; c.Cout = Cout; c.Cin = Cin;
     const float* w = get(p + ".weight", {Cout, Cin, 3, 3});
@@ -358,19 +461,22 @@ struct Loader {
   }
   BlockW block(const std::string& p, int dim, int heads, bool cross, int cross_dim) {
     BlockW b; b.dim = dim; b.heads = heads; b.cross = cross;
+    const bool fuse = u->ln_fuse;
     b.ln1 = norm(p + ".norm1", dim);
-    b.qkv1 = lin_stack({p + ".attn1.to_q", p + ".attn1.to_k", p + ".attn1.to_v"}, dim, dim);
+    b.qkv1 = fuse ? lin_ln({p + ".attn1.to_q", p + ".attn1.to_k", p + ".attn1.to_v"}, dim, dim, false, b.ln1)
+                  : lin_stack({p + ".attn1.to_q", p + ".attn1.to_k", p + ".attn1.to_v"}, dim, dim);
     b.o1 = lin(p + ".attn1.to_out.0", dim, dim, true);
     b.ln2 = norm(p + ".norm2", dim);
     if (cross) {
-      b.q2 = lin(p + ".attn2.to_q", dim, dim, false);
+      b.q2 = fuse ? lin_ln({p + ".attn2.to_q"}, dim, dim, false, b.ln2) : lin(p + ".attn2.to_q", dim, dim, false);
       b.kv2 = lin_stack({p + ".attn2.to_k", p + ".attn2.to_v"}, dim, cross_dim);
     } else {
-      b.qkv2 = lin_stack({p + ".attn2.to_q", p + ".attn2.to_k", p + ".attn2.to_v"}, dim, dim);
+      b.qkv2 = fuse ? lin_ln({p + ".attn2.to_q", p + ".attn2.to_k", p + ".attn2.to_v"}, dim, dim, false, b.ln2)
+                    : lin_stack({p + ".attn2.to_q", p + ".attn2.to_k", p + ".attn2.to_v"}, dim, dim);
     }
     b.o2 = lin(p + ".attn2.to_out.0", dim, dim, true);
     b.ln3 = norm(p + ".norm3", dim);
-    b.ff1 = geglu(p + ".ff.net.0.proj", dim);
+    b.ff1 = fuse ? geglu_ln(p + ".ff.net.0.proj", dim, b.ln3) : geglu(p + ".ff.net.0.proj", dim);
     b.ff2 = lin(p + ".ff.net.2", dim, 4 * dim, true);
     return b;
   }
@@ -441,12 +547,13 @@ struct Act { bf16* p; int64_t rows; int C; int H, W; };  // rows = B*F*H*W
 
 // feeds_gn: the output goes (first) into a GroupNorm without concat — ask the epilogue for its statistics
 void gemm(Ctx& c, const bf16* a, int64_t M, const Lin& l, const bf16* residual, bf16* out, int flags = 0,
-          int64_t lda = 0, bool feeds_gn = false) {
+          int64_t lda = 0, bool feeds_gn = false, float* row_stats = nullptr) {
   c.flops += 2.0 * (double)M * l.N * l.K;
   float* st = feeds_gn ? c.want_stats(out, M, l.N, M) : nullptr;
   if (!c.live()) return;
   GemmArgs g;
   g.gn_stats = st; g.gn_groups = c.u->cfg.norm_num_groups;
+  g.row_stats = row_stats;
   g.adt = c.u->adt;
   g.a = a; g.lda = lda; g.w = l.w; g.bias = l.b; g.residual = residual; g.out = out;
   g.M = M; g.N = l.N; g.Kc = l.K; g.taps = 1; g.rows_per_batch = M; g.flags = flags;
@@ -542,12 +649,45 @@ Act temp_conv(Ctx& c, const TempConvW& t, const Act& x) {
   return Act{prev_owned, M, t.C, x.H, x.W};
 }
 
-void feed_forward(Ctx& c, const BlockW& b, bf16* h, int64_t M) {
-  bf16* l = c.act(M, b.dim);
-  if (c.live()) c.run(layer_norm(c.u->adt, h, b.ln3.g, b.ln3.b, l, M, b.dim, 1e-5f, c.s));
+// Row statistics of the hidden states [M, dim] for the LayerNorm fused into the NEXT linear layer: the buffer the
+// producing GEMM fills (null when this handle keeps separate LayerNorm passes or the shape has no such epilogue).
+struct RowStats { float* p = nullptr; int slots = 0; };
+RowStats row_stats_alloc(Ctx& c, int64_t M, int dim) {
+  RowStats r;
+  if (!c.u->ln_fuse) return r;
+  r.slots = row_stats_slots(M, dim, M);
+  if (r.slots > 0) r.p = (float*)c.bytes(sizeof(float) * 2 * (size_t)M * r.slots);
+  return r;
+}
+// out = LayerNorm(h) W^T + b for a layer whose LayerNorm `ln` may be folded in (Lin::lnsum): with row statistics the
+// normalisation happens in the GEMM epilogue; a folded layer without statistics gets a unit-affine LayerNorm pass in
+// front (W diag(gamma) n(h) + W beta is the same function); an unfolded layer gets the classic pass.
+void ln_gemm(Ctx& c, const bf16* h, int64_t M, const Norm& ln, const Lin& l, bf16* out, const RowStats& rs, int flags = 0) {
+  if (l.lnsum && rs.p) {
+    c.flops += 2.0 * (double)M * l.N * l.K;
+    if (!c.live()) return;
+    GemmArgs g;
+    g.adt = c.u->adt;
+    g.a = h; g.w = l.w; g.bias = l.b; g.out = out;
+    g.M = M; g.N = l.N; g.Kc = l.K; g.taps = 1; g.rows_per_batch = M; g.flags = flags;
+    g.ln_stats = rs.p; g.ln_csum = l.lnsum; g.ln_slots = rs.slots; g.ln_eps = 1e-5f;
+    c.run(gemm_tiled(g, c.s));
+    return;
+  }
+  bf16* n = c.act(M, l.K);
+  if (c.live()) {
+    const float* gm = l.lnsum ? c.u->ln_ones : ln.g;
+    const float* bt = l.lnsum ? c.u->ln_zeros : ln.b;
+    c.run(layer_norm(c.u->adt, h, gm, bt, n, M, l.K, 1e-5f, c.s));
+  }
+  gemm(c, n, M, l, nullptr, out, flags);
+  c.free(n);
+}
+
+void feed_forward(Ctx& c, const BlockW& b, bf16* h, int64_t M, RowStats& rs) {
   bf16* g = c.act(M, 4 * b.dim);
-  gemm(c, l, M, b.ff1, nullptr, g, B2V_EPI_GEGLU);
-  c.free(l);
+  ln_gemm(c, h, M, b.ln3, b.ff1, g, rs, B2V_EPI_GEGLU);
+  if (rs.p) { c.free(rs.p); rs.p = nullptr; }
   gemm(c, g, M, b.ff2, h, h);  // in-place residual: each element is read then written by the same thread
   c.free(g);
 }
@@ -560,15 +700,13 @@ Act spatial(Ctx& c, const SpatialW& a, const Act& x) {
   bf16* n = c.act(M, C);
   gn(c, x.p, C, nullptr, 0, a.norm, n, N, HW, 1e-6f, 0);
   bf16* h = c.act(M, C);
-  gemm(c, n, M, a.proj_in, nullptr, h);
+  RowStats rs = row_stats_alloc(c, M, C);  // statistics of h for norm1 / norm2 / norm3 in turn
+  gemm(c, n, M, a.proj_in, nullptr, h, 0, 0, false, rs.p);
   c.free(n);
   const BlockW& b = a.blk;
   {  // self attention
-    bf16* l = c.act(M, C);
-    if (c.live()) c.run(layer_norm(c.u->adt, h, b.ln1.g, b.ln1.b, l, M, C, 1e-5f, c.s));
     bf16* qkv = c.act(M, 3 * C);
-    gemm(c, l, M, b.qkv1, nullptr, qkv);
-    c.free(l);
+    ln_gemm(c, h, M, b.ln1, b.qkv1, qkv, rs);
     bf16* o = c.act(M, C);
     c.flops += 4.0 * (double)N * heads * (double)HW * (double)HW * 64.0;
     if (c.live()) {
@@ -580,16 +718,13 @@ Act spatial(Ctx& c, const SpatialW& a, const Act& x) {
       c.run(attention(t, c.s));
     }
     c.free(qkv);
-    gemm(c, o, M, b.o1, h, h);
+    gemm(c, o, M, b.o1, h, h, 0, 0, false, rs.p);  // the statistics of the updated h replace the consumed ones
     c.free(o);
   }
   {  // cross attention against the text tokens (K/V depend only on the prompt: B*77 rows, shared by all frames)
     const int TL = c.u->cfg.text_len;
-    bf16* l = c.act(M, C);
-    if (c.live()) c.run(layer_norm(c.u->adt, h, b.ln2.g, b.ln2.b, l, M, C, 1e-5f, c.s));
     bf16* q = c.act(M, C);
-    gemm(c, l, M, b.q2, nullptr, q);
-    c.free(l);
+    ln_gemm(c, h, M, b.ln2, b.q2, q, rs);
     bf16* kv = c.act((int64_t)c.B * TL, 2 * C);
     gemm(c, c.text, (int64_t)c.B * TL, b.kv2, nullptr, kv);
     bf16* o = c.act(M, C);
@@ -604,10 +739,10 @@ Act spatial(Ctx& c, const SpatialW& a, const Act& x) {
     }
     c.free(q);
     c.free(kv);
-    gemm(c, o, M, b.o2, h, h);
+    gemm(c, o, M, b.o2, h, h, 0, 0, false, rs.p);
     c.free(o);
   }
-  feed_forward(c, b, h, M);
+  feed_forward(c, b, h, M, rs);
   bf16* out = c.act(M, C);
   gemm(c, h, M, a.proj_out, x.p, out, 0, 0, true);
   c.free(h);
@@ -622,26 +757,24 @@ Act temporal(Ctx& c, const TemporalW& a, const Act& x) {
   bf16* n = c.act(M, C);
   gn(c, x.p, C, nullptr, 0, a.norm, n, c.B, (int64_t)c.F * HW, 1e-6f, 0);
   bf16* h = c.act(M, D);
-  gemm(c, n, M, a.proj_in, nullptr, h);
+  RowStats rs = row_stats_alloc(c, M, D);
+  gemm(c, n, M, a.proj_in, nullptr, h, 0, 0, false, rs.p);
   c.free(n);
   const BlockW& b = a.blk;
   for (int which = 0; which < 2; ++which) {
     const Norm& ln = which == 0 ? b.ln1 : b.ln2;
     const Lin& qkvw = which == 0 ? b.qkv1 : b.qkv2;
     const Lin& ow = which == 0 ? b.o1 : b.o2;
-    bf16* l = c.act(M, D);
-    if (c.live()) c.run(layer_norm(c.u->adt, h, ln.g, ln.b, l, M, D, 1e-5f, c.s));
     bf16* qkv = c.act(M, 3 * D);
-    gemm(c, l, M, qkvw, nullptr, qkv);
-    c.free(l);
+    ln_gemm(c, h, M, ln, qkvw, qkv, rs);
     bf16* o = c.act(M, D);
     c.flops += 4.0 * (double)c.B * HW * heads * (double)c.F * (double)c.F * 64.0;
     if (c.live()) c.run(temporal_attention(c.u->adt, qkv, 3 * D, 0, D, 2 * D, o, D, c.B, c.F, HW, heads, scale, c.s));
     c.free(qkv);
-    gemm(c, o, M, ow, h, h);
+    gemm(c, o, M, ow, h, h, 0, 0, false, rs.p);
     c.free(o);
   }
-  feed_forward(c, b, h, M);
+  feed_forward(c, b, h, M, rs);
   bf16* out = c.act(M, C);
   gemm(c, h, M, a.proj_out, x.p, out, 0, 0, true);
   c.free(h);
@@ -866,9 +999,21 @@ extern "C" int b2v_unet3d_finalize(b2v_unet3d* u) {
   B2V_CHECK(u, "null handle");
   if (u->finalized) return 0;
   const b2v_unet3d_config& cfg = u->cfg;
+  {
+    const char* e = getenv("B2V_LN_FUSE");
+    u->ln_fuse = !(e && atoi(e) == 0);
+  }
   Loader L{u};
   const int* ch = cfg.block_out_channels;
   const int hd = cfg.attention_head_dim;
+  if (u->ln_fuse) {
+    u->ln_ones = L.dalloc<float>(2048);
+    u->ln_zeros = L.dalloc<float>(2048);
+    if (u->ln_ones && u->ln_zeros) {
+      fill_kernel<<<8, 256>>>(u->ln_ones, 1.0f, 2048);
+      fill_kernel<<<8, 256>>>(u->ln_zeros, 0.0f, 2048);
+    }
+  }
   // stem
   {
     const float* w = L.get("conv_in.weight", {ch[0], cfg.in_channels, 3, 3});

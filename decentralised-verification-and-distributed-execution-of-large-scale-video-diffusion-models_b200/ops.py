@@ -252,6 +252,33 @@ def gemm(a, w, bias=None, rowbias=None, rows_per_group=0, residual=None, taps=1,
     return out
 
 
+def gemm_rowstats(a, w, bias=None, residual=None):
+    """gemm() that also emits the per-row {sum, sumsq} partials of its output: (out, stats [M, slots, 2] fp32)."""
+    lib = _lib.load()
+    _cuda(a); _cuda(w)
+    M, Kc = a.shape
+    N = w.shape[0]
+    slots = lib.b2v_row_stats_slots(M, N, 0)
+    out = torch.empty((M, N), dtype=a.dtype, device=a.device)
+    stats = torch.zeros((M, max(slots, 1), 2), dtype=torch.float32, device=a.device)
+    check(lib.b2v_op_gemm_rowstats(ptr(a), ptr(w), ptr(bias), ptr(residual), ptr(out), M, N, Kc, act_tag(a), ptr(stats),
+                                   stream()))
+    return out, stats
+
+
+def gemm_lnin(a_raw, w_gamma, bias_folded, csum, ln_stats, eps=1e-5, flags=0):
+    """LayerNorm(a_raw) @ W^T + b with the normalisation finished in the epilogue (see include/b2v.h)."""
+    lib = _lib.load()
+    _cuda(a_raw); _cuda(w_gamma)
+    M, Kc = a_raw.shape
+    N = w_gamma.shape[0]
+    n_out = N // 2 if flags & _lib.EPI_GEGLU else N
+    out = torch.empty((M, n_out), dtype=a_raw.dtype, device=a_raw.device)
+    check(lib.b2v_op_gemm_lnin(ptr(a_raw), ptr(w_gamma), ptr(bias_folded), ptr(csum), ptr(ln_stats), ln_stats.shape[1],
+                               float(eps), ptr(out), M, N, Kc, int(flags), act_tag(a_raw), stream()))
+    return out
+
+
 def gn_stats_ok(M, N, rows_per_batch=0, groups=32):
     return bool(_lib.load().b2v_gn_stats_ok(int(M), int(N), int(rows_per_batch), int(groups)))
 

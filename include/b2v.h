@@ -244,6 +244,19 @@ int b2v_op_gemm_gnstats(const void* a_dev, const void* w_dev, const float* bias_
 int b2v_op_conv3x3_gnstats(const void* x_dev, const void* w_dev, const float* bias_dev, const float* rowbias_dev,
                            int64_t rows_per_group, const void* residual_dev, void* out_dev, int N, int H, int W,
                            int Cin, int Cout, int act_dtype, float* gn_stats_dev, int gn_groups, void* stream);
+/* LayerNorm fused across two linear layers (BasicTransformerBlock: norm1 -> to_q/k/v, norm2 -> to_q, norm3 -> GEGLU):
+ * the GEMM that PRODUCES the hidden states (proj_in, to_out + residual) also writes, per output row, the {sum, sum of
+ * squares} of the row over each epilogue warp's columns (b2v_op_gemm_rowstats: row_stats_dev[M][b2v_row_stats_slots()]
+ * float2); the GEMM that CONSUMES them reads the raw hidden states with W' = W diag(gamma) and finishes the
+ * normalisation in its epilogue: out = rstd (acc - mean csum) + bias', csum[n] = sum_k W'[n][k] (of the rounded W'),
+ * bias' = b + W beta (b2v_op_gemm_lnin; flags may carry B2V_EPI_GEGLU with W', bias', csum packed like W).
+ * The LayerNorm pass (one read + one write of the activation) disappears. */
+int b2v_row_stats_slots(int64_t M, int N, int64_t rows_per_batch);
+int b2v_op_gemm_rowstats(const void* a_dev, const void* w_dev, const float* bias_dev, const void* residual_dev,
+                         void* out_dev, int64_t M, int N, int Kc, int act_dtype, float* row_stats_dev, void* stream);
+int b2v_op_gemm_lnin(const void* a_raw_dev, const void* w_gamma_dev, const float* bias_folded_dev, const float* csum_dev,
+                     const float* ln_stats_dev, int ln_slots, float eps, void* out_dev, int64_t M, int N, int Kc,
+                     int flags, int act_dtype, void* stream);
 int b2v_op_group_norm_pre(const void* x_dev, int C, const float* gamma_dev, const float* beta_dev, void* y_dev,
                           int64_t n_items, int64_t rows_per_item, int groups, float eps, int silu, void* scratch_dev,
                           const float* pre_dev, int act_dtype, void* stream);

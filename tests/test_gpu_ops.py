@@ -298,3 +298,58 @@ def test_conv3x3_emits_group_norm_stats(cuda, adt):
     a = ops.group_norm_pre(rows, gam, bet, Nimg, 32, 1e-5, 1, stats)
     b = ops.group_norm(rows, gam, bet, Nimg, 32, 1e-5, 1)
     assert rel_l2(a, b) < 5e-3
+
+
+# ---- LayerNorm fused across two GEMMs (producer emits row partials, consumer finishes the normalisation) ---------------
+@pytest.mark.parametrize("adt", [torch.bfloat16, torch.float16])
+@pytest.mark.parametrize("M,C,Nout,res,geglu", [(512, 320, 960, False, False), (1000, 320, 320, True, False),
+                                                (2048, 640, 1920, True, False), (768, 1280, 1280, False, False),
+                                                (1024, 512, 1536, True, False), (512, 320, 2560, True, True),
+                                                (40000, 320, 960, True, False)])
+def test_layer_norm_fused_across_gemms(cuda, adt, M, C, Nout, res, geglu):
+    """h = a W1^T + b1 (+ h0)  [row partials out];  y = LayerNorm(h) W2^T + b2  [normalisation in the epilogue]
+    vs the unfused chain gemm -> layer_norm -> gemm and vs torch fp32 on the same rounded h."""
+    from b2v import ops, _lib
+    g = torch.Generator(device=cuda).manual_seed(M + C + Nout)
+    a = torch.randn(M, 128, device=cuda, generator=g).to(adt)
+    w1 = (torch.randn(C, 128, device=cuda, generator=g) / math.sqrt(128)).to(adt)
+    b1 = torch.randn(C, device=cuda, generator=g) * 0.5 + 0.3          # a row mean that is not zero
+    h0 = torch.randn(M, C, device=cuda, generator=g).to(adt) if res else None
+    h, stats = ops.gemm_rowstats(a, w1, bias=b1, residual=h0)
+    assert torch.equal(h, ops.gemm(a, w1, bias=b1, residual=h0))
+    hf = h.float()
+    tot = stats.sum(dim=1)                                              # [M, 2]
+    assert rel_l2(tot[:, 0], hf.sum(1)) < 2e-3 and rel_l2(tot[:, 1], (hf * hf).sum(1)) < 2e-3
+    gamma = 1 + 0.2 * torch.randn(C, device=cuda, generator=g)
+    beta = 0.2 * torch.randn(C, device=cuda, generator=g)
+    w2 = torch.randn(Nout, C, device=cuda, generator=g) / math.sqrt(C)
+    b2 = torch.randn(Nout, device=cuda, generator=g)
+    w2g = (w2 * gamma[None, :]).to(adt)                                 # W' = W diag(gamma), rounded once
+    csum = w2g.float().sum(1)
+    b2f = b2 + w2 @ beta
+    flags = 0
+    if geglu:
+        _, csum = pack_geglu(w2, csum)           # vectors are permuted like the rows of W
+        w2g, b2f = pack_geglu(w2g, b2f)
+        flags = _lib.EPI_GEGLU
+    y = ops.gemm_lnin(h, w2g, b2f, csum, stats, eps=1e-5, flags=flags)
+    # reference: torch fp32 on the same (rounded) hidden states
+    ln = torch.nn.functional.layer_norm(hf, (C,), gamma, beta, 1e-5)
+    proj = ln @ w2.t() + b2
+    if geglu:
+        v, gt = proj.chunk(2, dim=-1)
+        ref = v * torch.nn.functional.gelu(gt)
+    else:
+        ref = proj
+    # unfused chain of the same library
+    l = ops.layer_norm(h, gamma, beta)
+    if geglu:
+        wp, bp = pack_geglu(w2.to(adt), b2)
+        chain = ops.gemm(l, wp, bias=bp, flags=_lib.EPI_GEGLU)
+    else:
+        chain = ops.gemm(l, w2.to(adt), bias=b2)
+    e_f, e_c = rel_l2(y, ref), rel_l2(chain, ref)
+    print("ln fused", adt, (M, C, Nout, res, geglu), "fused %.3e  unfused %.3e" % (e_f, e_c))
+    assert e_f < tol(adt, 8e-3), e_f
+    assert e_f < 1.5 * e_c + 1e-4          # no worse than the chain it replaces
+    assert torch.equal(y, ops.gemm_lnin(h, w2g, b2f, csum, stats, eps=1e-5, flags=flags))
