@@ -113,13 +113,6 @@ ln_fold_rows_kernel(const float* __restrict__ w, const float* __restrict__ gamma
     bias_out[n] = (bias_in ? bias_in[n] : 0.f) + sh[1][0];
   }
 }
-// a [2H] vector permuted like the rows of a packed GEGLU weight (pack_geglu_kernel)
-__global__ void pack_geglu_vec_kernel(const float* __restrict__ v, float* __restrict__ vo, int H) {
-  const int r = blockIdx.x * blockDim.x + threadIdx.x;
-  if (r >= 2 * H) return;
-  const int tile = r / 256, within = r % 256;
-  vo[r] = v[within < 128 ? tile * 128 + within : H + tile * 128 + (within - 128)];
-}
 __global__ void fill_kernel(float* __restrict__ p, float v, int n) {
   const int i = blockIdx.x * blockDim.x + threadIdx.x;
   if (i < n) p[i] = v;
@@ -392,22 +385,6 @@ struct Loader {
     tmp_free(t);
     return l;
   }
-  Lin geglu_ln(const std::string& p, int dim, const Norm& ln) {
-    const int H = 4 * dim;
-    Lin l; l.N = 2 * H; l.K = dim;
-    Tmp t = tmp_alloc(2 * H, dim);
-    fold_rows(p, true, 2 * H, dim, ln, t.w, t.cs, t.b, 0);
-    l.w = dalloc<bf16>((size_t)2 * H * dim);
-    l.b = dalloc<float>((size_t)2 * H);
-    l.lnsum = dalloc<float>((size_t)2 * H);
-    if (t.w && t.b && t.cs && l.w && l.b && l.lnsum) {
-      if (f16()) pack_geglu_kernel<true><<<ew_grid((int64_t)2 * H * dim), 256, 0, s>>>(t.w, t.b, l.w, l.b, H, dim);
-      else pack_geglu_kernel<false><<<ew_grid((int64_t)2 * H * dim), 256, 0, s>>>(t.w, t.b, l.w, l.b, H, dim);
-      pack_geglu_vec_kernel<<<(2 * H + 255) / 256, 256, 0, s>>>(t.cs, l.lnsum, H);
-    }
-    tmp_free(t);
-    return l;
-  }
   Conv conv3x3(const std::string& p, int Cout, int Cin) {
     Conv c; c.Cout = Cout; c.Cin = Cin;
     const float* w = get(p + ".weight", {Cout, Cin, 3, 3});
@@ -476,7 +453,9 @@ struct Loader {
     }
     b.o2 = lin(p + ".attn2.to_out.0", dim, dim, true);
     b.ln3 = norm(p + ".norm3", dim);
-    b.ff1 = fuse ? geglu_ln(p + ".ff.net.0.proj", dim, b.ln3) : geglu(p + ".ff.net.0.proj", dim);
+    // norm3 stays a separate pass: folded into the GEGLU epilogue (already the heaviest epilogue of the network) it cost
+    // more than the pass it removes (ncu launch lists rd2f: the K = 320 GEGLU GEMM +34 % against a 1.3 % LayerNorm)
+    b.ff1 = geglu(p + ".ff.net.0.proj", dim);
     b.ff2 = lin(p + ".ff.net.2", dim, 4 * dim, true);
     return b;
   }
@@ -739,7 +718,7 @@ Act spatial(Ctx& c, const SpatialW& a, const Act& x) {
     }
     c.free(q);
     c.free(kv);
-    gemm(c, o, M, b.o2, h, h, 0, 0, false, rs.p);
+    gemm(c, o, M, b.o2, h, h, 0, 0, false, b.ff1.lnsum ? rs.p : nullptr);  // norm3 is a separate pass: no statistics
     c.free(o);
   }
   feed_forward(c, b, h, M, rs);
@@ -771,7 +750,7 @@ Act temporal(Ctx& c, const TemporalW& a, const Act& x) {
     c.flops += 4.0 * (double)c.B * HW * heads * (double)c.F * (double)c.F * 64.0;
     if (c.live()) c.run(temporal_attention(c.u->adt, qkv, 3 * D, 0, D, 2 * D, o, D, c.B, c.F, HW, heads, scale, c.s));
     c.free(qkv);
-    gemm(c, o, M, ow, h, h, 0, 0, false, rs.p);
+    gemm(c, o, M, ow, h, h, 0, 0, false, (which == 0 || b.ff1.lnsum) ? rs.p : nullptr);
     c.free(o);
   }
   feed_forward(c, b, h, M, rs);
