@@ -321,6 +321,9 @@ def gpu_main(args):
             dist.barrier()
             torch.cuda.synchronize(dev)
 
+    # the dominant kernel once BEFORE the load (clocks not yet pulled down by the power cap): reported next to the
+    # in-load measurement the roofline uses
+    cold = dominant_kernel_roofline(torch, ops, dev, peaks, mine) if rank == 0 else None
     for i in range(args.warmup):
         video_step(i)
     sync_all()
@@ -423,6 +426,9 @@ def gpu_main(args):
                      "what": "whole UNet3D forward(s) of the bottleneck rank per video-step: algorithmic FLOPs "
                              "(b2v_unet3d_flops, MAC=2) / CUDA-event time; peak = sustained cuBLAS bf16, " + peaks["source"]}
     roofline = dominant_kernel_roofline(torch, ops, dev, peaks, mine)
+    roofline["when"] = "right after the timed steps: GPU under the power cap (clocks as in `clocks`)"
+    roofline["cold"] = {"achieved": cold["achieved"], "frac": cold["frac"], "ms_per_launch": cold["ms_per_launch"],
+                        "when": "before the first step of the process (boost clocks)"}
     if args.timed_only:
         emit({"metric": METRIC, "value": value, "unit": "steps/s", "n_gpus": world, "steps": args.steps,
               "warmup": args.warmup, "ms_per_step": per_step_ms, "gpu_launches": int(launches), "clocks": clocks,
@@ -626,11 +632,11 @@ def dominant_kernel_roofline(torch, ops, dev, peaks, mine):
     flops = 4.0 * nb * heads * S * S * 64
     ach = flops / (ms / 1e3) / 1e12
     # dram__bytes_read.sum + dram__bytes_write.sum of ONE launch of this shape from the committed `ncu --set full` capture
-    # (profiles/r01j_ncu_full_summary.md: 566.4 MB read + 172.1 MB written; algorithmic q+k+v+out = 755 MB)
-    traffic = 738.4e6 if (nb, heads, S) == (32, 5, 9216) else None
+    # (profiles/rd2b_ncu_full_summary.md: 566.6 MB read + 171.6 MB written; algorithmic q+k+v+out = 755 MB)
+    traffic = 738.2e6 if (nb, heads, S) == (32, 5, 9216) else None
     return {"bound": "tensor", "achieved": ach, "peak": peaks["bf16_burst"], "unit": "TFLOP/s",
             "frac": ach / peaks["bf16_burst"], "traffic": traffic,
-            "traffic_source": "ncu --set full, profiles/r01j_ncu_full_summary.md (bytes per launch)",
+            "traffic_source": "ncu --set full, profiles/rd2b_ncu_full_summary.md (bytes per launch)",
             "kernel": "attn_kernel (spatial self-attention L0)",
             "shape": {"batch": nb, "heads": heads, "seq": S, "head_dim": 64}, "ms_per_launch": ms,
             "flops_per_launch": flops, "peak_source": "burst cuBLAS bf16, " + peaks["source"]}

@@ -130,8 +130,9 @@ def _cfg(**kw):
 # 1.0-1.6e-2 relative L2 of the fp32 oracle (8-bit mantissa, ~150 sequential roundings; cosine >= 0.9998).
 # Classifier-free guidance forms u + gs (c - u) with |c - u| ~ 0.1-0.3 |u|, which amplifies that noise by ~gs/2:
 # gs = 7.5 -> guided eps 6.5e-2, per-step latents 4.2-4.6e-2 (flat over steps: DDIM contracts it, 3.6e-2 at step 25);
-# gs = 1 -> latents 6e-3. Gates: 6e-2 with CFG 7.5 (the reference's setting), 1.5e-2 without amplification.
-@pytest.mark.parametrize("coherent,gs,tol", [(False, 7.5, 6e-2), (True, 7.5, 6e-2), (False, 1.0, 1.5e-2)])
+# gs = 1 -> latents 6e-3. Gates = measured x 1.25 (profiles/rd2h_parity_numbers.log: 4.40e-2 / 4.30e-2 / 6.0e-3); the
+# fp16 arithmetic mode — the reference's own — is gated at 1e-2 on BASELINE configs[0] (tests/test_gpu_fullsize.py).
+@pytest.mark.parametrize("coherent,gs,tol", [(False, 7.5, 5.5e-2), (True, 7.5, 5.4e-2), (False, 1.0, 7.6e-3)])
 def test_strategy_single_process_vs_oracle(cuda, coherent, gs, tol):
     """config[0] shape with the TINY-width UNet: world = 1 process plays both ranks' windows (plan for world=2 is
     injected), every per-step latent is compared with the fp32 oracle trajectory."""
