@@ -5,6 +5,8 @@
 //   * LayerNorm over channels
 //   * nearest 2x upsample, channel concat, explicit im2col (fallback / stride-2 cross-check)
 // All 128-bit vectorised, 8 bf16 per thread per access, fp32 math.
+#include <stdlib.h>
+
 #include "common.cuh"
 #include "ops.h"
 
@@ -123,35 +125,38 @@ __device__ __forceinline__ void gn_fold_item(const float* __restrict__ partial, 
   __syncthreads();
 }
 
-// Statistics that arrive from the producing GEMM's epilogue come as one {sum, sumsq} per 32-row block and group. When an
-// item has more of them than an apply CTA should fold by itself (temporal norms: F*H*W / 32 blocks per batch element),
-// this kernel folds them once per item — fixed order, fp64 — into ONE partial per (item, group): grid = (groups, items),
-// a warp-strided sum per thread, then a fixed-order tree over the CTA.
+// Statistics that arrive from the producing GEMM's epilogue come as one {sum, sumsq} per 32-row block and group. An apply
+// CTA that folded all of them itself paid for it (ncu rd2j: 288 blocks per frame made gn_apply 90 us instead of 68), so
+// this kernel folds them first: grid = (parts, items), each CTA a contiguous range of blocks, lane = group (a warp reads
+// whole 256-byte rows of the table: coalesced), warps stride over the blocks, fp64, fixed order; the apply pass then folds
+// `parts` (<= 16) partials per item.
 __global__ void __launch_bounds__(256)
-gn_prefold_kernel(const float* __restrict__ pre, int splits, int groups, float* __restrict__ out /*[item][group][2]*/) {
-  __shared__ double2 sh[256];
+gn_prefold_kernel(const float* __restrict__ pre, int splits, int groups, float* __restrict__ out /*[item][part][group][2]*/) {
+  __shared__ double2 sh[8][64];
   pdl_wait();
-  const int g = blockIdx.x, item = blockIdx.y;
-  double a = 0.0, q = 0.0;
-  for (int sp = threadIdx.x; sp < splits; sp += 256) {
-    const float2 v = __ldg(reinterpret_cast<const float2*>(pre + ((((int64_t)item * splits + sp) * groups + g) << 1)));
-    a += (double)v.x;
-    q += (double)v.y;
-  }
-  sh[threadIdx.x] = make_double2(a, q);
-  __syncthreads();
-  for (int w = 128; w >= 1; w >>= 1) {
-    if (threadIdx.x < w) {
-      const double2 o = sh[threadIdx.x + w];
-      sh[threadIdx.x].x += o.x;
-      sh[threadIdx.x].y += o.y;
+  const int part = blockIdx.x, parts = gridDim.x, item = blockIdx.y;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int per = (splits + parts - 1) / parts;
+  const int s0 = part * per, s1 = (s0 + per < splits) ? s0 + per : splits;
+  for (int g = lane; g < groups; g += 32) {
+    double a = 0.0, q = 0.0;
+    for (int sp = s0 + warp; sp < s1; sp += 8) {
+      const float2 v = __ldg(reinterpret_cast<const float2*>(pre + ((((int64_t)item * splits + sp) * groups + g) << 1)));
+      a += (double)v.x;
+      q += (double)v.y;
     }
-    __syncthreads();
+    sh[warp][g] = make_double2(a, q);
   }
-  if (threadIdx.x == 0) {
-    float* dst = out + (((int64_t)item * groups + g) << 1);
-    dst[0] = (float)sh[0].x;  // the apply pass re-reads them as float partials (splits = 1)
-    dst[1] = (float)sh[0].y;
+  __syncthreads();
+  if (warp == 0) {
+    for (int g = lane; g < groups; g += 32) {
+      double a = 0.0, q = 0.0;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) { a += sh[w][g].x; q += sh[w][g].y; }
+      float* dst = out + ((((int64_t)item * parts + part) * groups + g) << 1);
+      dst[0] = (float)a;  // re-read by the apply pass as float partials
+      dst[1] = (float)q;
+    }
   }
 }
 
@@ -402,7 +407,7 @@ size_t group_norm_scratch_bytes(int64_t n_items, int64_t rows_per_item, int grou
   return ((partial + 255) & ~(size_t)255) + sizeof(float2) * (size_t)n_items * groups;
 }
 
-constexpr int GN_DIRECT_FOLD_MAX = 512;  // 32-row blocks per item an apply CTA folds by itself (128 KiB out of L2)
+constexpr int GN_DIRECT_FOLD_MAX = 24;   // 32-row blocks per item an apply CTA folds by itself; more go through gn_prefold
 
 template <bool F16>
 static int group_norm_t(const void* x1, int C1, const void* x2, int C2, const float* gamma, const float* beta, void* y,
@@ -429,14 +434,24 @@ static int group_norm_t(const void* x1, int C1, const void* x2, int C2, const fl
     // statistics emitted by the producing GEMM (one partial per 32-row block): no pass over the activation
     B2V_CHECK(C2 == 0 && rows_per_item % 32 == 0, "group_norm: precomputed statistics need whole 32-row blocks, no concat");
     const int64_t blocks = rows_per_item / 32;
-    if (blocks <= GN_DIRECT_FOLD_MAX) {
+    static int direct_max = -1;  // B2V_GN_DIRECT_FOLD=<blocks>: A/B knob
+    if (direct_max < 0) { const char* e = getenv("B2V_GN_DIRECT_FOLD"); direct_max = e ? atoi(e) : GN_DIRECT_FOLD_MAX; }
+    if (blocks <= direct_max) {
       fold_src = pre;
       fold_splits = (int)blocks;
     } else {
-      B2V_CUDA_OK(launch_pdl(gn_prefold_kernel, dim3((unsigned)groups, (unsigned)n_items), dim3(256), 0, s, pre,
+      // enough CTAs to pull the table out of L2 quickly (>= 64 blocks each), at most 16 partials per item for the apply
+      int parts = (int)((blocks + 63) / 64);
+      const int want = (int)((2 * (int64_t)sm_count() + n_items - 1) / n_items);
+      if (parts > want) parts = want;
+      if (parts > 16) parts = 16;
+      if (parts < 1) parts = 1;
+      B2V_CHECK(sizeof(float) * 2 * (size_t)n_items * parts * groups <= group_norm_scratch_bytes(n_items, rows_per_item, groups),
+                "group_norm: scratch too small for the pre-fold");
+      B2V_CUDA_OK(launch_pdl(gn_prefold_kernel, dim3((unsigned)parts, (unsigned)n_items), dim3(256), 0, s, pre,
                              (int)blocks, groups, partial));
       count_launch();
-      fold_splits = 1;
+      fold_splits = parts;
     }
   } else {
     B2V_CUDA_OK(launch_pdl(gn_stats_kernel<F16>, grid, dim3(threads), shb, s, (const __nv_bfloat16*)x1, C1,

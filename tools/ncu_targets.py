@@ -52,3 +52,23 @@ if what in ("sha", "all"):
     zl, el = [zs[i] for i in range(50)], [es[i] for i in range(50)]
     t(lambda: ops.sha256_leaves(zl, el, prefixes=list(range(50)), mode=1), "sha256 chain kernel, 50 XL leaves")
     t(lambda: ops.sha256_leaves(zl[:1], el[:1], prefixes=[981], mode=3), "sha256 warp kernel, 1 XL leaf")
+if what in ("fuse", "all"):
+    # round 2 fusions at the level-0 shape (2 x 16 frames of 72 x 128, C = 320):
+    # (a) proj_out-like GEMM emitting GroupNorm statistics -> group_norm_pre (no statistics pass): traffic of the norm
+    # (b) to_out-like GEMM emitting row partials -> QKV GEMM that finishes the LayerNorm in its epilogue
+    a = torch.randn(M, 320, device=dev).bfloat16()
+    w = (torch.randn(320, 320, device=dev) / math.sqrt(320)).bfloat16()
+    bias = torch.zeros(320, device=dev)
+    res = torch.randn(M, 320, device=dev).bfloat16()
+    g, b = torch.ones(320, device=dev), torch.zeros(320, device=dev)
+    out, st = ops.gemm_gnstats(a, w, bias=bias, residual=res, groups=32)
+    t(lambda: ops.gemm_gnstats(a, w, bias=bias, residual=res, groups=32), "gemm N=320 K=320 res + GN stats")
+    t(lambda: ops.group_norm_pre(out, g, b, 32, 32, 1e-5, True, st), "group_norm_pre+silu L0 (items=32, 288 blocks)")
+    t(lambda: ops.group_norm_pre(out, g, b, 2, 32, 1e-5, True, st), "group_norm_pre+silu L0 temporal (items=2: prefold)")
+    h, rs = ops.gemm_rowstats(a, w, bias=bias, residual=res)
+    t(lambda: ops.gemm_rowstats(a, w, bias=bias, residual=res), "gemm N=320 K=320 res + row stats")
+    w3 = (torch.randn(960, 320, device=dev) / math.sqrt(320)).bfloat16()
+    cs = w3.float().sum(1)
+    b3 = torch.zeros(960, device=dev)
+    t(lambda: ops.gemm_lnin(h, w3, b3, cs, rs), "gemm N=960 K=320 LayerNorm in the epilogue")
+    t(lambda: ops.gemm(h, w3), "gemm N=960 K=320 plain (for comparison)")
