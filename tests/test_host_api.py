@@ -301,3 +301,52 @@ def test_frame_decode_and_validator_have_no_cpu_path():
             ops.softmax_rows_(torch.zeros(4, 8, dtype=torch.bfloat16), 1.0)
         with pytest.raises(B2VError):
             ops.base64_decode_rows(torch.zeros(1, 16, dtype=torch.uint8))
+
+
+def test_leaf_store_host_semantics():
+    """The (caller_hotkey, request_id) store of miner.py:131/636/813-888 without a GPU: a stand-in trajectory records what
+    was asked of it; None / 'unknown' / delete-after-reveal / never-raise behaviour is the reference's."""
+    import types
+    from b2v.miner import LeafStore
+
+    class FakeTraj:
+        timesteps = [981, 961, 941]
+
+        def __init__(self):
+            self.asked = []
+
+        def reveal(self, indices):
+            self.asked.append(list(indices))
+            return {int(i): (("z%d" % i, "e%d" % i, ["p"]) if int(i) in self.timesteps else None) for i in indices}
+
+    st, tr = LeafStore(), FakeTraj()
+    assert st.open_leaves([1, 2], request_id=None, caller_hotkey="hk") == {1: None, 2: None}
+    assert st.open_leaves([981], request_id="nope", caller_hotkey="hk") == {981: None}
+    st.put("hk", "r", tr)
+    assert len(st) == 1
+    got = st.open_leaves(["981", 7], request_id="r", caller_hotkey="hk")
+    assert got == {981: ("z981", "e981", ["p"]), 7: None} and tr.asked == [[981, 7]] and len(st) == 0
+    assert st.open_leaves([981], request_id="r", caller_hotkey="hk") == {981: None}      # gone after one reveal
+    st.put("unknown", "r2", tr)
+    assert st.open_leaves([961], request_id="r2")[961][0] == "z961"                      # caller_hotkey None -> 'unknown'
+    st.put("hk", "s", tr)
+    syn = types.SimpleNamespace(indices=[941, 5], request_id="s", caller_hotkey="hk", leaves=None)
+    assert st.forward_reveal_leaves(syn) is syn and syn.leaves == {941: ("z941", "e941", ["p"]), 5: None} and len(st) == 0
+    bad = types.SimpleNamespace(indices=["x"], request_id="s", caller_hotkey="hk", leaves=None)
+    assert st.forward_reveal_leaves(bad).leaves == {"x": None}                           # never raises
+    st.put("hk", "t", tr)
+    resp = st.spot_check_all("hk", "t")
+    assert set(resp["leaf_data"]) == {981, 961, 941} and resp["seed"] == 0 and resp["challenge"] == "" and len(st) == 0
+    assert st.spot_check_all("hk", "t")["leaf_data"] == {} and st.spot_check_all(None, "t")["leaf_data"] == {}
+
+
+def test_bench_flops_model_matches_baseline_table():
+    """bench.py's host-side FLOP model (the denominator of every roofline) against BASELINE.md section 3."""
+    import importlib.util
+    spec = importlib.util.spec_from_file_location("bench_mod", os.path.join(ROOT, "bench.py"))
+    bench = importlib.util.module_from_spec(spec)
+    spec.loader.exec_module(bench)
+    # BASELINE.md counts a few small projections more (0.1 %): agreement within 0.3 %
+    for (F, h, w), tf in (((24, 72, 128), 156.97), ((16, 72, 128), 104.59), ((4, 72, 128), 26.12), ((24, 40, 72), 42.79)):
+        assert abs(bench.unet_flops(F, h, w) / 1e12 / tf - 1.0) < 3e-3, (F, h, w)
+    assert abs(bench.video_step_flops([(0, 16), (12, 24)], 72, 128) / 1e12 / 183.0 - 1.0) < 3e-3
