@@ -220,6 +220,34 @@ def test_attention(cuda, act, nb, heads, Sq, Skv, kv_group):
     assert err < tol(act, 1e-2), err
 
 
+@pytest.mark.parametrize("amp,drift", [(4.0, 0.0), (10.0, 0.0), (2.0, 40.0), (1.0, 400.0)])
+def test_attention_sharp_rows_and_moving_maximum(cuda, act, amp, drift):
+    """The softmax paths the unit-variance test does not reach: near one-hot rows (amp), a row maximum that keeps growing
+    along the kv axis (drift: every kv tile beats the reference of the one before it, so O is rescaled in TMEM tile after
+    tile) and score ranges beyond the exponent field (drift 400: the FMA-pipe exponentials clamp at 2^-125, the MUFU ones
+    flush to zero, both vanish against the row's maximum)."""
+    from b2v import ops
+    g = torch.Generator(device="cuda").manual_seed(int(amp * 10 + drift))
+    nb, heads, Sq, Skv = 2, 2, 384, 1024
+    D = heads * 64
+    q = torch.randn(nb, Sq, D, device=cuda, generator=g) * amp
+    k = torch.randn(nb, Skv, D, device=cuda, generator=g)
+    if drift:
+        # a component of k that grows with the kv index, aligned with a constant component of q: scores rise by `drift`
+        # (in logit units) from the first to the last kv position
+        q[:, :, 0::64] = 8.0
+        k[:, :, 0::64] = torch.linspace(0, drift, Skv, device=cuda)[None, :, None] / 8.0 * 8.0
+    v = torch.randn(nb, Skv, D, device=cuda, generator=g)
+    q, k, v = A(q), A(k), A(v)
+    out = ops.attention(q, k, v, heads)
+    qh, kh, vh = (t.float().reshape(nb, -1, heads, 64).transpose(1, 2) for t in (q, k, v))
+    ref = (torch.softmax(qh @ kh.transpose(-1, -2) * 0.125, -1) @ vh).transpose(1, 2).reshape(nb, Sq, D)
+    assert bool(torch.isfinite(out).all())
+    err = rel_l2(out, ref)
+    print("attention sharp", act, (amp, drift), "rel-l2 %.3e" % err)
+    assert err < tol(act, 1.2e-2), err
+
+
 @pytest.mark.parametrize("B,F,HW,heads", [(1, 4, 64, 1), (2, 8, 100, 5), (2, 16, 45, 20), (1, 24, 33, 8), (1, 1, 16, 2)])
 def test_temporal_attention(cuda, act, B, F, HW, heads):
     from b2v import ops
