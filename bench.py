@@ -435,7 +435,8 @@ def gpu_main(args):
         emit({"metric": METRIC, "value": value, "unit": "steps/s", "n_gpus": world, "steps": args.steps,
               "warmup": args.warmup, "ms_per_step": per_step_ms, "gpu_launches": int(launches), "clocks": clocks,
               "roofline": roofline, "roofline_step": roofline_step, "e2e": {"value": e2e_value, "unit": "steps/s"},
-              "note": "--timed-only: auxiliary legs skipped"})
+              "exchange_blend_ms": exch["ms"] if exch else None, "exchange_parity": exch["parity"] if exch else None,
+              "exchange": exch, "note": "--timed-only: auxiliary legs skipped"})
         if world > 1:
             dist.barrier()
             dist.destroy_process_group()
@@ -564,7 +565,43 @@ def exchange_leg(torch, dist, dev, plan, rank, world, my_windows, h, w, iters=5)
     dist.all_reduce(hi, op=dist.ReduceOp.MAX)
     ok = bool(same.item()) and int(lo.item()) == int(hi.item())
     payload = sum(t.numel() * t.element_size() for _, _, t in my_windows)
-    return {"ms": ms, "parity": "bit-exact" if ok else "MISMATCH", "transports_equal": bool(same.item()),
+    # per-step halo exchange (--halo_sync): the neighbours' overlap frames read out of their HBM over NVLink
+    # and crossfaded, against the same synchronisation done by ONE process holding every window (gathered over NCCL)
+    halo = None
+    try:
+        hs = exchange.HaloSync(plan, world, rank, C_, h, w, dtype, dev)
+        lats = [t for _, _, t in my_windows]
+        got = hs.sync(lats)
+        torch.cuda.synchronize(dev)
+        dist.barrier()
+        h0, h1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+        h0.record()
+        for _ in range(iters):
+            got = hs.sync(lats)
+        h1.record()
+        torch.cuda.synchronize(dev)
+        ht = torch.tensor([h0.elapsed_time(h1) / iters], device=dev, dtype=torch.float64)
+        dist.all_reduce(ht, op=dist.ReduceOp.MAX)
+        every, _ = exchange.nccl_all_gather(my_windows, plan, rank, world, dev)
+
+        class OneRank:
+            ranges, overlap, chunk_size = [(s, e) for s, e, _ in every], plan.overlap, plan.chunk_size
+
+            @staticmethod
+            def of_rank(r):
+                return [(s, e) for s, e, _ in every]
+        one = exchange.HaloSync(OneRank, 1, 0, C_, h, w, dtype, dev)
+        ref = {(s, e): t for (s, e, _), t in zip(every, one.sync([t for _, _, t in every]))}
+        eq = torch.tensor([1 if all(torch.equal(g_, ref[(s, e)]) for (s, e, _), g_ in zip(my_windows, got)) else 0],
+                          device=dev)
+        dist.all_reduce(eq, op=dist.ReduceOp.MIN)
+        halo = {"ms": float(ht.item()), "parity": "bit-exact" if bool(eq.item()) else "MISMATCH",
+                "what": "HaloSync.sync of the denoised windows over NVLink peer mappings vs one process holding every window"}
+    except ValueError as ex:  # plans the halo exchange does not take (a frame under three windows)
+        halo = {"ms": None, "parity": "n/a", "what": str(ex)}
+    except Exception as ex:  # a report, never a reason to lose the line
+        halo = {"ms": None, "parity": "error", "what": repr(ex)}
+    return {"ms": ms, "halo_sync": halo, "parity": "bit-exact" if ok else "MISMATCH", "transports_equal": bool(same.item()),
             "ranks_equal": int(lo.item()) == int(hi.item()), "window_bytes_this_rank": payload,
             "what": "stage -> device barrier -> ONE blend kernel reading every window from its owner's HBM over NVLink "
                     "peer mappings -> barrier (p2p_fused_blend) vs all_gather_into_tensor + the same blend kernel on "
