@@ -99,7 +99,7 @@ struct GemmParams {
   int ln_slots;
   float ln_eps;
 };
-constexpr int FUSE_RSTAT = 16, FUSE_LNIN = 32;  // FUSE template argument: 0 | GNG (2, 4, 8) | FUSE_RSTAT | FUSE_LNIN
+constexpr int FUSE_RSTAT = 64, FUSE_LNIN = 128;  // FUSE template argument: 0 | GNG (2, 4, 8, 16) | FUSE_RSTAT | FUSE_LNIN
 
 constexpr int EPI_PLAIN = 0, EPI_GEGLU_T = 1, EPI_NCFHW = 2;
 
@@ -147,7 +147,7 @@ __device__ __forceinline__ uint64_t gelu_fast2(uint64_t x2) {
 // GEMMs were bound by the LSU/L2 request rate of the latter). With RES the residual panel ARRIVES in the same buffer by
 // TMA load and is updated in place; when a tile is one panel wide (all but BN = 256) two buffers alternate so the
 // residual of the NEXT tile is already in flight while this one is processed.
-// GNG > 0 (BN = 160 only): the 80 columns of this warp are GNG whole GroupNorm groups of the OUTPUT tensor. Every lane
+// GNG > 0: the columns of this warp (half a tile: 80 / 64 / 128) are GNG whole GroupNorm groups of the OUTPUT tensor. Every lane
 // accumulates {sum, sum of squares} of its row per group while the values pass through its registers, the warp folds the
 // 32 rows with a fixed-order shuffle tree (deterministic) and writes 2 GNG floats per 32-row block: the consumer's
 // GroupNorm needs no statistics pass over the activation (norm.cu: group_norm with `pre`).
@@ -156,7 +156,7 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
                                               uint8_t* stage0, uint32_t rbar0, uint32_t tmem_base, uint32_t tfull0,
                                               uint32_t tempty0, int warp, int lane, int num_tiles) {
   using Cfg = TileCfg<BN, GEGLU, RES, CG>;
-  constexpr int GNG = FUSE & 15;
+  constexpr int GNG = FUSE & 31;
   constexpr bool RSTAT = FUSE == FUSE_RSTAT, LNIN = FUSE == FUSE_LNIN;
   constexpr int OUT_COLS = Cfg::OUT_COLS;
   constexpr int NCH = OUT_COLS / 32;  // 16-column chunks per group
@@ -437,7 +437,7 @@ __device__ __forceinline__ void epilogue_loop(const GemmParams& p, const CUtenso
           rv[0] += __shfl_xor_sync(0xffffffffu, rv[0], off);
         }
       }
-      constexpr int SH = NV == 16 ? 1 : (NV == 8 ? 2 : 3);
+      constexpr int SH = NV == 32 ? 0 : (NV == 16 ? 1 : (NV == 8 ? 2 : 3));
       if ((lane & ((1 << SH) - 1)) == 0) {
         constexpr int CPG = (OUT_COLS / 2) / GNG;
         const int idx = lane >> SH;
@@ -731,19 +731,19 @@ int dispatch_gemm_t(int bn, bool geglu, const CUtensorMap& tmA, const CUtensorMa
       return fail(B2V_ERR_ARG, "no row-statistics tile for N");
     }
   }
+  if constexpr (CG == 2) {  // statistics-emitting epilogues exist for CTA pairs only (gn_stats_ok)
+    if (p.gn_stats) {
+      const int gng = (bn / 2) / (p.N / p.gn_groups);  // whole groups per epilogue warp (gn_stats_shape_ok)
+#define B2V_GNS(BN_, G_) if (bn == BN_ && gng == G_) return launch_plain<BN_, MODE, CG, F16, G_>(tmA, tmB, p, orows, oslabs, s)
+      B2V_GNS(160, 8); B2V_GNS(160, 4); B2V_GNS(160, 2);      // UNet: 320 / 640 / 1280 channels
+      B2V_GNS(256, 16); B2V_GNS(256, 8); B2V_GNS(128, 16);    // SD VAE decoder: 256 / 512 / 128 channels
+#undef B2V_GNS
+      return fail(B2V_ERR_ARG, "gn_stats: no epilogue for tile %d with %d groups per warp", bn, gng);
+    }
+  }
   switch (bn) {
     case 256: return launch_plain<256, MODE, CG, F16>(tmA, tmB, p, orows, oslabs, s);
-    case 160:
-      if constexpr (CG == 2) {  // statistics-emitting epilogues exist for CTA pairs only (gn_stats_ok)
-        if (p.gn_stats) {
-          const int cpg = p.N / p.gn_groups;
-          if (cpg == 10) return launch_plain<160, MODE, CG, F16, 8>(tmA, tmB, p, orows, oslabs, s);
-          if (cpg == 20) return launch_plain<160, MODE, CG, F16, 4>(tmA, tmB, p, orows, oslabs, s);
-          if (cpg == 40) return launch_plain<160, MODE, CG, F16, 2>(tmA, tmB, p, orows, oslabs, s);
-          return fail(B2V_ERR_ARG, "gn_stats: %d channels per group unsupported", cpg);
-        }
-      }
-      return launch_plain<160, MODE, CG, F16>(tmA, tmB, p, orows, oslabs, s);
+    case 160: return launch_plain<160, MODE, CG, F16>(tmA, tmB, p, orows, oslabs, s);
     case 128: return launch_plain<128, MODE, CG, F16>(tmA, tmB, p, orows, oslabs, s);
     case 64: return launch_plain<64, MODE, CG, F16>(tmA, tmB, p, orows, oslabs, s);
   }
@@ -806,13 +806,17 @@ int pick_bn(int N, bool geglu, int64_t m_units, int cg) {
   return (N % 64 == 0) ? 64 : 0;
 }
 
-// The epilogue emits GroupNorm statistics when a warp's 80 output columns are whole groups (N a multiple of 160, 10 / 20
-// / 40 channels per group), the tile is 160 wide by the cost model's own choice, the rows form whole CTA-pair units
+// The epilogue emits GroupNorm statistics when an epilogue warp's columns (half a tile) are whole groups and that
+// (tile, groups-per-warp) pair is instantiated, the tile width is the cost model's own choice, the rows form whole CTA-pair units
 // (no clipped rows in any 32-row block) and there are at least two 128-row tiles per slab (CTA pairs).
 static bool gn_stats_shape_ok(int64_t M, int N, int64_t rpb, int groups, int bn, int cg) {
-  if (groups <= 0 || N % groups != 0) return false;
-  const int cpg = N / groups;
-  return bn == 160 && cg == 2 && N % 160 == 0 && (cpg == 10 || cpg == 20 || cpg == 40) && rpb % (BM * 2) == 0 && M % rpb == 0;
+  if (groups <= 0 || N % groups != 0 || bn <= 0 || N % bn != 0) return false;
+  const int cpg = N / groups, half = bn / 2;
+  if (cpg <= 0 || half % cpg != 0) return false;
+  const int gng = half / cpg;  // instantiated: 160 x {8, 4, 2}, 256 x {16, 8}, 128 x {16}
+  const bool inst = (bn == 160 && (gng == 8 || gng == 4 || gng == 2)) || (bn == 256 && (gng == 16 || gng == 8)) ||
+                    (bn == 128 && gng == 16);
+  return inst && cg == 2 && rpb % (BM * 2) == 0 && M % rpb == 0;
 }
 // number of {sum, sumsq} partials per row a GEMM with GemmArgs::row_stats writes (2 per N tile: one per epilogue warp
 // column half); 0 when the shape has no row-statistics epilogue (64-wide tiles)

@@ -12,6 +12,7 @@ csrc/norm.cu, the mid-block attention (ONE head of width 512) is S = Q K^T -> ro
 added after P V (rows of P sum to one). Weights are fed under their diffusers ``state_dict`` names. No CPU path.
 """
 import math
+import os
 from types import SimpleNamespace
 
 import torch
@@ -105,6 +106,10 @@ def canonical_keys(sd):
     return out
 
 
+def _gn_fuse():
+    return os.environ.get("B2V_GN_FUSE", "1") != "0"
+
+
 class AutoencoderKL:
     def __init__(self, config=None, device="cuda"):
         cfg = dict(SD_VAE_CONFIG)
@@ -191,11 +196,24 @@ class AutoencoderKL:
     # ---- layers (activations: channels-last bf16 rows [n*H*W, C]) -----------------------------------------------
     def _gn(self, x, p, n, silu=True):
         g, b = self._w[p]
+        pre = getattr(x, "_b2v_gn_stats", None)   # emitted by the conv / GEMM that produced x (see _conv)
+        if pre is not None:
+            return ops.group_norm_pre(x, g, b, n, self.config.norm_num_groups, self.config.norm_eps, silu, pre)
         return ops.group_norm(x, g, b, n, self.config.norm_num_groups, self.config.norm_eps, silu)
 
-    def _conv(self, x, p, n, H, W_, residual=None):
+    def _conv(self, x, p, n, H, W_, residual=None, feeds_gn=True):
+        """3x3 conv on rows [n*H*W, Cin]. Every conv of the decoder but conv_out feeds a GroupNorm: where the shape has a
+        statistics epilogue (b2v_gn_stats_ok) the conv also emits the {sum, sumsq} partials of its output and the norm
+        skips its first pass over the activation (B2V_GN_FUSE=0: off)."""
         w, b = self._w[p]
-        return ops.conv3x3(x.view(n, H, W_, x.shape[1]), w, b, residual=residual).view(n * H * W_, w.shape[0])
+        Cout, M = w.shape[0], n * H * W_
+        x4 = x.view(n, H, W_, x.shape[1])
+        if feeds_gn and _gn_fuse() and ops.gn_stats_ok(M, Cout, 0, self.config.norm_num_groups):
+            out, st = ops.conv3x3_gnstats(x4, w, b, residual=residual, groups=self.config.norm_num_groups)
+            out = out.view(M, Cout)
+            out._b2v_gn_stats = st
+            return out
+        return ops.conv3x3(x4, w, b, residual=residual).view(M, Cout)
 
     def _resnet(self, x, p, n, H, W_):
         h = self._conv(self._gn(x, p + ".norm1", n), p + ".conv1", n, H, W_)
@@ -223,6 +241,10 @@ class AutoencoderKL:
             ops.softmax_rows_(scores, 1.0 / math.sqrt(Cc))               # P
             ops.gemm(wv, t[rows], out=vt)                                # V^T = Wv X^T (bias deferred)
             ops.gemm(scores, vt, bias=bv, out=o[rows])                   # O = P V + bv
+        if _gn_fuse() and ops.gn_stats_ok(o.shape[0], wo.shape[0], 0, self.config.norm_num_groups):
+            out, st = ops.gemm_gnstats(o, wo, bias=bo, residual=x, groups=self.config.norm_num_groups)
+            out._b2v_gn_stats = st   # the next resnet's norm1 reads them
+            return out
         return ops.gemm(o, wo, bias=bo, residual=x)
 
     def _batch(self, T, H, W_):
@@ -251,7 +273,7 @@ class AutoencoderKL:
                 H, W_ = 2 * H, 2 * W_
                 x = self._conv(x.view(n * H * W_, -1), "decoder.up_blocks.%d.upsamplers.0.conv" % i, n, H, W_)
         x = self._gn(x, "decoder.conv_norm_out", n)
-        return self._conv(x, "decoder.conv_out", n, H, W_), H, W_
+        return self._conv(x, "decoder.conv_out", n, H, W_, feeds_gn=False), H, W_
 
     # ---- the reference's call: per-frame / per-batch decode of already scaled latents ---------------------------
     @torch.no_grad()
