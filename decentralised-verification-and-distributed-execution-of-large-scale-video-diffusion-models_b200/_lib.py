@@ -39,6 +39,8 @@ _SIGNATURES = {
     "b2v_merkle_depth": (_i, [_i]),
     "b2v_merkle_scratch_bytes": (_sz, [_i]),
     "b2v_merkle_build": (_i, [_vp, _i, _vp, _vp, _vp, _vp]),
+    "b2v_merkle_static_max_leaves": (_i, []),
+    "b2v_merkle_build_static": (_i, [_vp, _i, _vp, _vp, _vp]),
     "b2v_merkle_verify": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
     "b2v_merkle_verify_roots": (_i, [_vp, _vp, _i, _i, _vp, _vp, _vp]),
     "b2v_base64_len": (_u64, [_u64]),

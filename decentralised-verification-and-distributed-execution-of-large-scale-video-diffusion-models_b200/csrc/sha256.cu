@@ -12,6 +12,7 @@
 //                     block) and stores W[t]+K[t] to shared memory; warp 1 (consumer) runs the 64
 //                     dependent rounds per block reading the precomputed schedule. Double buffered.
 //   * lane kernel   : one lane per leaf for thousands of leaves (all 32 lanes busy in the rounds).
+#include <mutex>
 #include <vector>
 
 #include "common.cuh"
@@ -498,6 +499,78 @@ extern "C" int b2v_merkle_verify_roots(const uint8_t* leaf_hashes_dev, const uin
   merkle_verify_kernel<<<(m + 63) / 64, 64, 0, (cudaStream_t)stream>>>(leaf_hashes_dev, paths_dev, m, depth,
                                                                      roots_dev, 32, ok_dev);
   count_launch();
+  B2V_CUDA_OK(launch_check());
+  return 0;
+}
+
+// ---------------------------------------------------------------------------------------------------------------
+// Merkle build for callers that must not allocate (b2v.h: b2v_merkle_build_static).
+//
+// The tree levels live in one file-scope device array instead of a caller-supplied scratch buffer. Every device that
+// loads libb2v.so carries its own copy of the array (B2V_MERKLE_STATIC_BYTES, about 257 KiB) until the process exits.
+// The levels are written in full, bottom-up, before anything reads them, so nothing has to be cleared between calls;
+// what the previous call left behind is simply overwritten (and stays readable by nobody: the array is not exported).
+// ---------------------------------------------------------------------------------------------------------------
+#define B2V_MERKLE_STATIC_BYTES ((2 * (size_t)B2V_MERKLE_STATIC_MAX_LEAVES + 32) * 32 + 64)
+
+static __device__ __align__(256) uint8_t g_merkle_static_levels[B2V_MERKLE_STATIC_BYTES];
+
+namespace {
+// `g_merkle_static_levels` in HOST code is only a handle for the runtime's symbol table, not a device address: it must go
+// through cudaGetSymbolAddress, once per device and with that device current, before a kernel can be given it.
+constexpr int kMaxDevices = 64;
+std::mutex g_static_mu;
+uint8_t* g_static_levels_ptr[kMaxDevices] = {nullptr};
+
+int merkle_static_levels(uint8_t** out) {
+  int dev = -1;
+  B2V_CUDA_OK(cudaGetDevice(&dev));
+  B2V_CHECK(dev >= 0 && dev < kMaxDevices, "merkle_build_static: device ordinal %d outside [0,%d)", dev, kMaxDevices);
+  std::lock_guard<std::mutex> lock(g_static_mu);
+  if (!g_static_levels_ptr[dev]) {
+    void* p = nullptr;
+    B2V_CUDA_OK(cudaGetSymbolAddress(&p, g_merkle_static_levels));  // resolves on the CURRENT device (= dev)
+    B2V_CHECK(p != nullptr, "merkle_build_static: cudaGetSymbolAddress returned a null address on device %d", dev);
+    g_static_levels_ptr[dev] = (uint8_t*)p;
+  }
+  *out = g_static_levels_ptr[dev];
+  return 0;
+}
+}  // namespace
+
+extern "C" int b2v_merkle_static_max_leaves(void) { return B2V_MERKLE_STATIC_MAX_LEAVES; }
+
+extern "C" int b2v_merkle_build_static(const uint8_t* leaf_hashes_dev, int n, uint8_t* root_dev, uint8_t* paths_dev,
+                                       void* stream) {
+  B2V_CHECK(n >= 1, "merkle_build_static needs n >= 1 (the empty tree is handled by the host shim, proof.py:252)");
+  B2V_CHECK(n <= B2V_MERKLE_STATIC_MAX_LEAVES,
+            "merkle_build_static: %d leaves exceed the built-in scratch (B2V_MERKLE_STATIC_MAX_LEAVES = %d); "
+            "use b2v_merkle_build with a caller-provided scratch buffer for larger trees",
+            n, B2V_MERKLE_STATIC_MAX_LEAVES);
+  B2V_CHECK(b2v_merkle_scratch_bytes(n) <= B2V_MERKLE_STATIC_BYTES, "merkle_build_static: scratch bound violated");
+  B2V_CHECK(leaf_hashes_dev && root_dev, "null argument");
+  B2V_TRY(b2v_device_check());
+  uint8_t* levels = nullptr;
+  B2V_TRY(merkle_static_levels(&levels));  // first call on a device: symbol lookup; afterwards a table read
+  cudaStream_t s = (cudaStream_t)stream;
+  // Same launches as b2v_merkle_build from here on, against the built-in array. No cudaMalloc / cudaFree / pool use.
+  B2V_CUDA_OK(cudaMemcpyAsync(levels, leaf_hashes_dev, (size_t)n * 32, cudaMemcpyDeviceToDevice, s));
+  size_t off = 0;
+  int len = n;
+  while (len > 1) {
+    const int nn = (len + 1) >> 1;
+    merkle_level_kernel<<<(nn + 63) / 64, 64, 0, s>>>(levels + off * 32, len, levels + (off + (size_t)len) * 32);
+    count_launch();
+    off += (size_t)len;
+    len = nn;
+  }
+  B2V_CUDA_OK(cudaMemcpyAsync(root_dev, levels + off * 32, 32, cudaMemcpyDeviceToDevice, s));
+  const int depth = b2v_merkle_depth(n);
+  if (paths_dev && depth > 0) {
+    const int64_t total = (int64_t)n * depth * 8;
+    merkle_paths_kernel<<<(unsigned)((total + 255) / 256), 256, 0, s>>>(levels, n, depth, paths_dev);
+    count_launch();
+  }
   B2V_CUDA_OK(launch_check());
   return 0;
 }

@@ -190,6 +190,20 @@ def merkle_build(leaf_hashes, want_paths=True):
     return root, paths
 
 
+def merkle_build_static(leaf_hashes, root, paths=None):
+    """b2v_merkle_build_static: the Merkle build for hosts that may not allocate device memory at the call site (a commit
+    issued beside a running denoise loop, a process whose HBM is fully owned by its own pool). The caller brings the
+    outputs — root uint8[32], paths uint8[n,depth,32] or None — and the tree levels go to an array inside libb2v.so;
+    nothing is allocated here or in the library. n <= lib.b2v_merkle_static_max_leaves(), else B2VError. Calls share
+    that array: keep them on one stream."""
+    lib = _lib.load()
+    _cuda(leaf_hashes, "leaf_hashes"); _cuda(root, "root")
+    if paths is not None:
+        _cuda(paths, "paths")
+    check(lib.b2v_merkle_build_static(ptr(leaf_hashes), leaf_hashes.shape[0], ptr(root), ptr(paths), stream()))
+    return root, paths
+
+
 def merkle_verify(leaf_hashes, paths, root):
     lib = _lib.load()
     _cuda(leaf_hashes); _cuda(paths); _cuda(root)

@@ -75,6 +75,30 @@ size_t b2v_merkle_scratch_bytes(int n);
 int b2v_merkle_build(const uint8_t* leaf_hashes_dev, int n, uint8_t* root_dev, uint8_t* paths_dev,
                      void* scratch_dev, void* stream);
 
+/* b2v_merkle_build without a scratch argument and without any device allocation. It has no counterpart in the
+ * reference (which builds its tree in Python lists on the host); it exists for hosts that cannot hand this library a
+ * scratch buffer because they are not allowed to allocate one at the point of the call:
+ *   - a miner that commits its trajectory from a helper thread while the denoising loop is running on the same GPU:
+ *     cudaMalloc / cudaFree stall until the device is idle, so an allocation there stops the loop it runs beside;
+ *   - a serving process that has given all of HBM to its own pool (UNet workspace, VAE, leaf store) and reports
+ *     any allocation made behind its back as a leak, or simply has nothing left to give.
+ * The tree levels are kept in an array that is part of libb2v.so's device image: about 257 KiB on every GPU the
+ * library is loaded on, held until the process exits. Inputs and outputs are the caller's, as in b2v_merkle_build
+ * (leaf_hashes_dev [n][32] -> root_dev [32], paths_dev [n][depth][32] or NULL), and the results are the same bytes.
+ *   - n must be 1 .. B2V_MERKLE_STATIC_MAX_LEAVES (also returned by b2v_merkle_static_max_leaves()); anything larger
+ *     is refused with B2V_ERR_ARG and a message naming the limit, and needs b2v_merkle_build.
+ *   - the first call on each device looks up the array's device address (once per device, with that device
+ *     current) and remembers it; make that first call outside any stream capture, e.g. at start-up on a dummy leaf.
+ *   - all calls on a device share the one array. Nothing in it has to start at zero: each level is written in full
+ *     before it is read, so the previous call's contents are overwritten, never consumed. Two calls whose work
+ *     overlaps on the GPU (different streams, or different host threads on different streams) race on the array and
+ *     give wrong roots: issue them on one stream, or order them with events.
+ *   - it calls no cudaMalloc, cudaFree, stream-ordered allocator or other allocating routine. */
+#define B2V_MERKLE_STATIC_MAX_LEAVES 4096
+int b2v_merkle_static_max_leaves(void);
+int b2v_merkle_build_static(const uint8_t* leaf_hashes_dev, int n, uint8_t* root_dev, uint8_t* paths_dev,
+                            void* stream);
+
 /* Batched leaf verification (proof.py:291-304 verify_merkle_leaf): for each of m leaves fold
  * cur = SHA256(min(cur,sib)‖max(cur,sib)) over `depth` siblings and compare with root.
  * ok_dev[i] = 1/0. */
