@@ -23,6 +23,7 @@ parallelise ACROSS leaves, so
   step after its leaf, but the warp shares an SM with one CTA of every persistent GEMM and that CTA paces the kernel:
   measured +15 % per step (bench.py ``merkle.in_loop``). Use it only when the commitment must stream out during the run.
 """
+import time
 from typing import Dict, List, Optional, Tuple
 
 import torch
@@ -97,13 +98,44 @@ class LeafStore:
     """The miner's ``_leaf_data_by_request`` (miner.py:131, 636): committed trajectories parked per
     ``(caller_hotkey, request_id)`` until the validator asks for leaves, DEVICE-resident (a 50-step XL trajectory is
     177 MB of HBM; the reference keeps the same bytes on the host) and deleted after one reveal like the reference does
-    (miner.py:420, 841, 877)."""
+    (miner.py:420, 841, 877).
 
-    def __init__(self):
-        self._leaf_data_by_request: Dict[Tuple[str, str], Trajectory] = {}
+    Unlike the reference's dict the store is BOUNDED: a request that no validator ever spot-checks would otherwise stay
+    in HBM for the life of the process, until the UNet workspace or the VAE can no longer be allocated. ``put`` drops
+    the oldest entries beyond ``max_entries`` (default 64: about 11 GB of XL trajectories) and, with ``ttl_s``, those
+    older than that many seconds; a reveal for a dropped request answers like one for an unknown request (every index
+    -> None), which is what the reference answers for a request it does not hold. ``evicted`` counts the drops."""
+
+    def __init__(self, max_entries: Optional[int] = 64, ttl_s: Optional[float] = None, clock=time.monotonic):
+        if max_entries is not None and int(max_entries) < 1:
+            raise ValueError("LeafStore: max_entries must be >= 1 or None")
+        self.max_entries = None if max_entries is None else int(max_entries)
+        self.ttl_s = None if ttl_s is None else float(ttl_s)
+        self._clock = clock
+        self._born: Dict[Tuple[str, str], float] = {}
+        self.evicted = 0
+        self._leaf_data_by_request: Dict[Tuple[str, str], Trajectory] = {}   # insertion-ordered: oldest first
+
+    def _drop(self, key):
+        self._leaf_data_by_request.pop(key, None)
+        self._born.pop(key, None)
+        self.evicted += 1
+
+    def _expire(self):
+        if self.ttl_s is not None:
+            now = self._clock()
+            for key in [k for k, t in self._born.items() if now - t > self.ttl_s]:
+                self._drop(key)
+        if self.max_entries is not None:
+            while len(self._leaf_data_by_request) > self.max_entries:
+                self._drop(next(iter(self._leaf_data_by_request)))
 
     def put(self, caller_hotkey, request_id, trajectory: Trajectory):
-        self._leaf_data_by_request[(caller_hotkey, request_id)] = trajectory   # miner.py:636
+        key = (caller_hotkey, request_id)
+        self._leaf_data_by_request.pop(key, None)          # a re-commit of the same request becomes the newest entry
+        self._leaf_data_by_request[key] = trajectory       # miner.py:636
+        self._born[key] = self._clock()
+        self._expire()
 
     def __len__(self):
         return len(self._leaf_data_by_request)
@@ -116,11 +148,13 @@ class LeafStore:
         if request_id is None:
             return {i: None for i in indices}
         key = (caller_hotkey, request_id)
+        self._expire()
         traj = self._leaf_data_by_request.get(key)
         if not traj:
             return {i: None for i in indices}
         result = traj.reveal(indices)
         del self._leaf_data_by_request[key]
+        self._born.pop(key, None)
         return result
 
     def forward_reveal_leaves(self, synapse):
@@ -129,12 +163,14 @@ class LeafStore:
         try:
             indices = [int(i) for i in synapse.indices]
             key = (synapse.caller_hotkey, synapse.request_id)
+            self._expire()
             traj = self._leaf_data_by_request.get(key)
             if not traj:
                 synapse.leaves = {i: None for i in indices}
                 return synapse
             result = traj.reveal(indices)
             del self._leaf_data_by_request[key]
+            self._born.pop(key, None)
             synapse.leaves = result
             return synapse
         except Exception:
@@ -149,12 +185,14 @@ class LeafStore:
         if caller_hotkey is None:
             return empty
         key = (caller_hotkey, request_id)
+        self._expire()
         traj = self._leaf_data_by_request.get(key)
         if not traj:
             return empty
         try:
             result = traj.reveal(traj.timesteps)
             del self._leaf_data_by_request[key]
+            self._born.pop(key, None)
             return dict(empty, leaf_data=result)
         except Exception:
             return empty
