@@ -214,6 +214,19 @@ def vram_mb(device):
         return 0
 
 
+MAX_FRAMES_PER_FORWARD = 32   # b2v_unet3d_forward / b2v_op_temporal_attention: one window's frames stay in registers
+
+
+def check_pre_steps(pre_steps, num_frames):
+    """--pre_steps sends the WHOLE video through the UNet in one forward; one forward takes at most 32 frames. The
+    legacy coordinator (run_worker.py:161-176) pre-denoises at any length — this port refuses up front, before any model
+    is loaded, instead of failing with B2V_ERR_ARG inside the first pre-denoise step."""
+    if int(pre_steps or 0) > 0 and int(num_frames) > MAX_FRAMES_PER_FORWARD:
+        raise ValueError("--pre_steps %d: the pre-denoise runs all %d frames through the UNet in one forward, and one "
+                         "forward takes at most %d frames; use --pre_steps 0 for longer videos"
+                         % (int(pre_steps), int(num_frames), MAX_FRAMES_PER_FORWARD))
+
+
 class WindowedDiffuser:
     """Engine behind ChunkedVideoDiffuser (chunk_only.py:36) and DistributedVideoDiffuser
     (fsdp_chunked_coherent.py:47, fsdp_chunked.py:45). ``cfg`` is the argparse namespace of the script.
@@ -226,6 +239,8 @@ class WindowedDiffuser:
 
     def __init__(self, cfg, pipe=None, denoise_fn=None, blend_fn=None, base=None):
         self.cfg = cfg
+        if denoise_fn is None:
+            check_pre_steps(getattr(cfg, "pre_steps", 0), cfg.num_frames)
         self.rank, self.world, self.local_rank = init_distributed(cfg.device)
         self.device = torch.device("cuda", self.local_rank) if cfg.device.startswith("cuda") else torch.device("cpu")
         self.dtype = torch_dtype(getattr(cfg, "dtype", "bf16"))
@@ -305,6 +320,7 @@ class WindowedDiffuser:
         n = int(getattr(self.cfg, "pre_steps", 0) or 0)
         if n <= 0 or self._denoise_fn is not None:
             return base
+        check_pre_steps(n, base.shape[2])
         if getattr(self, "_cuda_denoiser", None) is None:
             self._cuda_denoiser = CudaDenoiser(self.pipe, self.uncond_emb, self.cond_emb, self.guidance_scale,
                                                ctx=self.ctx, context_weight=self.context_weight if self.use_ctx else 0.0)

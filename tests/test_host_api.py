@@ -340,6 +340,48 @@ def test_leaf_store_host_semantics():
     assert st.spot_check_all("hk", "t")["leaf_data"] == {} and st.spot_check_all(None, "t")["leaf_data"] == {}
 
 
+def test_leaf_store_is_bounded():
+    """Requests nobody spot-checks must not pile up in HBM: oldest-first eviction beyond max_entries, optional time to
+    live, evicted requests answer like unknown ones (the reference's answer for a request it does not hold)."""
+    from b2v.miner import LeafStore
+
+    class T:
+        timesteps = [1]
+
+        def reveal(self, indices):
+            return {int(i): ("z", "e", []) for i in indices}
+
+    st = LeafStore(max_entries=3)
+    for k in range(5):
+        st.put("hk", "r%d" % k, T())
+    assert len(st) == 3 and st.evicted == 2
+    assert st.open_leaves([1], request_id="r0", caller_hotkey="hk") == {1: None}          # evicted = unknown
+    assert st.open_leaves([1], request_id="r4", caller_hotkey="hk") == {1: ("z", "e", [])}
+    st.put("hk", "r2", T())                                                               # re-commit: newest again
+    st.put("hk", "r5", T()); st.put("hk", "r6", T())
+    assert [k[1] for k in st._leaf_data_by_request] == ["r2", "r5", "r6"] and set(st._born) == set(st._leaf_data_by_request)
+    now = [0.0]
+    st = LeafStore(max_entries=None, ttl_s=10.0, clock=lambda: now[0])
+    st.put("hk", "old", T()); now[0] = 8.0; st.put("hk", "new", T()); now[0] = 12.0
+    assert st.spot_check_all("hk", "old")["leaf_data"] == {} and len(st) == 1 and st.evicted == 1
+    assert st.spot_check_all("hk", "new")["leaf_data"] == {1: ("z", "e", [])} and len(st) == 0 and not st._born
+    assert len(LeafStore()._leaf_data_by_request) == 0 and LeafStore().max_entries == 64
+    with pytest.raises(ValueError):
+        LeafStore(max_entries=0)
+
+
+def test_pre_steps_is_refused_up_front_beyond_one_forward():
+    """--pre_steps runs the whole video through one UNet forward (<= 32 frames): BASELINE's 96-frame plan must fail with a
+    clear message before any model is built, not with B2V_ERR_ARG in the first pre-denoise step."""
+    from b2v.strategies import common
+    common.check_pre_steps(0, 96); common.check_pre_steps(3, 32); common.check_pre_steps(None, 500)
+    with pytest.raises(ValueError, match="at most 32 frames"):
+        common.check_pre_steps(3, 96)
+    cfg = chunk_only.parse_args(["--num_frames", "96", "--pre_steps", "3"])
+    with pytest.raises(ValueError, match="--pre_steps 3"):   # raised before init_distributed / any CUDA call
+        common.WindowedDiffuser(cfg)
+
+
 def test_bench_flops_model_matches_baseline_table():
     """bench.py's host-side FLOP model (the denominator of every roofline) against BASELINE.md section 3."""
     import importlib.util
