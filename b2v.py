@@ -13,7 +13,7 @@ _pkg = importlib.import_module(PKG_NAME)
 sys.modules[__name__] = _pkg
 sys.modules.setdefault("b2v", _pkg)
 # make ``import b2v.ops`` / ``from b2v.strategies import chunk_only`` resolve to the SAME module objects
-for _sub in ("ops", "scheduler", "unet", "pipeline", "planner", "proof", "strategies", "strategies.common",
+for _sub in ("_lib", "ops", "checkpoint", "vae", "validator", "scheduler", "unet", "pipeline", "planner", "proof", "strategies", "strategies.common",
              "strategies.chunk_only", "strategies.fsdp_chunked_coherent", "strategies.fsdp_chunked",
              "strategies.fsdp", "build", "exchange", "miner"):
     try:

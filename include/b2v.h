@@ -257,8 +257,10 @@ int b2v_op_layer_norm(const void* x_dev, const float* gamma_dev, const float* be
  * norm_{i+1}, proj_out -> the next block's norm: the statistics pass over the activation disappears).
  * b2v_op_gemm_gnstats / b2v_op_conv3x3_gnstats are b2v_op_gemm / b2v_op_conv3x3 (stride 1, TMA im2col) whose epilogue
  * also writes gn_stats_dev[M/32][gn_groups][2] = fp32 {sum, sum of squares} of the output per 32-row block and group
- * (fixed-order, bit-reproducible). Shapes qualify when b2v_gn_stats_ok() is 1 (N a multiple of 160 with 10 / 20 / 40
- * channels per group, whole 256-row units); otherwise the calls fail with B2V_ERR_ARG.
+ * (fixed-order, bit-reproducible). Shapes qualify when b2v_gn_stats_ok() is 1: the GEMM's tile width (160 for the UNet's
+ * 320 / 640 / 1280 channels, 256 or 128 for the VAE decoder's 512 / 256 / 128) holds whole groups per half tile (10 / 20 /
+ * 40 channels per group at 160; 16 / 32 at 256; 4 at 128) and M is whole 256-row units; otherwise the calls fail with
+ * B2V_ERR_ARG. The consumer folds the partials per item in 32-row blocks, so rows_per_item must be a multiple of 32.
  * b2v_op_group_norm_pre is b2v_op_group_norm (no concat) fed with such statistics instead of its own first pass. */
 int b2v_gn_stats_ok(int64_t M, int N, int64_t rows_per_batch, int groups);
 int b2v_op_gemm_gnstats(const void* a_dev, const void* w_dev, const float* bias_dev, const float* rowbias_dev,
