@@ -893,6 +893,10 @@ int gemm_tiled(const GemmArgs& g, cudaStream_t s) {
   }
   if (g.row_stats) {
     B2V_CHECK(!geglu && !p.gelu && g.taps == 1 && !p.gn_stats && bn != 64, "row_stats: plain linear epilogues only");
+    // The epilogue writes a row's partials for every lane of a 128-row tile below M. With several slabs whose length is
+    // not whole M units, the clipped tail lanes of one slab would alias the first rows of the next and race with them.
+    B2V_CHECK(slabs == 1 || rpb % ((int64_t)BM * cg) == 0,
+              "row_stats: rows_per_batch=%lld must be a multiple of %d when M holds several slabs", (long long)rpb, BM * cg);
     p.row_stats = g.row_stats;
   }
   if (g.ln_stats) {
