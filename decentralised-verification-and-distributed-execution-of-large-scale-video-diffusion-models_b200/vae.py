@@ -201,6 +201,13 @@ class AutoencoderKL:
             return ops.group_norm_pre(x, g, b, n, self.config.norm_num_groups, self.config.norm_eps, silu, pre)
         return ops.group_norm(x, g, b, n, self.config.norm_num_groups, self.config.norm_eps, silu)
 
+    def _stats_ok(self, M, Cout, rows_per_item):
+        """May the producer of an [M, Cout] activation emit GroupNorm partials? The GEMM side needs whole 256-row tiles
+        (b2v_gn_stats_ok); the consuming b2v_op_group_norm_pre folds them per item in 32-row units, so a frame whose
+        H*W is not a multiple of 32 (20x20 latents) must take the two-pass norm instead, as unet.cu's gn() does."""
+        return (_gn_fuse() and rows_per_item % 32 == 0
+                and ops.gn_stats_ok(M, Cout, 0, self.config.norm_num_groups))
+
     def _conv(self, x, p, n, H, W_, residual=None, feeds_gn=True):
         """3x3 conv on rows [n*H*W, Cin]. Every conv of the decoder but conv_out feeds a GroupNorm: where the shape has a
         statistics epilogue (b2v_gn_stats_ok) the conv also emits the {sum, sumsq} partials of its output and the norm
@@ -208,7 +215,7 @@ class AutoencoderKL:
         w, b = self._w[p]
         Cout, M = w.shape[0], n * H * W_
         x4 = x.view(n, H, W_, x.shape[1])
-        if feeds_gn and _gn_fuse() and ops.gn_stats_ok(M, Cout, 0, self.config.norm_num_groups):
+        if feeds_gn and self._stats_ok(M, Cout, H * W_):
             out, st = ops.conv3x3_gnstats(x4, w, b, residual=residual, groups=self.config.norm_num_groups)
             out = out.view(M, Cout)
             out._b2v_gn_stats = st
@@ -241,7 +248,7 @@ class AutoencoderKL:
             ops.softmax_rows_(scores, 1.0 / math.sqrt(Cc))               # P
             ops.gemm(wv, t[rows], out=vt)                                # V^T = Wv X^T (bias deferred)
             ops.gemm(scores, vt, bias=bv, out=o[rows])                   # O = P V + bv
-        if _gn_fuse() and ops.gn_stats_ok(o.shape[0], wo.shape[0], 0, self.config.norm_num_groups):
+        if self._stats_ok(o.shape[0], wo.shape[0], S):
             out, st = ops.gemm_gnstats(o, wo, bias=bo, residual=x, groups=self.config.norm_num_groups)
             out._b2v_gn_stats = st   # the next resnet's norm1 reads them
             return out

@@ -104,6 +104,20 @@ def test_tiny_decoder_vs_oracle(cuda, n, h, w):
     assert cos >= 0.9995 and rel <= 2.5e-2, (cos, rel)
 
 
+def test_decoder_refuses_frames_off_the_attention_tile(cuda):
+    """A 20x20 latent (400 rows per frame: not a multiple of 64, nor of the 32-row blocks the GroupNorm statistics
+    epilogue is folded in) is refused up front by decode / decode_frames with a ValueError that names the rule, not by a
+    B2V_CHECK deep inside a norm — also when 16 frames make n*h*w a whole number of 256-row GEMM tiles."""
+    from oracle import vae_ref as V
+    _, net = _pair(cuda, V.TINY)
+    z = torch.randn(16, 4, 20, 20, device=cuda)
+    with pytest.raises(ValueError, match="multiple of 64"):
+        net.decode(z)
+    with pytest.raises(ValueError, match="multiple of 64"):
+        net.decode_frames(z.permute(1, 0, 2, 3).unsqueeze(0).contiguous())
+    assert not net._stats_ok(16 * 400, 128, 400) and net._stats_ok(16 * 1600, 128, 1600)
+
+
 def test_full_width_decoder_vs_oracle(cuda):
     """The SD VAE decoder at full width (49 490 199 parameters, the published decoder + post_quant_conv) on a 16 x 16
     latent: cos >= 0.9995, rel-l2 <= 2.5e-2 against fp32."""
