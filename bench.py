@@ -193,8 +193,9 @@ class CpuOracleArm:
         g = torch.Generator().manual_seed(0)
         lat = torch.randn(1, 4, F, h, w, generator=g)
         t0 = time.perf_counter()
+        ctx = lat.mean(dim=2, keepdim=True)              # fsdp_chunked_coherent.py:112-118 (stand-in: this window's mean)
         with torch.no_grad():
-            x = torch.cat([lat] * 2)
+            x = torch.cat([lat + CTX_W * ctx] * 2)      # fsdp_chunked_coherent.py:134-137 hybrid_ctx injection
             noise = self.net(x, t, self.emb)
             u, c = noise.chunk(2)
             out = self.sched.step(u + GUIDANCE * (c - u), t, lat).prev_sample
@@ -206,14 +207,15 @@ def cpu_line(args, ranges, h, w, as_reference):
     """CPU arm. as_reference (``--impl reference``): the whole-video step of the plan — every window at its real frame
     count, one after the other on the host — is MEASURED as often as a ~4 minute budget allows (at least once); nothing
     is extrapolated unless even one whole step does not fit, in which case the largest window is measured and the others
-    follow by their FLOP ratio (flagged). Otherwise (the cpu_baseline leg of the GPU line, ~30 s budget): ONE real
-    4-frame 72x128 window step is measured and scaled to the whole-video step by the FLOP ratio (flagged)."""
+    follow by their FLOP ratio (flagged). Otherwise (the cpu_baseline leg of the GPU line, ~45 s budget): ONE real
+    12-frame 72x128 window step (a window of the N = 1 plan) is measured and scaled to the whole-video step by the FLOP
+    ratio (flagged; small windows run the host less efficiently, so the largest affordable one is used)."""
     arm = CpuOracleArm()
     ts = [int(t) for t in arm.sched.timesteps]
     step_flops = video_step_flops(ranges, h, w)
     t_cal = arm.window_step(1, 16, 16, ts[0])            # warm-up of the thread pool / primitive caches
     if not as_reference:
-        F = min(4, max(e - s for s, e in ranges))
+        F = min(12, max(e - s for s, e in ranges))       # round 2: 4 frames x 7.00 was 40 % off the measured arm
         dt = arm.window_step(F, h, w, ts[0])
         ratio = step_flops / unet_flops(F, h, w)
         value = 1.0 / (dt * ratio)
@@ -264,6 +266,14 @@ def cpu_line(args, ranges, h, w, as_reference):
                            "probe_1_frame_s": t_probe, "calibration_s": t_cal, "sample": sample}
 
 
+def workload_config(plan, note, h, w):
+    """The `config` both arms print, key for key (the driver compares them): the workload, not how an arm ran it."""
+    return {"workload": "ZeroscopeXL 1024x576x24f fsdp_chunked_coherent hybrid_ctx, CFG 7.5, DDIM 50-step schedule",
+            "plan": {"note": note, "chunk_size": plan.chunk_size, "overlap": plan.overlap, "windows": plan.ranges},
+            "latent": [1, 4, FRAMES, h, w],
+            "l2": "no flush: each step streams 2.8 GB of weights + >2 GB of activations (>> 126 MB L2)"}
+
+
 # ---------------------------------------------------------------------------------------------------------------
 # GPU arm
 # ---------------------------------------------------------------------------------------------------------------
@@ -290,7 +300,7 @@ def gpu_main(args):
     plan = planner.plan(FRAMES, world, cs, ov, variant="coherent")
     mine = plan.of_rank(rank)
 
-    dtype = torch.bfloat16
+    dtype = {"bf16": torch.bfloat16, "fp16": torch.float16}[args.dtype]
     pipe = VideoPipeline.from_random("cerspense/zeroscope_v2_XL", device=dev, seed=1234, dtype=dtype)
     pipe.scheduler.set_timesteps(TOTAL_STEPS, device="cuda")
     ts = pipe.scheduler.host_timesteps()
@@ -323,7 +333,7 @@ def gpu_main(args):
 
     # the dominant kernel once BEFORE the load (clocks not yet pulled down by the power cap): reported next to the
     # in-load measurement the roofline uses
-    cold = dominant_kernel_roofline(torch, ops, dev, peaks, mine) if rank == 0 else None
+    cold = dominant_kernel_roofline(torch, ops, dev, peaks, mine, dtype=dtype) if rank == 0 else None
     for i in range(args.warmup):
         video_step(i)
     sync_all()
@@ -410,6 +420,16 @@ def gpu_main(args):
     if world > 1:
         exch = exchange_leg(torch, dist, dev, plan, rank, world, [(s, e, st[0]) for (s, e), st in zip(mine, state)], h, w)
 
+    # ---- the same timed steps in the OTHER 16-bit arithmetic (fp16 = the reference's torch_dtype, chunk_only.py:44-47,
+    # and the strategy CLI's default; bf16 = the wider-range mode): same plan, same timing rules, every rank ----
+    other = None
+    if not args.timed_only:
+        try:
+            other = other_dtype_leg(torch, dist, dev, world, mine, h, w, args,
+                                    "bf16" if args.dtype == "fp16" else "fp16", sync_all)
+        except Exception as ex:  # a report, never a reason to lose the line
+            other = {"error": repr(ex)}
+
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -425,7 +445,7 @@ def gpu_main(args):
                      "frac": achieved_step / peaks["bf16_sustained"], "traffic": None,
                      "what": "whole UNet3D forward(s) of the bottleneck rank per video-step: algorithmic FLOPs "
                              "(b2v_unet3d_flops, MAC=2) / CUDA-event time; peak = sustained cuBLAS bf16, " + peaks["source"]}
-    roofline = dominant_kernel_roofline(torch, ops, dev, peaks, mine, in_load=True)
+    roofline = dominant_kernel_roofline(torch, ops, dev, peaks, mine, in_load=True, dtype=dtype)
     roofline["when"] = ("right after the timed steps, GPU under the power cap of the long step (clocks as in `clocks`): "
                         "sustained peak as denominator")
     roofline["cold"] = {"achieved": cold["achieved"], "peak": cold["peak"], "frac": cold["frac"],
@@ -468,13 +488,11 @@ def gpu_main(args):
     line = {
         "metric": METRIC, "value": value, "unit": "steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": per_step_ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "bf16", "data": "synthetic (random-init weights seed 1234, seeded prompt embeddings, seed-0 base noise)",
-        "config": {"workload": "ZeroscopeXL 1024x576x24f fsdp_chunked_coherent hybrid_ctx, CFG 7.5, DDIM 50-step schedule",
-                   "plan": {"note": plan_note, "chunk_size": plan.chunk_size, "overlap": plan.overlap,
-                            "windows": plan.ranges, "windows_per_rank": len(mine)},
-                   "reference_default_plan": ref_default,
-                   "latent": [1, 4, FRAMES, h, w], "unet_flops_per_step_bottleneck_rank": step_flops,
-                   "l2": "no flush: each step streams 2.8 GB of weights + >2 GB of activations (>> 126 MB L2)"},
+        "dtype": args.dtype, "other_dtype": other,
+        "data": "synthetic (random-init weights seed 1234, seeded prompt embeddings, seed-0 base noise)",
+        "config": workload_config(plan, plan_note, h, w),
+        "run": {"windows_per_rank": len(mine), "unet_flops_per_step_bottleneck_rank": step_flops,
+                "reference_default_plan": ref_default},
         "e2e": {"value": e2e_value, "unit": "steps/s", "h2d_bytes_per_step": bi, "d2h_bytes_per_step": bo},
         "gpu_launches": int(launches), "clocks": clocks, "roofline": roofline, "roofline_step": roofline_step,
         "merkle": merkle, "frame_decode": decode, "cpu_baseline": cpu, "gpu_torch_eager": eager,
@@ -487,6 +505,57 @@ def gpu_main(args):
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
+
+
+def other_dtype_leg(torch, dist, dev, world, mine, h, w, args, name, sync_all):
+    """The headline's timed region again with latents and UNet arithmetic in `name`: its own pipeline (same seed, same
+    weights rounded to that type), W warm-up steps, K timed steps between CUDA events, max over ranks."""
+    from b2v import ops
+    from b2v.pipeline import VideoPipeline
+    from b2v.strategies.common import CudaDenoiser, base_noise
+    dtype = {"bf16": torch.bfloat16, "fp16": torch.float16}[name]
+    pipe = VideoPipeline.from_random("cerspense/zeroscope_v2_XL", device=dev, seed=1234, dtype=dtype)
+    pipe.scheduler.set_timesteps(TOTAL_STEPS, device="cuda")
+    ts = pipe.scheduler.host_timesteps()
+    emb = pipe.text_encoder(pipe.tokenizer(["a rocket in space, 4k", ""]).input_ids)[0]
+    base = base_noise(4, FRAMES, h, w, dtype, dev)
+    ctx = ops.context_mean(base)
+    den = CudaDenoiser(pipe, emb[1:], emb[:1], GUIDANCE, ctx=ctx, context_weight=CTX_W)
+    state = []
+    for s, e in mine:
+        lat = base[:, :, s:e].clone()
+        x = ops.make_unet_input(lat, 2, ctx=ctx, ctx_w=CTX_W)
+        state.append([lat, x, torch.empty_like(x)])
+
+    def video_step(i):
+        t = ts[i % len(ts)]
+        for st in state:
+            pipe.unet.forward_into(st[1], t, den.emb, st[2])
+            st[0], st[1] = pipe.scheduler.fused_cfg_step(st[0], st[2], t, GUIDANCE, ctx=ctx, ctx_w=CTX_W, n_dup=2,
+                                                         xnext=st[1])
+
+    for i in range(args.warmup):
+        video_step(i)
+    sync_all()
+    l0 = ops.launch_count()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record()
+    for i in range(args.steps):
+        video_step(args.warmup + i)
+    e1.record()
+    sync_all()
+    launches = ops.launch_count() - l0
+    ms = torch.tensor([e0.elapsed_time(e1)], device=dev, dtype=torch.float64)
+    if world > 1:
+        dist.all_reduce(ms, op=dist.ReduceOp.MAX)
+    finite = all(bool(torch.isfinite(st[0].float()).all()) for st in state)
+    del state, den, pipe
+    torch.cuda.empty_cache()
+    per = float(ms.item()) / args.steps
+    return {"dtype": name, "value": 1e3 / per, "unit": "steps/s", "ms_per_step": per, "gpu_launches": int(launches),
+            "latents_finite": finite,
+            "what": "the headline's timed region (same plan, W warm-up + K timed steps, CUDA events, max over ranks) with "
+                    "latents and UNet arithmetic in this type"}
 
 
 def gpu_torch_eager(torch, dev, ranges, h, w):
@@ -660,7 +729,7 @@ def _time_cuda(torch, fn, iters=3, warm=2):
     return e0.elapsed_time(e1) / iters
 
 
-def dominant_kernel_roofline(torch, ops, dev, peaks, mine, in_load=False):
+def dominant_kernel_roofline(torch, ops, dev, peaks, mine, in_load=False, dtype=None):
     """The kernel with the largest share of a step (profiles/: attn_kernel at UNet level 0, spatial self-attention,
     seq 9216, 5 heads, batch 2*F) timed live with CUDA events. in_load: right after the timed steps, the GPU still under
     the power cap of the long step -> the SUSTAINED measured peak is the denominator; otherwise (cold, boost clocks, the
@@ -668,7 +737,7 @@ def dominant_kernel_roofline(torch, ops, dev, peaks, mine, in_load=False):
     F = max(e - s for s, e in mine)
     nb, heads, S = 2 * F, 5, (HEIGHT // 8) * (WIDTH // 8)
     g = torch.Generator(device=dev).manual_seed(0)
-    q, k, v = (torch.randn(nb, S, heads * 64, device=dev, generator=g).to(torch.bfloat16) for _ in range(3))
+    q, k, v = (torch.randn(nb, S, heads * 64, device=dev, generator=g).to(dtype or torch.bfloat16) for _ in range(3))
     ms = _time_cuda(torch, lambda: ops.attention(q, k, v, heads))
     flops = 4.0 * nb * heads * S * S * 64
     ach = flops / (ms / 1e3) / 1e12
@@ -681,6 +750,7 @@ def dominant_kernel_roofline(torch, ops, dev, peaks, mine, in_load=False):
             "traffic_source": "ncu --set full, profiles/rd2b_ncu_full_summary.md (bytes per launch)",
             "kernel": "attn_kernel (spatial self-attention L0)",
             "shape": {"batch": nb, "heads": heads, "seq": S, "head_dim": 64}, "ms_per_launch": ms,
+            "operand_dtype": str(q.dtype).replace("torch.", ""),
             "flops_per_launch": flops,
             "peak_source": ("sustained" if in_load else "burst") + " cuBLAS bf16, " + peaks["source"]}
 
@@ -828,6 +898,10 @@ def main():
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b2v", choices=["b2v", "reference"])
     ap.add_argument("--no-cpu-baseline", dest="no_cpu_baseline", action="store_true")
+    ap.add_argument("--dtype", default="fp16", choices=["fp16", "bf16"],
+                    help="16-bit arithmetic of the headline steps (latents + UNet). fp16 is the reference's torch_dtype "
+                         "(chunk_only.py:44-47), the strategy CLI's default and the mode that meets Appendix D's 1e-2 "
+                         "parity bar; the other type is timed too and reported under other_dtype")
     ap.add_argument("--timed-only", dest="timed_only", action="store_true",
                     help="only the timed denoise steps + e2e leg (no Merkle / decode / baseline legs): for ncu launch lists")
     args = ap.parse_args()
@@ -847,12 +921,10 @@ def main():
             "steps": args.steps, "warmup": args.warmup, "ms_per_step": per * 1e3, "higher_is_better": True,
             "scaling": "strong", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
             "extrapolated": cpu["extrapolated"], "measured_steps": cpu["measured_steps"], "measured_s": cpu["measured_s"],
-            "config": {"workload": "ZeroscopeXL 1024x576x24f fsdp_chunked_coherent hybrid_ctx, CFG 7.5, DDIM 50-step schedule",
-                       "plan": {"note": note, "chunk_size": plan.chunk_size, "overlap": plan.overlap, "windows": plan.ranges},
-                       "latent": [1, 4, FRAMES, h, w],
-                       "note": "CPU oracle port of the reference's step on the host cores; each whole-video step takes "
-                               "minutes on a CPU, so `steps` whole steps are measured only as far as a ~4 min budget "
-                               "allows (measured_steps); ms_per_step is the measured mean, not steps x anything"},
+            "config": workload_config(plan, note, h, w),
+            "note": "CPU oracle port of the reference's step on the host cores; each whole-video step takes minutes on a "
+                    "CPU, so `steps` whole steps are measured only as far as a ~4 min budget allows (measured_steps); "
+                    "ms_per_step is the measured mean, not steps x anything",
             "cpu_baseline": cpu, "e2e": {"value": value, "unit": "steps/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
             "gpu_launches": 0})
         return
