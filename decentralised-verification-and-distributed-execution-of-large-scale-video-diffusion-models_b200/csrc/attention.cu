@@ -38,7 +38,7 @@ __device__ __forceinline__ float ex2(float x) {
 // P never touches shared memory: the softmax warps write the rounded probabilities back to TMEM (tcgen05.st) and the
 // P V MMA takes its A operand from there — no st.shared, no MEMBAR + proxy fence, no operand fetch from shared
 // memory for P (measured with the FMA-pipe exponentials below: 4.49 -> 4.01 ms on the L0 shape,
-// profiles/r02_attn_ab.md).
+// profiles/rd2a_attn_ab_final.log).
 // ------------------------------------------------------------------------------------------------
 constexpr int AT_THREADS = 192;
 constexpr int AT_TILE = 16384;  // 128 rows x 64 bf16
