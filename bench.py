@@ -430,6 +430,22 @@ def gpu_main(args):
         except Exception as ex:  # a report, never a reason to lose the line
             other = {"error": repr(ex)}
 
+    # ---- N = 1: BASELINE configs[1] — Zeroscope v2 576w, 24 frames of 576x320 (latent 40x72), chunk_only windows, bf16
+    # as that config names it, and fp16; same timing rules (the schedule there is 25 steps: a step is a step) ----
+    config_576w = None
+    if world == 1 and not args.timed_only:
+        try:
+            config_576w = {"workload": "Zeroscope v2 576w, 24 frames 576x320 (latent 40x72), chunk_only windows "
+                                       "[(0,16),(12,24)], CFG 7.5, 25-step DDIM schedule (BASELINE configs[1])"}
+            for nm in ("bf16", "fp16"):
+                leg = other_dtype_leg(torch, dist, dev, world, [(0, 16), (12, 24)], 40, 72, args, nm, sync_all,
+                                      use_ctx=False)
+                leg["roofline_step"] = {"bound": "tensor", "achieved": leg["tflops"], "peak": peaks["bf16_sustained"],
+                                        "unit": "TFLOP/s", "frac": leg["tflops"] / peaks["bf16_sustained"]}
+                config_576w[nm] = leg
+        except Exception as ex:  # a report, never a reason to lose the line
+            config_576w = {"error": repr(ex)}
+
     if rank != 0:
         if world > 1:
             dist.barrier()
@@ -488,7 +504,7 @@ def gpu_main(args):
     line = {
         "metric": METRIC, "value": value, "unit": "steps/s", "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
         "ms_per_step": per_step_ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": args.dtype, "other_dtype": other,
+        "dtype": args.dtype, "other_dtype": other, "config_576w": config_576w,
         "data": "synthetic (random-init weights seed 1234, seeded prompt embeddings, seed-0 base noise)",
         "config": workload_config(plan, plan_note, h, w),
         "run": {"windows_per_rank": len(mine), "unet_flops_per_step_bottleneck_rank": step_flops,
@@ -507,7 +523,7 @@ def gpu_main(args):
         dist.destroy_process_group()
 
 
-def other_dtype_leg(torch, dist, dev, world, mine, h, w, args, name, sync_all):
+def other_dtype_leg(torch, dist, dev, world, mine, h, w, args, name, sync_all, use_ctx=True):
     """The headline's timed region again with latents and UNet arithmetic in `name`: its own pipeline (same seed, same
     weights rounded to that type), W warm-up steps, K timed steps between CUDA events, max over ranks."""
     from b2v import ops
@@ -519,19 +535,20 @@ def other_dtype_leg(torch, dist, dev, world, mine, h, w, args, name, sync_all):
     ts = pipe.scheduler.host_timesteps()
     emb = pipe.text_encoder(pipe.tokenizer(["a rocket in space, 4k", ""]).input_ids)[0]
     base = base_noise(4, FRAMES, h, w, dtype, dev)
-    ctx = ops.context_mean(base)
-    den = CudaDenoiser(pipe, emb[1:], emb[:1], GUIDANCE, ctx=ctx, context_weight=CTX_W)
+    ctx = ops.context_mean(base) if use_ctx else None
+    ctx_w = CTX_W if use_ctx else 0.0
+    den = CudaDenoiser(pipe, emb[1:], emb[:1], GUIDANCE, ctx=ctx, context_weight=ctx_w)
     state = []
     for s, e in mine:
         lat = base[:, :, s:e].clone()
-        x = ops.make_unet_input(lat, 2, ctx=ctx, ctx_w=CTX_W)
+        x = ops.make_unet_input(lat, 2, ctx=ctx, ctx_w=ctx_w)
         state.append([lat, x, torch.empty_like(x)])
 
     def video_step(i):
         t = ts[i % len(ts)]
         for st in state:
             pipe.unet.forward_into(st[1], t, den.emb, st[2])
-            st[0], st[1] = pipe.scheduler.fused_cfg_step(st[0], st[2], t, GUIDANCE, ctx=ctx, ctx_w=CTX_W, n_dup=2,
+            st[0], st[1] = pipe.scheduler.fused_cfg_step(st[0], st[2], t, GUIDANCE, ctx=ctx, ctx_w=ctx_w, n_dup=2,
                                                          xnext=st[1])
 
     for i in range(args.warmup):
@@ -549,11 +566,12 @@ def other_dtype_leg(torch, dist, dev, world, mine, h, w, args, name, sync_all):
     if world > 1:
         dist.all_reduce(ms, op=dist.ReduceOp.MAX)
     finite = all(bool(torch.isfinite(st[0].float()).all()) for st in state)
+    flops = sum(pipe.unet.flops(2, e - s, h, w) for s, e in mine)
     del state, den, pipe
     torch.cuda.empty_cache()
     per = float(ms.item()) / args.steps
     return {"dtype": name, "value": 1e3 / per, "unit": "steps/s", "ms_per_step": per, "gpu_launches": int(launches),
-            "latents_finite": finite,
+            "latents_finite": finite, "unet_flops_per_step": flops, "tflops": flops / (per / 1e3) / 1e12,
             "what": "the headline's timed region (same plan, W warm-up + K timed steps, CUDA events, max over ranks) with "
                     "latents and UNet arithmetic in this type"}
 
@@ -827,12 +845,15 @@ def merkle_bench(torch, ops, proof, dev, peaks, h, w, sm_mhz=None, cpu=True):
             dt = time.perf_counter() - t0
             out["e2e_build_merkle_tree_50"] = {"gb_per_s": alg / dt / 1e9, "ms": dt * 1e3,
                                                "note": "drop-in call incl. D2H of every leaf's bytes (return value): one "
-                                                       "pinned DMA under the hashing, then host slicing into bytes"}
+                                                       "pinned DMA and the host slicing into bytes both under the hashing"}
             if cpu:
                 # CPU baseline leg (the oracle / hashlib as the reported baseline, never the product): identical bytes
                 from oracle import merkle_ref as M
+                torch.cuda.synchronize()
+                t0 = time.perf_counter()   # what the reference does before it can hash (miner.py:203-204), per leaf
                 zb = [z.cpu().numpy().tobytes() for z in zl]
                 eb = [e.cpu().numpy().tobytes() for e in el]
+                t_fetch = time.perf_counter() - t0
                 t0 = time.perf_counter()
                 hs = [M.leaf_hash(t, z, e) for t, z, e in zip(ts, zb, eb)]
                 lv = M.tree_levels(hs)
@@ -848,7 +869,13 @@ def merkle_bench(torch, ops, proof, dev, peaks, h, w, sm_mhz=None, cpu=True):
                 out["cpu_baseline"] = {
                     "value": alg / tp / 1e9, "unit": "GB/s", "cores": cores, "kind": "reference",
                     "single_thread_gb_per_s": alg / t1 / 1e9, "single_thread_ms": t1 * 1e3, "pool_ms": tp * 1e3,
-                    "roots_equal": True,
+                    "roots_equal": True, "fetch_ms": t_fetch * 1e3,
+                    "like_for_like": {
+                        "what": "miner.py:203-233 as the reference runs it from device latents: z.cpu().numpy().tobytes() "
+                                "per leaf + hashlib leaves + tree; compares with e2e_build_merkle_tree_50 (device latents "
+                                "in, root + bytes + paths out)",
+                        "single_thread_ms": (t_fetch + t1) * 1e3, "pool_ms": (t_fetch + tp) * 1e3,
+                        "single_thread_gb_per_s": alg / (t_fetch + t1) / 1e9, "pool_gb_per_s": alg / (t_fetch + tp) / 1e9},
                     "sample": "the reference's construction (miner.py:207-233 leaf = sha256(be16(t) + z + eps) via hashlib, "
                               "proof.py:260-286 tree) on the same 50 leaves (%.1f MB): single thread as written, and "
                               "ThreadPoolExecutor(%d) over leaves; hashing only (bytes already on the host)"

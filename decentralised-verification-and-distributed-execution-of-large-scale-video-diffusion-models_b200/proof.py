@@ -213,14 +213,16 @@ def build_merkle_tree(latents, noise_preds, timesteps, with_bytes=True):
     """Drop-in for ``Miner._build_merkle_tree``: returns (root bytes, {t: (z_bytes, eps_bytes, [sibling, ...])}).
     The hashing happens on the device in place; the byte images are copied to the host only because the reference's
     return value contains them (with_bytes=False leaves them empty) — as one pinned DMA on a side stream UNDER the
-    hashing."""
+    hashing, and the host-side slicing into ``bytes`` also runs under it."""
     fetch = None
     if with_bytes:
         fetch = leaf_bytes_to_host([z.contiguous() for z in latents] + [e.contiguous() for e in noise_preds])
-    root, _, paths = commit_trajectory_device(latents, noise_preds, timesteps)
-    plist = _paths_as_lists(paths, len(timesteps))
+    root, _, paths = commit_trajectory_device(latents, noise_preds, timesteps)   # launches only: nothing waited for yet
     n = len(timesteps)
+    # the DMA (a few ms) ends long before the serial SHA-256 chains (54 ms for 50 XL leaves): cut the staging buffer into
+    # the per-leaf bytes objects NOW, while the device is still hashing, and only then wait for the tree
     blobs = fetch() if fetch is not None else [b""] * (2 * n)
+    plist = _paths_as_lists(paths, n)
     leaf_data = {}
     for i, t in enumerate(timesteps):
         leaf_data[int(t)] = (blobs[i], blobs[n + i], plist[i])
